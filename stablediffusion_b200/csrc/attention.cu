@@ -1,0 +1,352 @@
+// Fused flash-style attention on tcgen05 (sm_100a):  O = softmax(scale * Q K^T) V  per (batch, head).
+// Replaces F.scaled_dot_product_attention behind diffusers' AttnProcessor2_0 (self- and cross-attention of
+// every BasicTransformerBlock).  No mask, no dropout, scale = d^-1/2 (given).
+//
+// One CTA = 128 query rows of one head.  Warp roles: warp 0 TMA producer, warp 1 MMA issuer, warps 2-5
+// softmax + correction + epilogue (one query row per thread: the TMEM lane IS the row, so row max / row sum
+// need no shuffles).
+//   S_j = Q K_j^T          tcgen05.mma 128x128x16, K-major operands, S double-buffered in TMEM (2 x 128 cols)
+//   P_j = exp2(S_j - m)    registers -> bf16 -> shared memory in the K-major SWIZZLE_128B layout the MMA expects
+//   O  += P_j V_j          tcgen05.mma 128 x round16(d) x 16, V consumed MN-major straight from its [keys, d]
+//                          row layout (no transpose anywhere), O accumulates in TMEM and is rescaled in place
+//                          (tcgen05.ld / tcgen05.st) only when a row max moved.
+// Head dims that are not a multiple of 64 (SD1.5: 40, 80, 160) are handled by TMA itself: the box is 64 wide
+// but the tensor-map extent is d, so columns >= d arrive as zeros and never touch HBM.
+#include <algorithm>
+#include <new>
+
+#include "common.cuh"
+#include "internal.h"
+
+namespace b200sd {
+namespace {
+
+constexpr int ATT_THREADS = 192;
+constexpr int BLK = 128;           // query rows per CTA and keys per KV block
+constexpr int TILE16K = BLK * 128; // one [128 rows x 64 bf16] swizzled tile
+
+struct alignas(64) AttnParams {
+  CUtensorMap tmQ, tmK, tmV;  // 4D (d, heads, rows, B), box (64, 1, 128, 1)
+  bf16* out;
+  long long ldo;
+  int B, heads, Nq, Nkv, d;
+  int kv_blocks;
+  int n_pv;        // round16(d): UMMA N of the PV product
+  int ksteps_qk;   // ceil(d/16)
+  float scale_log2;
+};
+
+template <int DPAD>
+struct AttnCfg {
+  static constexpr int DB = DPAD / 64;
+  static constexpr int NST = DPAD == 64 ? 3 : (DPAD == 128 ? 2 : 1);
+  static constexpr int Q_BYTES = DB * TILE16K;
+  static constexpr int KV_BYTES = DB * TILE16K;           // each of K and V per stage
+  static constexpr int P_BYTES = 2 * TILE16K;             // 128 rows x 128 keys bf16
+  static constexpr int SMEM = Q_BYTES + NST * 2 * KV_BYTES + 2 * P_BYTES + 1024 + 256;
+};
+
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+template <int DPAD>
+__global__ void __launch_bounds__(ATT_THREADS, 1) attention_kernel(const __grid_constant__ AttnParams p) {
+  using Cfg = AttnCfg<DPAD>;
+  constexpr int DB = Cfg::DB;
+  constexpr int NST = Cfg::NST;
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sQ = smem;
+  uint8_t* sK = sQ + Cfg::Q_BYTES;                 // [NST][KV_BYTES]
+  uint8_t* sV = sK + NST * Cfg::KV_BYTES;          // [NST][KV_BYTES]
+  uint8_t* sP = sV + NST * Cfg::KV_BYTES;          // [2][P_BYTES]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sP + 2 * Cfg::P_BYTES);
+  uint64_t* q_full = bars;            // 1
+  uint64_t* k_full = bars + 1;        // NST
+  uint64_t* v_full = k_full + NST;    // NST
+  uint64_t* kv_empty = v_full + NST;  // NST
+  uint64_t* s_full = kv_empty + NST;  // 2
+  uint64_t* p_full = s_full + 2;      // 2
+  uint64_t* pv_done = p_full + 2;     // 1
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(pv_done + 1);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int q0 = blockIdx.x * BLK;
+  const int head = blockIdx.y;
+  const int batch = blockIdx.z;
+  const int nkv = p.kv_blocks;
+
+  if (threadIdx.x == 0) {
+    mbar_init(q_full, 1);
+    for (int i = 0; i < NST; ++i) { mbar_init(&k_full[i], 1); mbar_init(&v_full[i], 1); mbar_init(&kv_empty[i], 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&s_full[i], 1); mbar_init(&p_full[i], 128); }
+    mbar_init(pv_done, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) { tmem_alloc(tmem_slot, 512); tmem_relinquish(); }
+  if (warp == 0 && lane == 0) { tma_prefetch_desc(&p.tmQ); tma_prefetch_desc(&p.tmK); tma_prefetch_desc(&p.tmV); }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t tmem_S = tmem_base;        // 2 x 128 columns
+  const uint32_t tmem_O = tmem_base + 256;  // up to 256 columns
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      mbar_arrive_expect_tx(q_full, Cfg::Q_BYTES);
+      for (int db = 0; db < DB; ++db) tma_load_4d(sQ + db * TILE16K, &p.tmQ, q_full, db * 64, head, q0, batch);
+      int st = 0;
+      uint32_t ph = 0;
+      for (int j = 0; j < nkv; ++j) {
+        mbar_wait(&kv_empty[st], ph ^ 1);
+        mbar_arrive_expect_tx(&k_full[st], Cfg::KV_BYTES);
+        for (int db = 0; db < DB; ++db)
+          tma_load_4d(sK + st * Cfg::KV_BYTES + db * TILE16K, &p.tmK, &k_full[st], db * 64, head, j * BLK, batch);
+        mbar_arrive_expect_tx(&v_full[st], Cfg::KV_BYTES);
+        for (int db = 0; db < DB; ++db)
+          tma_load_4d(sV + st * Cfg::KV_BYTES + db * TILE16K, &p.tmV, &v_full[st], db * 64, head, j * BLK, batch);
+        if (++st == NST) { st = 0; ph ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    const uint32_t idesc_s = umma_idesc_bf16(BLK, BLK, 0);
+    const uint32_t idesc_o = umma_idesc_bf16(BLK, p.n_pv, 1);
+    const uint32_t q_addr = smem_u32(sQ);
+    auto issue_S = [&](int j) {  // S_j = Q K_j^T into S buffer j&1
+      const int st = j % NST;
+      mbar_wait(&k_full[st], (j / NST) & 1);
+      tc_fence_after();
+      if (lane == 0) {
+        const uint32_t k_addr = smem_u32(sK + st * Cfg::KV_BYTES);
+        const uint32_t d_tmem = tmem_S + (j & 1) * BLK;
+        for (int ks = 0; ks < p.ksteps_qk; ++ks) {
+          const uint32_t off = (ks >> 2) * TILE16K + (ks & 3) * 32;
+          umma_bf16_ss(d_tmem, umma_smem_desc_sw128(q_addr + off, 16, 1024),
+                       umma_smem_desc_sw128(k_addr + off, 16, 1024), idesc_s, ks != 0 ? 1u : 0u);
+        }
+        umma_commit(&s_full[j & 1]);
+      }
+      __syncwarp();
+    };
+    mbar_wait(q_full, 0);
+    issue_S(0);
+    for (int j = 0; j < nkv; ++j) {
+      if (NST >= 2 && j + 1 < nkv) issue_S(j + 1);
+      const int st = j % NST;
+      mbar_wait(&p_full[j & 1], (j >> 1) & 1);
+      mbar_wait(&v_full[st], (j / NST) & 1);
+      tc_fence_after();
+      if (lane == 0) {
+        const uint32_t p_addr = smem_u32(sP + (j & 1) * Cfg::P_BYTES);
+        const uint32_t v_addr = smem_u32(sV + st * Cfg::KV_BYTES);
+#pragma unroll
+        for (int ks = 0; ks < BLK / 16; ++ks) {
+          const uint64_t da = umma_smem_desc_sw128(p_addr + (ks >> 2) * TILE16K + (ks & 3) * 32, 16, 1024);
+          // V: MN-major; 16 keys = 2 groups of 8 rows (SBO 1024), 64-wide d chunks TILE16K apart (LBO)
+          const uint64_t db = umma_smem_desc_sw128(v_addr + ks * 2048, TILE16K, 1024);
+          umma_bf16_ss(tmem_O, da, db, idesc_o, (j | ks) != 0 ? 1u : 0u);
+        }
+        umma_commit(&kv_empty[st]);
+        umma_commit(pv_done);
+      }
+      __syncwarp();
+      if (NST < 2 && j + 1 < nkv) issue_S(j + 1);
+    }
+  } else {
+    // ===================== softmax / correction / epilogue: thread <-> query row =====================
+    const int q = warp & 3;
+    const int r = q * 32 + lane;
+    const uint32_t lane_base = static_cast<uint32_t>(q * 32) << 16;
+    float m_run = -INFINITY;  // running max in the scaled log2 domain
+    float l_run = 0.f;
+    for (int j = 0; j < nkv; ++j) {
+      mbar_wait(&s_full[j & 1], (j >> 1) & 1);
+      tc_fence_after();
+      const uint32_t s_addr = tmem_S + lane_base + (j & 1) * BLK;
+      const int kv_valid = min(BLK, p.Nkv - j * BLK);  // keys of this block that exist
+      // pass 1: row max
+      float mx = -INFINITY;
+#pragma unroll 1
+      for (int c = 0; c < BLK / 32; ++c) {
+        uint32_t u[32];
+        tmem_ld32(s_addr + c * 32, u);
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          const float s = __uint_as_float(u[i]);
+          if (c * 32 + i < kv_valid) mx = fmaxf(mx, s);
+        }
+      }
+      const float m_new = fmaxf(m_run, mx * p.scale_log2);
+      const float alpha = ex2_approx(m_run - m_new);  // 0 on the first block (m_run = -inf)
+      // pass 2: probabilities -> bf16 -> swizzled smem (K-major, 128-byte rows, 16-byte chunk ^= row % 8)
+      uint8_t* prow = sP + (j & 1) * Cfg::P_BYTES + r * 128;
+      float rsum = 0.f;
+#pragma unroll 1
+      for (int c = 0; c < BLK / 32; ++c) {
+        uint32_t u[32];
+        tmem_ld32(s_addr + c * 32, u);
+        tmem_ld_wait();
+        uint32_t pk[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          float p0 = ex2_approx(fmaf(__uint_as_float(u[2 * i]), p.scale_log2, -m_new));
+          float p1 = ex2_approx(fmaf(__uint_as_float(u[2 * i + 1]), p.scale_log2, -m_new));
+          if (c * 32 + 2 * i >= kv_valid) p0 = 0.f;
+          if (c * 32 + 2 * i + 1 >= kv_valid) p1 = 0.f;
+          rsum += p0 + p1;
+          pk[i] = pack_bf16x2(p0, p1);
+        }
+        uint8_t* pblk = prow + (c >> 1) * TILE16K;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int chunk = ((c & 1) * 4 + i) ^ (r & 7);
+          *reinterpret_cast<uint4*>(pblk + chunk * 16) = make_uint4(pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
+        }
+      }
+      l_run = l_run * alpha + rsum;
+      m_run = m_new;
+      // correction: O *= alpha, only after PV_{j-1} has landed and only if some row of this warp moved
+      if (j > 0) {
+        mbar_wait(pv_done, (j - 1) & 1);
+        tc_fence_after();
+        if (__any_sync(0xffffffffu, alpha != 1.0f)) {
+          const uint32_t o_addr = tmem_O + lane_base;
+#pragma unroll 1
+          for (int c = 0; c < p.n_pv / 16; ++c) {
+            uint32_t u[16];
+            tmem_ld16(o_addr + c * 16, u);
+            tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 16; ++i) u[i] = __float_as_uint(__uint_as_float(u[i]) * alpha);
+            tmem_st16(o_addr + c * 16, u);
+          }
+          tmem_st_wait();
+        }
+      }
+      fence_proxy_async_smem();  // P (generic-proxy stores) -> visible to the MMA's async-proxy reads
+      tc_fence_before();
+      mbar_arrive(&p_full[j & 1]);
+    }
+    // ---- epilogue: O / l -> bf16 -> global ----
+    mbar_wait(pv_done, (nkv - 1) & 1);
+    tc_fence_after();
+    const float inv_l = 1.0f / l_run;
+    const int qrow = q0 + r;
+    bf16* orow = p.out + (static_cast<long long>(batch) * p.Nq + qrow) * p.ldo + head * p.d;
+    const uint32_t o_addr = tmem_O + lane_base;
+#pragma unroll 1
+    for (int c = 0; c < p.n_pv / 16; ++c) {
+      uint32_t u[16];
+      tmem_ld16(o_addr + c * 16, u);
+      tmem_ld_wait();
+      if (qrow < p.Nq) {
+        uint32_t o[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+          o[i] = pack_bf16x2(__uint_as_float(u[2 * i]) * inv_l, __uint_as_float(u[2 * i + 1]) * inv_l);
+        if (c * 16 + 8 <= p.d) *reinterpret_cast<uint4*>(orow + c * 16) = make_uint4(o[0], o[1], o[2], o[3]);
+        if (c * 16 + 16 <= p.d) *reinterpret_cast<uint4*>(orow + c * 16 + 8) = make_uint4(o[4], o[5], o[6], o[7]);
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  if (warp == 1) tmem_dealloc(tmem_base, 512);
+}
+
+struct AttnPlan {
+  AttnParams kp;
+  int dpad;
+  dim3 grid;
+};
+
+template <int DPAD>
+int prepare_attention_t() {  // plan time, outside any stream capture
+  static bool attr_set = false;
+  if (!attr_set) {
+    B200SD_CUDA(cudaFuncSetAttribute(attention_kernel<DPAD>, cudaFuncAttributeMaxDynamicSharedMemorySize, AttnCfg<DPAD>::SMEM));
+    attr_set = true;
+  }
+  return 0;
+}
+int prepare_attention(int dpad) {
+  switch (dpad) {
+    case 64: return prepare_attention_t<64>();
+    case 128: return prepare_attention_t<128>();
+    case 192: return prepare_attention_t<192>();
+  }
+  return fail(B200SD_ERR_UNSUPPORTED, "attention: padded head dim %d unsupported", dpad);
+}
+
+template <int DPAD>
+int launch_attention_t(const AttnPlan& pl, cudaStream_t s) {
+  attention_kernel<DPAD><<<pl.grid, ATT_THREADS, AttnCfg<DPAD>::SMEM, s>>>(pl.kp);
+  B200SD_CUDA(cudaGetLastError());
+  return 0;
+}
+int launch_attention(const void* plan, cudaStream_t s) {
+  const AttnPlan& pl = *static_cast<const AttnPlan*>(plan);
+  switch (pl.dpad) {
+    case 64: return launch_attention_t<64>(pl, s);
+    case 128: return launch_attention_t<128>(pl, s);
+    case 192: return launch_attention_t<192>(pl, s);
+  }
+  return fail(B200SD_ERR_UNSUPPORTED, "attention: padded head dim %d unsupported", pl.dpad);
+}
+
+}  // namespace
+
+int plan_attention(const b200sd_attention& a, PlannedOp* out) {
+  B200SD_CHECK_ARG(a.q && a.k && a.v && a.out, "attention: NULL pointer");
+  B200SD_CHECK_ARG(a.B >= 1 && a.heads >= 1 && a.Nq >= 1 && a.Nkv >= 1, "attention: bad shape");
+  B200SD_CHECK_ARG(a.d >= 8 && a.d % 8 == 0 && a.d <= 192, "attention: head dim %d unsupported (multiple of 8, <= 192)", a.d);
+  B200SD_CHECK_ARG(a.ldq % 8 == 0 && a.ldk % 8 == 0 && a.ldv % 8 == 0 && a.ldo % 8 == 0, "attention: pitches must be multiples of 8");
+  B200SD_CHECK_ARG(a.ldq >= a.heads * a.d && a.ldk >= a.heads * a.d && a.ldv >= a.heads * a.d && a.ldo >= a.heads * a.d,
+                   "attention: pitch smaller than heads*d");
+  for (const void* ptr : {a.q, a.k, a.v, (const void*)a.out})
+    B200SD_CHECK_ARG((reinterpret_cast<uintptr_t>(ptr) & 15) == 0, "attention: pointers must be 16-byte aligned");
+  AttnPlan* pl = new (std::nothrow) AttnPlan();
+  if (!pl) return fail(B200SD_ERR_CUDA, "out of host memory");
+  AttnParams& kp = pl->kp;
+  memset(&kp, 0, sizeof(kp));
+  auto make_map = [&](CUtensorMap* m, const void* base, long long ld, int rows) {
+    uint64_t dims[4] = {(uint64_t)a.d, (uint64_t)a.heads, (uint64_t)rows, (uint64_t)a.B};
+    uint64_t st[3] = {(uint64_t)a.d * 2, (uint64_t)ld * 2, (uint64_t)rows * ld * 2};
+    uint32_t box[4] = {64, 1, BLK, 1};
+    return encode_tensor_map_bf16(m, base, 4, dims, st, box);
+  };
+  int rc = make_map(&kp.tmQ, a.q, a.ldq, a.Nq);
+  if (!rc) rc = make_map(&kp.tmK, a.k, a.ldk, a.Nkv);
+  if (!rc) rc = make_map(&kp.tmV, a.v, a.ldv, a.Nkv);
+  if (rc) { delete pl; return rc; }
+  kp.out = static_cast<bf16*>(a.out);
+  kp.ldo = a.ldo;
+  kp.B = a.B; kp.heads = a.heads; kp.Nq = a.Nq; kp.Nkv = a.Nkv; kp.d = a.d;
+  kp.kv_blocks = (a.Nkv + BLK - 1) / BLK;
+  kp.n_pv = (a.d + 15) / 16 * 16;
+  kp.ksteps_qk = (a.d + 15) / 16;
+  kp.scale_log2 = a.scale * 1.4426950408889634f;
+  pl->dpad = (a.d + 63) / 64 * 64;
+  pl->grid = dim3((a.Nq + BLK - 1) / BLK, a.heads, a.B);
+  rc = prepare_attention(pl->dpad);
+  if (rc) { delete pl; return rc; }
+  out->kind = B200SD_OP_ATTENTION;
+  out->plan = pl;
+  out->launch = launch_attention;
+  out->destroy = destroy_plan<AttnPlan>;
+  out->launches = 1;
+  return 0;
+}
+
+}  // namespace b200sd

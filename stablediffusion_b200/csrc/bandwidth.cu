@@ -1,0 +1,650 @@
+// HBM-bound kernels of the denoising loop (SURVEY §2.3 "bandwidth-bound pieces"): coalesced 16-byte vector
+// accesses, fp32 math, warp-shuffle / shared-memory reductions.  Algorithmic bytes per unit are stated at
+// each kernel; DESIGN.md carries the roofline table.
+#include <algorithm>
+#include <new>
+
+#include "common.cuh"
+#include "internal.h"
+
+namespace b200sd {
+namespace {
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+__device__ __forceinline__ uint4 ldg_stream(const void* p) {
+  uint4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p));
+  return r;
+}
+__device__ __forceinline__ float load_as_float(const void* p, long long i, int dtype) {
+  if (dtype == B200SD_F32) return reinterpret_cast<const float*>(p)[i];
+  if (dtype == B200SD_BF16) return __bfloat162float(reinterpret_cast<const bf16*>(p)[i]);
+  return __half2float(reinterpret_cast<const __half*>(p)[i]);
+}
+__device__ __forceinline__ void store_from_float(void* p, long long i, int dtype, float v) {
+  if (dtype == B200SD_F32) reinterpret_cast<float*>(p)[i] = v;
+  else if (dtype == B200SD_BF16) reinterpret_cast<bf16*>(p)[i] = __float2bfloat16_rn(v);
+  else reinterpret_cast<__half*>(p)[i] = __float2half_rn(v);
+}
+
+// ======================================================================================================
+// GroupNorm (+SiLU), NHWC bf16, one or two channel-concatenated sources.
+// Reference: ResnetBlock2D norm1/norm2 + act, Transformer2DModel.norm, conv_norm_out (diffusers).
+// Pass 1 (stats): 1 read.  Pass 2 (apply): 1 read + 1 write.  Algorithmic bytes = 1R + 1W of the tensor.
+// Thread t owns channel-vector (t % cols) (8 channels = 16 B) and walks pixels with stride R, so a warp
+// always touches consecutive 16-byte chunks of one pixel row.
+// ======================================================================================================
+struct GNParams {
+  const bf16* x1;
+  const bf16* x2;
+  long long ld1, ld2;
+  int C1, C2, C;
+  int NB, HW, groups, cpg, silu;
+  float eps;
+  const float* gamma;
+  const float* beta;
+  bf16* out;
+  float* partials;
+  int chunks, ppc, cols, R;
+};
+
+__device__ __forceinline__ const bf16* gn_src(const GNParams& p, int n, int pix, int c0) {
+  long long row = static_cast<long long>(n) * p.HW + pix;
+  return (c0 < p.C1) ? p.x1 + row * p.ld1 + c0 : p.x2 + row * p.ld2 + (c0 - p.C1);
+}
+
+__global__ void gn_stats_kernel(const GNParams p) {
+  __shared__ float gsum[64][2];
+  const int chunk = blockIdx.x, n = blockIdx.y;
+  const int tid = threadIdx.x;
+  const int vcol = tid % p.cols, r = tid / p.cols;
+  const int c0 = vcol * 8;
+  if (tid < p.groups) { gsum[tid][0] = 0.f; gsum[tid][1] = 0.f; }
+  __syncthreads();
+  float s[8], ss[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) { s[j] = 0.f; ss[j] = 0.f; }
+  const int pix_end = min((chunk + 1) * p.ppc, p.HW);
+  for (int pix = chunk * p.ppc + r; pix < pix_end; pix += p.R) {
+    uint4 v = ldg_stream(gn_src(p, n, pix, c0));
+    uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      float2 f = unpack_bf16x2(w[j]);
+      s[2 * j] += f.x; ss[2 * j] += f.x * f.x;
+      s[2 * j + 1] += f.y; ss[2 * j + 1] += f.y * f.y;
+    }
+  }
+  // fold the 8 channels into their groups (a vector can straddle group boundaries when cpg % 8 != 0)
+  int g_prev = c0 / p.cpg;
+  float as = 0.f, ass = 0.f;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    int g = (c0 + j) / p.cpg;
+    if (g != g_prev) {
+      atomicAdd(&gsum[g_prev][0], as);
+      atomicAdd(&gsum[g_prev][1], ass);
+      as = 0.f; ass = 0.f; g_prev = g;
+    }
+    as += s[j]; ass += ss[j];
+  }
+  atomicAdd(&gsum[g_prev][0], as);
+  atomicAdd(&gsum[g_prev][1], ass);
+  __syncthreads();
+  if (tid < p.groups) {
+    float* dst = p.partials + ((static_cast<long long>(n) * p.chunks + chunk) * p.groups + tid) * 2;
+    dst[0] = gsum[tid][0];
+    dst[1] = gsum[tid][1];
+  }
+}
+
+__global__ void gn_apply_kernel(const GNParams p) {
+  extern __shared__ float sm[];  // a[C], b[C], mean[groups], rstd[groups]
+  float* sa = sm;
+  float* sb = sm + p.C;
+  float* smean = sb + p.C;
+  float* srstd = smean + p.groups;
+  const int chunk = blockIdx.x, n = blockIdx.y;
+  const int tid = threadIdx.x;
+  if (tid < p.groups) {
+    double S = 0.0, SS = 0.0;
+    const float* src = p.partials + (static_cast<long long>(n) * p.chunks * p.groups + tid) * 2;
+    for (int c = 0; c < p.chunks; ++c) {
+      S += src[static_cast<long long>(c) * p.groups * 2];
+      SS += src[static_cast<long long>(c) * p.groups * 2 + 1];
+    }
+    const double cnt = static_cast<double>(p.HW) * p.cpg;
+    const double mean = S / cnt;
+    double var = SS / cnt - mean * mean;
+    if (var < 0.0) var = 0.0;
+    smean[tid] = static_cast<float>(mean);
+    srstd[tid] = static_cast<float>(1.0 / sqrt(var + static_cast<double>(p.eps)));
+  }
+  __syncthreads();
+  for (int c = tid; c < p.C; c += blockDim.x) {
+    const int g = c / p.cpg;
+    const float a = srstd[g] * __ldg(p.gamma + c);
+    sa[c] = a;
+    sb[c] = __ldg(p.beta + c) - smean[g] * a;
+  }
+  __syncthreads();
+  const int vcol = tid % p.cols, r = tid / p.cols;
+  const int c0 = vcol * 8;
+  float a[8], b[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) { a[j] = sa[c0 + j]; b[j] = sb[c0 + j]; }
+  const int pix_end = min((chunk + 1) * p.ppc, p.HW);
+  for (int pix = chunk * p.ppc + r; pix < pix_end; pix += p.R) {
+    uint4 v = ldg_stream(gn_src(p, n, pix, c0));
+    uint32_t w[4] = {v.x, v.y, v.z, v.w};
+    uint32_t o[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      float2 f = unpack_bf16x2(w[j]);
+      float y0 = fmaf(f.x, a[2 * j], b[2 * j]);
+      float y1 = fmaf(f.y, a[2 * j + 1], b[2 * j + 1]);
+      if (p.silu) { y0 = silu_f(y0); y1 = silu_f(y1); }
+      o[j] = pack_bf16x2(y0, y1);
+    }
+    bf16* dst = p.out + (static_cast<long long>(n) * p.HW + pix) * p.C + c0;
+    *reinterpret_cast<uint4*>(dst) = make_uint4(o[0], o[1], o[2], o[3]);
+  }
+}
+
+struct GNPlan { GNParams p; int threads; size_t smem; };
+int launch_groupnorm(const void* plan, cudaStream_t s) {
+  const GNPlan& pl = *static_cast<const GNPlan*>(plan);
+  dim3 grid(pl.p.chunks, pl.p.NB);
+  gn_stats_kernel<<<grid, pl.threads, 0, s>>>(pl.p);
+  B200SD_CUDA(cudaGetLastError());
+  gn_apply_kernel<<<grid, pl.threads, pl.smem, s>>>(pl.p);
+  B200SD_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// ======================================================================================================
+// LayerNorm: warp per row, the row lives in registers (C <= 2048), two-pass mean/variance like torch.
+// Reference: BasicTransformerBlock.norm1/2/3 (eps 1e-5, affine).  Algorithmic bytes = 1R + 1W.
+// ======================================================================================================
+struct LNParams {
+  const bf16* x; bf16* out; long long ldx, ldo; int rows, C; float eps; const float* gamma; const float* beta;
+};
+constexpr int LN_MAXV = 8;  // 8 vectors * 32 lanes * 8 elements = 2048 channels
+__global__ void __launch_bounds__(256) layernorm_kernel(const LNParams p) {
+  const int row = blockIdx.x * 8 + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (row >= p.rows) return;
+  const int nvec = p.C >> 3;
+  const bf16* xr = p.x + static_cast<long long>(row) * p.ldx;
+  float v[LN_MAXV][8];
+  float sum = 0.f;
+#pragma unroll
+  for (int i = 0; i < LN_MAXV; ++i) {
+    const int vi = lane + 32 * i;
+    if (vi < nvec) {
+      uint4 u = ldg_stream(xr + vi * 8);
+      uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        float2 f = unpack_bf16x2(w[j]);
+        v[i][2 * j] = f.x; v[i][2 * j + 1] = f.y;
+        sum += f.x + f.y;
+      }
+    }
+  }
+  const float mean = warp_sum(sum) / static_cast<float>(p.C);
+  float sq = 0.f;
+#pragma unroll
+  for (int i = 0; i < LN_MAXV; ++i) {
+    if (lane + 32 * i < nvec) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) { float d = v[i][j] - mean; sq += d * d; }
+    }
+  }
+  const float rstd = rsqrtf(warp_sum(sq) / static_cast<float>(p.C) + p.eps);
+  bf16* orow = p.out + static_cast<long long>(row) * p.ldo;
+#pragma unroll
+  for (int i = 0; i < LN_MAXV; ++i) {
+    const int vi = lane + 32 * i;
+    if (vi < nvec) {
+      const float4* g4 = reinterpret_cast<const float4*>(p.gamma + vi * 8);
+      const float4* b4 = reinterpret_cast<const float4*>(p.beta + vi * 8);
+      float4 g0 = __ldg(g4), g1 = __ldg(g4 + 1), b0 = __ldg(b4), b1 = __ldg(b4 + 1);
+      float g[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+      float b[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+      uint32_t o[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        o[j] = pack_bf16x2((v[i][2 * j] - mean) * rstd * g[2 * j] + b[2 * j],
+                           (v[i][2 * j + 1] - mean) * rstd * g[2 * j + 1] + b[2 * j + 1]);
+      *reinterpret_cast<uint4*>(orow + vi * 8) = make_uint4(o[0], o[1], o[2], o[3]);
+    }
+  }
+}
+int launch_layernorm(const void* plan, cudaStream_t s) {
+  const LNParams& p = *static_cast<const LNParams*>(plan);
+  layernorm_kernel<<<(p.rows + 7) / 8, 256, 0, s>>>(p);
+  B200SD_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// ======================================================================================================
+// Sinusoidal timestep embedding (diffusers Timesteps / get_timestep_embedding)
+// ======================================================================================================
+struct TEParams {
+  const float* t; const float* table; const int* counter; int t_stride, rows, dim, flip; float shift, max_period; bf16* out;
+};
+__global__ void timestep_embed_kernel(const TEParams p) {
+  const int half = p.dim / 2;
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= p.rows * half) return;
+  const int row = idx / half, k = idx - row * half;
+  float t;
+  if (p.t) t = p.t[row * p.t_stride];
+  else t = p.table[static_cast<long long>(*p.counter) * B200SD_STEP_ROW + B200SD_ST_TIMESTEP];
+  float exponent = -logf(p.max_period) * static_cast<float>(k);
+  exponent = exponent / (static_cast<float>(half) - p.shift);
+  const float arg = t * expf(exponent);
+  const float sn = sinf(arg), cs = cosf(arg);
+  bf16* o = p.out + static_cast<long long>(row) * p.dim;
+  if (p.flip) { o[k] = __float2bfloat16_rn(cs); o[half + k] = __float2bfloat16_rn(sn); }
+  else        { o[k] = __float2bfloat16_rn(sn); o[half + k] = __float2bfloat16_rn(cs); }
+}
+int launch_timestep_embed(const void* plan, cudaStream_t s) {
+  const TEParams& p = *static_cast<const TEParams*>(plan);
+  const int n = p.rows * (p.dim / 2);
+  timestep_embed_kernel<<<(n + 127) / 128, 128, 0, s>>>(p);
+  B200SD_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// ======================================================================================================
+// PREP_LATENTS: CFG duplicate (pipeline :467-469) + scale_model_input (:472) + NCHW -> NHWC(Cpad) bf16
+// ======================================================================================================
+struct PLParams {
+  const void* lat; bf16* out; const float* table; const int* counter; float fixed_scale; int in_dtype, B, C, hw, Cpad, rep;
+};
+__global__ void prep_latents_kernel(const PLParams p) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= p.B * p.hw) return;
+  const int b = idx / p.hw, pix = idx - b * p.hw;
+  float scale = p.fixed_scale;
+  if (p.counter) scale = p.table[static_cast<long long>(*p.counter) * B200SD_STEP_ROW + B200SD_ST_IN_SCALE];
+  for (int r = 0; r < p.rep; ++r) {
+    bf16* o = p.out + (static_cast<long long>(r * p.B + b) * p.hw + pix) * p.Cpad;
+    for (int c = 0; c < p.Cpad; ++c) {
+      float v = 0.f;
+      if (c < p.C) v = load_as_float(p.lat, (static_cast<long long>(b) * p.C + c) * p.hw + pix, p.in_dtype) * scale;
+      o[c] = __float2bfloat16_rn(v);
+    }
+  }
+}
+int launch_prep_latents(const void* plan, cudaStream_t s) {
+  const PLParams& p = *static_cast<const PLParams*>(plan);
+  const int n = p.B * p.hw;
+  prep_latents_kernel<<<(n + 127) / 128, 128, 0, s>>>(p);
+  B200SD_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// ======================================================================================================
+// nearest-2x upsample and stride-2 phase split (NHWC, 16-byte vectors)
+// ======================================================================================================
+struct USParams { const bf16* x; bf16* out; int NB, H, W, C; };
+__global__ void upsample2x_kernel(const USParams p) {
+  const int cv = p.C >> 3;
+  const long long total = static_cast<long long>(p.NB) * p.H * p.W * cv;
+  for (long long idx = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; idx < total;
+       idx += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int v = static_cast<int>(idx % cv);
+    long long pix = idx / cv;
+    const int w = static_cast<int>(pix % p.W);
+    pix /= p.W;
+    const int h = static_cast<int>(pix % p.H);
+    const int n = static_cast<int>(pix / p.H);
+    const uint4 val = ldg_stream(p.x + idx * 8);
+    const long long ob = ((static_cast<long long>(n) * 2 * p.H + 2 * h) * 2 * p.W + 2 * w) * p.C + v * 8;
+    const long long rowp = static_cast<long long>(2 * p.W) * p.C;
+    *reinterpret_cast<uint4*>(p.out + ob) = val;
+    *reinterpret_cast<uint4*>(p.out + ob + p.C) = val;
+    *reinterpret_cast<uint4*>(p.out + ob + rowp) = val;
+    *reinterpret_cast<uint4*>(p.out + ob + rowp + p.C) = val;
+  }
+}
+__global__ void phase_split_kernel(const USParams p) {
+  const int cv = p.C >> 3;
+  const int H2 = p.H >> 1, W2 = p.W >> 1;
+  const long long total = static_cast<long long>(p.NB) * p.H * p.W * cv;
+  for (long long idx = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; idx < total;
+       idx += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int v = static_cast<int>(idx % cv);
+    long long pix = idx / cv;
+    const int w = static_cast<int>(pix % p.W);
+    pix /= p.W;
+    const int h = static_cast<int>(pix % p.H);
+    const int n = static_cast<int>(pix / p.H);
+    const int ph = (h & 1) * 2 + (w & 1);
+    const long long o = (((static_cast<long long>(ph) * p.NB + n) * H2 + (h >> 1)) * W2 + (w >> 1)) * p.C + v * 8;
+    *reinterpret_cast<uint4*>(p.out + o) = ldg_stream(p.x + idx * 8);
+  }
+}
+int launch_upsample2x(const void* plan, cudaStream_t s) {
+  const USParams& p = *static_cast<const USParams*>(plan);
+  const long long total = static_cast<long long>(p.NB) * p.H * p.W * (p.C >> 3);
+  const int blocks = static_cast<int>(std::min<long long>((total + 255) / 256, 148 * 16));
+  upsample2x_kernel<<<blocks, 256, 0, s>>>(p);
+  B200SD_CUDA(cudaGetLastError());
+  return 0;
+}
+int launch_phase_split(const void* plan, cudaStream_t s) {
+  const USParams& p = *static_cast<const USParams*>(plan);
+  const long long total = static_cast<long long>(p.NB) * p.H * p.W * (p.C >> 3);
+  const int blocks = static_cast<int>(std::min<long long>((total + 255) / 256, 148 * 16));
+  phase_split_kernel<<<blocks, 256, 0, s>>>(p);
+  B200SD_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// ======================================================================================================
+// Row softmax (VAE mid-block attention, single head d=512: scores are materialised)
+// ======================================================================================================
+struct SMParams { const bf16* x; bf16* out; long long ldx, ldo; int rows, cols; float scale; };
+__global__ void __launch_bounds__(256) softmax_rows_kernel(const SMParams p) {
+  __shared__ float red[8];
+  __shared__ float bcast;
+  const int row = blockIdx.x;
+  const bf16* xr = p.x + static_cast<long long>(row) * p.ldx;
+  bf16* orow = p.out + static_cast<long long>(row) * p.ldo;
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  const int nvec = p.cols >> 3;
+  float mx = -INFINITY;
+  for (int v = tid; v < nvec; v += 256) {
+    uint4 u = *reinterpret_cast<const uint4*>(xr + v * 8);
+    uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) { float2 f = unpack_bf16x2(w[j]); mx = fmaxf(mx, fmaxf(f.x, f.y)); }
+  }
+  mx = warp_max(mx);
+  if (lane == 0) red[wid] = mx;
+  __syncthreads();
+  if (tid == 0) { float m = red[0]; for (int i = 1; i < 8; ++i) m = fmaxf(m, red[i]); bcast = m; }
+  __syncthreads();
+  mx = bcast;
+  __syncthreads();
+  const float sc = p.scale * 1.4426950408889634f;
+  float sum = 0.f;
+  for (int v = tid; v < nvec; v += 256) {
+    uint4 u = *reinterpret_cast<const uint4*>(xr + v * 8);
+    uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) { float2 f = unpack_bf16x2(w[j]); sum += exp2f((f.x - mx) * sc) + exp2f((f.y - mx) * sc); }
+  }
+  sum = warp_sum(sum);
+  if (lane == 0) red[wid] = sum;
+  __syncthreads();
+  if (tid == 0) { float t = 0.f; for (int i = 0; i < 8; ++i) t += red[i]; bcast = 1.0f / t; }
+  __syncthreads();
+  const float inv = bcast;
+  for (int v = tid; v < nvec; v += 256) {
+    uint4 u = *reinterpret_cast<const uint4*>(xr + v * 8);
+    uint32_t w[4] = {u.x, u.y, u.z, u.w};
+    uint32_t o[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      float2 f = unpack_bf16x2(w[j]);
+      o[j] = pack_bf16x2(exp2f((f.x - mx) * sc) * inv, exp2f((f.y - mx) * sc) * inv);
+    }
+    *reinterpret_cast<uint4*>(orow + v * 8) = make_uint4(o[0], o[1], o[2], o[3]);
+  }
+}
+int launch_softmax_rows(const void* plan, cudaStream_t s) {
+  const SMParams& p = *static_cast<const SMParams*>(plan);
+  softmax_rows_kernel<<<p.rows, 256, 0, s>>>(p);
+  B200SD_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// ======================================================================================================
+// CFG combine + scheduler update, fused (pipeline :484-489; scheduler math SURVEY App. B):
+//   eps = u + s*(c - u);  x0 = (x - K1*eps)*K2;  x' = CX*x + CE*eps + C0*x0 + C1*(x0 - x0_prev)
+// and optionally the NEXT step's scaled, CFG-duplicated NHWC UNet input.  Thread per (image, pixel).
+// Algorithmic bytes (cfg, C=4): 2 eps rows (8 B each) + x read/write in its dtype.
+// ======================================================================================================
+struct CSParams {
+  const bf16* eps; long long ld_eps; const void* x; void* x_out; float* x0_prev; bf16* next_in;
+  const float* table; const int* counter; float gs; int cfg, x_dtype, B, C, hw, Cpad, rep, nsteps;
+};
+__global__ void cfg_step_kernel(const CSParams p) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= p.B * p.hw) return;
+  const int b = idx / p.hw, pix = idx - b * p.hw;
+  const int step = *p.counter;
+  const float* row = p.table + static_cast<long long>(step) * B200SD_STEP_ROW;
+  const float K1 = row[B200SD_ST_K1], K2 = row[B200SD_ST_K2], CX = row[B200SD_ST_CX], CE = row[B200SD_ST_CE],
+              C0 = row[B200SD_ST_C0], C1 = row[B200SD_ST_C1];
+  float next_scale = 1.0f;
+  if (p.next_in && step + 1 < p.nsteps) next_scale = p.table[static_cast<long long>(step + 1) * B200SD_STEP_ROW + B200SD_ST_IN_SCALE];
+  const bf16* eu = p.eps + (static_cast<long long>(b) * p.hw + pix) * p.ld_eps;
+  const bf16* ec = p.eps + (static_cast<long long>(p.B + b) * p.hw + pix) * p.ld_eps;
+  for (int c = 0; c < p.C; ++c) {
+    const float u = __bfloat162float(eu[c]);
+    float e = u;
+    if (p.cfg) e = p.gs * (__bfloat162float(ec[c]) - u) + u;
+    const long long xi = (static_cast<long long>(b) * p.C + c) * p.hw + pix;
+    const float x = load_as_float(p.x, xi, p.x_dtype);
+    const float x0 = (x - K1 * e) * K2;
+    float xn = CX * x + CE * e + C0 * x0;
+    if (p.x0_prev) {
+      if (C1 != 0.f) xn += C1 * (x0 - p.x0_prev[xi]);
+      p.x0_prev[xi] = x0;
+    }
+    store_from_float(p.x_out, xi, p.x_dtype, xn);
+    if (p.next_in) {
+      // the UNet consumes the value the pipeline would hand it: latents in their storage dtype, scaled
+      const float xs = load_as_float(p.x_out, xi, p.x_dtype) * next_scale;
+      for (int r = 0; r < p.rep; ++r)
+        p.next_in[(static_cast<long long>(r * p.B + b) * p.hw + pix) * p.Cpad + c] = __float2bfloat16_rn(xs);
+    }
+  }
+  if (p.next_in) {
+    for (int r = 0; r < p.rep; ++r)
+      for (int c = p.C; c < p.Cpad; ++c)
+        p.next_in[(static_cast<long long>(r * p.B + b) * p.hw + pix) * p.Cpad + c] = __float2bfloat16_rn(0.f);
+  }
+}
+int launch_cfg_step(const void* plan, cudaStream_t s) {
+  const CSParams& p = *static_cast<const CSParams*>(plan);
+  const int n = p.B * p.hw;
+  cfg_step_kernel<<<(n + 127) / 128, 128, 0, s>>>(p);
+  B200SD_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// ======================================================================================================
+// small utilities
+// ======================================================================================================
+struct AXParams { const void* x; const void* y; void* out; float a, b; int xd, yd, od; long long n; };
+__global__ void axpby_kernel(const AXParams p) {
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < p.n;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    float v = p.a * load_as_float(p.x, i, p.xd);
+    if (p.y) v += p.b * load_as_float(p.y, i, p.yd);
+    store_from_float(p.out, i, p.od, v);
+  }
+}
+int launch_axpby(const void* plan, cudaStream_t s) {
+  const AXParams& p = *static_cast<const AXParams*>(plan);
+  const int blocks = static_cast<int>(std::min<long long>((p.n + 255) / 256, 148 * 8));
+  axpby_kernel<<<blocks, 256, 0, s>>>(p);
+  B200SD_CUDA(cudaGetLastError());
+  return 0;
+}
+
+struct IOParams { const bf16* x; void* out; long long ldx; int B, C, HW, od; };
+__global__ void image_out_kernel(const IOParams p) {
+  const long long total = static_cast<long long>(p.B) * p.HW;
+  for (long long idx = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; idx < total;
+       idx += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int b = static_cast<int>(idx / p.HW);
+    const int pix = static_cast<int>(idx - static_cast<long long>(b) * p.HW);
+    const bf16* src = p.x + idx * p.ldx;
+    for (int c = 0; c < p.C; ++c)
+      store_from_float(p.out, (static_cast<long long>(b) * p.C + c) * p.HW + pix, p.od, __bfloat162float(src[c]));
+  }
+}
+int launch_image_out(const void* plan, cudaStream_t s) {
+  const IOParams& p = *static_cast<const IOParams*>(plan);
+  const long long total = static_cast<long long>(p.B) * p.HW;
+  const int blocks = static_cast<int>(std::min<long long>((total + 255) / 256, 148 * 8));
+  image_out_kernel<<<blocks, 256, 0, s>>>(p);
+  B200SD_CUDA(cudaGetLastError());
+  return 0;
+}
+
+__global__ void step_advance_kernel(int* counter) { *counter += 1; }
+struct SAParams { int* counter; };
+int launch_step_advance(const void* plan, cudaStream_t s) {
+  step_advance_kernel<<<1, 1, 0, s>>>(static_cast<const SAParams*>(plan)->counter);
+  B200SD_CUDA(cudaGetLastError());
+  return 0;
+}
+
+template <class P>
+int finish_plan(PlannedOp* out, int kind, const P& p, int (*launch)(const void*, cudaStream_t), int launches = 1) {
+  P* h = new (std::nothrow) P(p);
+  if (!h) return fail(B200SD_ERR_CUDA, "out of host memory");
+  out->kind = kind;
+  out->plan = h;
+  out->launch = launch;
+  out->destroy = destroy_plan<P>;
+  out->launches = launches;
+  return 0;
+}
+bool dtype_ok(int d) { return d == B200SD_BF16 || d == B200SD_F32 || d == B200SD_F16; }
+bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+}  // namespace
+
+int groupnorm_chunks(int NB, int HW, int C) {
+  (void)C;
+  if (NB < 1 || HW < 1) return 1;
+  int target = (2 * 148 + NB - 1) / NB;
+  int max_chunks = std::max(1, HW / 16);
+  return std::max(1, std::min(target, max_chunks));
+}
+
+int plan_groupnorm(const b200sd_groupnorm& g, PlannedOp* out) {
+  GNPlan pl;
+  GNParams& p = pl.p;
+  B200SD_CHECK_ARG(g.x1 && g.out && g.gamma && g.beta && g.partials, "groupnorm: NULL pointer");
+  B200SD_CHECK_ARG(g.C1 > 0 && g.C1 % 8 == 0 && g.C2 >= 0 && g.C2 % 8 == 0, "groupnorm: C1=%d C2=%d must be multiples of 8", g.C1, g.C2);
+  B200SD_CHECK_ARG(g.C2 == 0 || g.x2, "groupnorm: C2>0 needs x2");
+  const int C = g.C1 + g.C2;
+  B200SD_CHECK_ARG(g.groups >= 1 && g.groups <= 64 && C % g.groups == 0, "groupnorm: groups=%d does not divide C=%d", g.groups, C);
+  B200SD_CHECK_ARG(g.NB >= 1 && g.HW >= 1, "groupnorm: NB=%d HW=%d", g.NB, g.HW);
+  B200SD_CHECK_ARG(g.ld1 % 8 == 0 && g.ld1 >= g.C1 && (g.C2 == 0 || (g.ld2 % 8 == 0 && g.ld2 >= g.C2)), "groupnorm: bad pitches");
+  B200SD_CHECK_ARG(aligned16(g.x1) && aligned16(g.out) && (g.C2 == 0 || aligned16(g.x2)), "groupnorm: pointers must be 16-byte aligned");
+  B200SD_CHECK_ARG(C / 8 <= 1024, "groupnorm: C=%d too large", C);
+  p.x1 = static_cast<const bf16*>(g.x1); p.x2 = static_cast<const bf16*>(g.x2);
+  p.ld1 = g.ld1; p.ld2 = g.ld2; p.C1 = g.C1; p.C2 = g.C2; p.C = C;
+  p.NB = g.NB; p.HW = g.HW; p.groups = g.groups; p.cpg = C / g.groups; p.silu = g.silu; p.eps = g.eps;
+  p.gamma = g.gamma; p.beta = g.beta; p.out = static_cast<bf16*>(g.out); p.partials = g.partials;
+  p.chunks = groupnorm_chunks(g.NB, g.HW, C);
+  p.ppc = (g.HW + p.chunks - 1) / p.chunks;
+  p.chunks = (g.HW + p.ppc - 1) / p.ppc;
+  p.cols = C / 8;
+  p.R = std::max(1, 256 / p.cols);
+  pl.threads = p.cols * p.R;
+  if (pl.threads < g.groups) { p.R = (g.groups + p.cols - 1) / p.cols; pl.threads = p.cols * p.R; }
+  pl.smem = (2 * static_cast<size_t>(C) + 2 * g.groups) * sizeof(float);
+  const long long need = static_cast<long long>(g.NB) * groupnorm_chunks(g.NB, g.HW, C) * g.groups * 2 * 4;
+  B200SD_CHECK_ARG(g.partials_bytes >= need, "groupnorm: partials workspace %lld < %lld bytes", (long long)g.partials_bytes, need);
+  return finish_plan(out, B200SD_OP_GROUPNORM, pl, launch_groupnorm, 2);
+}
+
+int plan_layernorm(const b200sd_layernorm& g, PlannedOp* out) {
+  B200SD_CHECK_ARG(g.x && g.out && g.gamma && g.beta, "layernorm: NULL pointer");
+  B200SD_CHECK_ARG(g.C >= 8 && g.C % 8 == 0 && g.C <= LN_MAXV * 256, "layernorm: C=%d unsupported (multiple of 8, <= %d)", g.C, LN_MAXV * 256);
+  B200SD_CHECK_ARG(g.rows >= 1 && g.ldx % 8 == 0 && g.ldo % 8 == 0 && g.ldx >= g.C && g.ldo >= g.C, "layernorm: bad shape");
+  B200SD_CHECK_ARG(aligned16(g.x) && aligned16(g.out) && aligned16(g.gamma) && aligned16(g.beta), "layernorm: pointers must be 16-byte aligned");
+  LNParams p{static_cast<const bf16*>(g.x), static_cast<bf16*>(g.out), g.ldx, g.ldo, g.rows, g.C, g.eps, g.gamma, g.beta};
+  return finish_plan(out, B200SD_OP_LAYERNORM, p, launch_layernorm);
+}
+
+int plan_timestep_embed(const b200sd_timestep_embed& g, PlannedOp* out) {
+  B200SD_CHECK_ARG(g.out && g.rows >= 1 && g.dim >= 2 && g.dim % 2 == 0, "timestep_embed: bad arguments");
+  B200SD_CHECK_ARG(g.t || (g.step_table && g.step_counter), "timestep_embed: need t or a step table");
+  TEParams p{g.t, g.step_table, g.step_counter, g.t_stride, g.rows, g.dim, g.flip_sin_to_cos, g.freq_shift,
+             g.max_period > 0.f ? g.max_period : 10000.f, static_cast<bf16*>(g.out)};
+  return finish_plan(out, B200SD_OP_TIMESTEP_EMBED, p, launch_timestep_embed);
+}
+
+int plan_prep_latents(const b200sd_prep_latents& g, PlannedOp* out) {
+  B200SD_CHECK_ARG(g.latents && g.out && dtype_ok(g.in_dtype), "prep_latents: bad pointers/dtype");
+  B200SD_CHECK_ARG(g.B >= 1 && g.C >= 1 && g.hw >= 1 && g.Cpad >= g.C && g.rep >= 1, "prep_latents: bad shape");
+  B200SD_CHECK_ARG(!g.step_counter || g.step_table, "prep_latents: step_counter without table");
+  PLParams p{g.latents, static_cast<bf16*>(g.out), g.step_table, g.step_counter, g.fixed_scale, g.in_dtype, g.B, g.C, g.hw, g.Cpad, g.rep};
+  return finish_plan(out, B200SD_OP_PREP_LATENTS, p, launch_prep_latents);
+}
+
+int plan_upsample2x(const b200sd_upsample2x& g, PlannedOp* out) {
+  B200SD_CHECK_ARG(g.x && g.out && aligned16(g.x) && aligned16(g.out), "upsample2x: bad pointers");
+  B200SD_CHECK_ARG(g.NB >= 1 && g.H >= 1 && g.W >= 1 && g.C >= 8 && g.C % 8 == 0, "upsample2x: bad shape");
+  USParams p{static_cast<const bf16*>(g.x), static_cast<bf16*>(g.out), g.NB, g.H, g.W, g.C};
+  return finish_plan(out, B200SD_OP_UPSAMPLE2X, p, launch_upsample2x);
+}
+
+int plan_phase_split(const b200sd_phase_split& g, PlannedOp* out) {
+  B200SD_CHECK_ARG(g.x && g.out && aligned16(g.x) && aligned16(g.out), "phase_split: bad pointers");
+  B200SD_CHECK_ARG(g.NB >= 1 && g.H >= 2 && g.W >= 2 && g.H % 2 == 0 && g.W % 2 == 0 && g.C >= 8 && g.C % 8 == 0,
+                   "phase_split: H=%d W=%d must be even, C=%d a multiple of 8", g.H, g.W, g.C);
+  USParams p{static_cast<const bf16*>(g.x), static_cast<bf16*>(g.out), g.NB, g.H, g.W, g.C};
+  return finish_plan(out, B200SD_OP_PHASE_SPLIT, p, launch_phase_split);
+}
+
+int plan_softmax_rows(const b200sd_softmax_rows& g, PlannedOp* out) {
+  B200SD_CHECK_ARG(g.x && g.out && aligned16(g.x) && aligned16(g.out), "softmax_rows: bad pointers");
+  B200SD_CHECK_ARG(g.rows >= 1 && g.cols >= 8 && g.cols % 8 == 0 && g.ldx % 8 == 0 && g.ldo % 8 == 0, "softmax_rows: bad shape");
+  SMParams p{static_cast<const bf16*>(g.x), static_cast<bf16*>(g.out), g.ldx, g.ldo, g.rows, g.cols, g.scale};
+  return finish_plan(out, B200SD_OP_SOFTMAX_ROWS, p, launch_softmax_rows);
+}
+
+int plan_cfg_step(const b200sd_cfg_step& g, PlannedOp* out) {
+  B200SD_CHECK_ARG(g.eps && g.x && g.x_out && g.step_table && g.step_counter && dtype_ok(g.x_dtype), "cfg_step: bad pointers/dtype");
+  B200SD_CHECK_ARG(g.B >= 1 && g.C >= 1 && g.hw >= 1 && g.ld_eps >= g.C && g.nsteps >= 1, "cfg_step: bad shape");
+  B200SD_CHECK_ARG(!g.next_in || (g.Cpad >= g.C && g.rep >= 1), "cfg_step: next_in needs Cpad/rep");
+  CSParams p{static_cast<const bf16*>(g.eps), g.ld_eps, g.x, g.x_out, g.x0_prev, static_cast<bf16*>(g.next_in),
+             g.step_table, g.step_counter, g.guidance_scale, g.cfg, g.x_dtype, g.B, g.C, g.hw, g.Cpad, g.rep, g.nsteps};
+  return finish_plan(out, B200SD_OP_CFG_STEP, p, launch_cfg_step);
+}
+
+int plan_axpby(const b200sd_axpby& g, PlannedOp* out) {
+  B200SD_CHECK_ARG(g.x && g.out && g.n >= 1 && dtype_ok(g.x_dtype) && dtype_ok(g.out_dtype) && (!g.y || dtype_ok(g.y_dtype)), "axpby: bad arguments");
+  AXParams p{g.x, g.y, g.out, g.a, g.b, g.x_dtype, g.y_dtype, g.out_dtype, g.n};
+  return finish_plan(out, B200SD_OP_AXPBY, p, launch_axpby);
+}
+
+int plan_image_out(const b200sd_image_out& g, PlannedOp* out) {
+  B200SD_CHECK_ARG(g.x && g.out && g.B >= 1 && g.C >= 1 && g.HW >= 1 && g.ldx >= g.C && dtype_ok(g.out_dtype), "image_out: bad arguments");
+  IOParams p{static_cast<const bf16*>(g.x), g.out, g.ldx, g.B, g.C, g.HW, g.out_dtype};
+  return finish_plan(out, B200SD_OP_IMAGE_OUT, p, launch_image_out);
+}
+
+int plan_step_advance(const b200sd_step_advance& g, PlannedOp* out) {
+  B200SD_CHECK_ARG(g.step_counter, "step_advance: NULL counter");
+  SAParams p{g.step_counter};
+  return finish_plan(out, B200SD_OP_STEP_ADVANCE, p, launch_step_advance);
+}
+
+}  // namespace b200sd

@@ -1,0 +1,706 @@
+// tcgen05 implicit-GEMM for sm_100a:  C[M,N] = A[M,K] * W[N,K]^T  (+ fused epilogue)
+//
+// One kernel serves every dense contraction of the UNet / VAE (reference call sites: the conv2d / linear
+// library calls behind pipelines/sd_unified_pipeline.py:475-482 and :523 — SURVEY §2.3):
+//   * linear / 1x1 conv : A rows are tokens, 2D TMA boxes [128 rows x 64 K]
+//   * 3x3 conv (stride 1, stride 2 after PHASE_SPLIT, any tap table): A rows are a [bn x bh x bw] patch of
+//     output pixels; for every tap the producer issues ONE 5D TMA box shifted by (dh,dw) — the halo is
+//     zero-filled by TMA's out-of-bounds handling, so no im2col buffer ever exists.
+//   * K may be the concatenation of up to 3 segments (e.g. conv2's 9*C taps followed by the 1x1 shortcut's
+//     C_in columns), each with its own activation and weight tensor map.
+// Structure: persistent CTAs (one per SM), warp-specialised — warp 0 TMA producer, warp 1 MMA issuer
+// (single thread, tcgen05.mma.cta_group::1 128xBNx16, fp32 accumulators in TMEM, double-buffered so the
+// epilogue of tile i overlaps the main loop of tile i+1), warps 2-5 epilogue (tcgen05.ld -> registers ->
+// fused bias / time-embedding row vector / residual / SiLU / GEGLU -> bf16 stores).
+// Split-K (for the M=128..512 low-resolution levels) writes fp32 partial tiles that a second small kernel
+// reduces with the same epilogue.
+#include <algorithm>
+#include <cmath>
+#include <new>
+
+#include "common.cuh"
+#include "internal.h"
+
+namespace b200sd {
+
+namespace {
+
+constexpr int BM = 128;
+constexpr int BK = 64;
+constexpr int A_STAGE_BYTES = BM * BK * 2;  // 16 KiB
+constexpr int GEMM_THREADS = 192;
+
+__host__ __device__ constexpr int gemm_stages(int bn) {
+  return bn <= 64 ? 8 : (bn <= 160 ? 6 : 4);
+}
+__host__ __device__ constexpr int tmem_cols_for(int bn) {
+  return 2 * bn <= 32 ? 32 : (2 * bn <= 64 ? 64 : (2 * bn <= 128 ? 128 : (2 * bn <= 256 ? 256 : 512)));
+}
+__host__ __device__ constexpr int gemm_smem_bytes(int bn) {
+  return gemm_stages(bn) * (A_STAGE_BYTES + bn * 128) + 1024 /*align slack*/ + 256 /*barriers*/;
+}
+
+struct alignas(64) GemmKParams {
+  CUtensorMap tmA[B200SD_MAX_SEG];
+  CUtensorMap tmB[B200SD_MAX_SEG];
+  int nseg;
+  int seg_cb[B200SD_MAX_SEG];        // 64-wide channel blocks per tap
+  int seg_taps[B200SD_MAX_SEG];
+  int seg_kb_start[B200SD_MAX_SEG + 1];
+  int8_t tap_phase[B200SD_MAX_SEG][12];
+  int8_t tap_dh[B200SD_MAX_SEG][12];
+  int8_t tap_dw[B200SD_MAX_SEG][12];
+  int kb_total, kb_per_split, splits;
+  int spatial;
+  int M, N;
+  int NB, H, W;
+  int bw_log2, bh_log2, bn_log2;
+  int tiles_w, tiles_h, tiles_nb;
+  int num_m_tiles, num_n_tiles;
+  // epilogue
+  void* out;
+  long long ldc;
+  int OH, OW, sy, sx, oy, ox;
+  const float* bias;
+  const float* rowvec;
+  long long ld_rowvec;
+  int rows_per_group;
+  const bf16* residual;
+  long long ldr;
+  float alpha;
+  int flags;
+  float* partial;
+};
+
+struct TileCoord {
+  int mt, nt, ks;
+  int m0;          // linear
+  int w0, h0, n0;  // spatial
+};
+
+__device__ __forceinline__ TileCoord decode_work(const GemmKParams& p, int work) {
+  TileCoord t;
+  t.mt = work % p.num_m_tiles;
+  int rest = work / p.num_m_tiles;
+  t.nt = rest % p.num_n_tiles;
+  t.ks = rest / p.num_n_tiles;
+  t.m0 = t.mt * BM;
+  if (p.spatial) {
+    int tw = t.mt % p.tiles_w;
+    int r2 = t.mt / p.tiles_w;
+    int th = r2 % p.tiles_h;
+    int tn = r2 / p.tiles_h;
+    t.w0 = tw << p.bw_log2;
+    t.h0 = th << p.bh_log2;
+    t.n0 = tn << p.bn_log2;
+  } else {
+    t.w0 = t.h0 = t.n0 = 0;
+  }
+  return t;
+}
+
+struct RowInfo {
+  bool valid;
+  long long out_off, res_off;
+  int group;
+  int m;
+};
+
+__device__ __forceinline__ RowInfo row_info(const GemmKParams& p, const TileCoord& t, int r) {
+  RowInfo ri;
+  if (p.spatial) {
+    int iw = r & ((1 << p.bw_log2) - 1);
+    int ih = (r >> p.bw_log2) & ((1 << p.bh_log2) - 1);
+    int in = r >> (p.bw_log2 + p.bh_log2);
+    int n = t.n0 + in, oh = t.h0 + ih, ow = t.w0 + iw;
+    ri.valid = (n < p.NB) && (oh < p.H) && (ow < p.W);
+    long long pix = (static_cast<long long>(n) * p.OH + (oh * p.sy + p.oy)) * p.OW + (ow * p.sx + p.ox);
+    ri.out_off = pix * p.ldc;
+    ri.res_off = pix * p.ldr;
+    ri.group = n;
+    ri.m = (n * p.H + oh) * p.W + ow;
+  } else {
+    int m = t.m0 + r;
+    ri.valid = m < p.M;
+    ri.out_off = static_cast<long long>(m) * p.ldc;
+    ri.res_off = static_cast<long long>(m) * p.ldr;
+    ri.group = p.rows_per_group > 0 ? m / p.rows_per_group : 0;
+    ri.m = m;
+  }
+  return ri;
+}
+
+// Fused epilogue on 16 consecutive output columns [n, n+16) of one row.
+__device__ __forceinline__ void epilogue_store16(const GemmKParams& p, const RowInfo& ri, int n, float (&v)[16]) {
+  if (!ri.valid || n >= p.N) return;
+  const int flags = p.flags;
+  const bool full = (n + 16 <= p.N);
+#pragma unroll
+  for (int j = 0; j < 16; ++j) v[j] *= p.alpha;
+  if (flags & B200SD_GEMM_BIAS) {
+    if (full) {
+      const float4* b4 = reinterpret_cast<const float4*>(p.bias + n);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        float4 b = __ldg(b4 + j);
+        v[4 * j + 0] += b.x; v[4 * j + 1] += b.y; v[4 * j + 2] += b.z; v[4 * j + 3] += b.w;
+      }
+    } else {
+      for (int j = 0; j < 16; ++j) if (n + j < p.N) v[j] += __ldg(p.bias + n + j);
+    }
+  }
+  if (flags & B200SD_GEMM_BIAS_ROW) {
+    float b = __ldg(p.bias + ri.m);
+#pragma unroll
+    for (int j = 0; j < 16; ++j) v[j] += b;
+  }
+  if (flags & B200SD_GEMM_ROWVEC) {
+    const float* rv = p.rowvec + static_cast<long long>(ri.group) * p.ld_rowvec + n;
+    if (full) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        float4 b = __ldg(reinterpret_cast<const float4*>(rv) + j);
+        v[4 * j + 0] += b.x; v[4 * j + 1] += b.y; v[4 * j + 2] += b.z; v[4 * j + 3] += b.w;
+      }
+    } else {
+      for (int j = 0; j < 16; ++j) if (n + j < p.N) v[j] += __ldg(rv + j);
+    }
+  }
+  if (flags & B200SD_GEMM_SILU) {
+#pragma unroll
+    for (int j = 0; j < 16; ++j) v[j] = silu_f(v[j]);
+  }
+  const bool vec_ok = full && ((p.ldc & 7) == 0);
+  if (flags & B200SD_GEMM_RESIDUAL) {
+    const bf16* rp = p.residual + ri.res_off + n;
+    if (full && ((p.ldr & 7) == 0)) {
+      uint4 r0 = __ldg(reinterpret_cast<const uint4*>(rp));
+      uint4 r1 = __ldg(reinterpret_cast<const uint4*>(rp) + 1);
+      uint32_t w[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float2 f = unpack_bf16x2(w[j]);
+        v[2 * j] += f.x; v[2 * j + 1] += f.y;
+      }
+    } else {
+      for (int j = 0; j < 16; ++j) if (n + j < p.N) v[j] += __bfloat162float(rp[j]);
+    }
+  }
+  if (flags & B200SD_GEMM_OUT_F32) {
+    float* op = reinterpret_cast<float*>(p.out) + ri.out_off + n;
+    if (full && ((p.ldc & 3) == 0)) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        reinterpret_cast<float4*>(op)[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+    } else {
+      for (int j = 0; j < 16; ++j) if (n + j < p.N) op[j] = v[j];
+    }
+  } else {
+    bf16* op = reinterpret_cast<bf16*>(p.out) + ri.out_off + n;
+    if (vec_ok) {
+      uint4 o0, o1;
+      o0.x = pack_bf16x2(v[0], v[1]);   o0.y = pack_bf16x2(v[2], v[3]);
+      o0.z = pack_bf16x2(v[4], v[5]);   o0.w = pack_bf16x2(v[6], v[7]);
+      o1.x = pack_bf16x2(v[8], v[9]);   o1.y = pack_bf16x2(v[10], v[11]);
+      o1.z = pack_bf16x2(v[12], v[13]); o1.w = pack_bf16x2(v[14], v[15]);
+      reinterpret_cast<uint4*>(op)[0] = o0;
+      reinterpret_cast<uint4*>(op)[1] = o1;
+    } else {
+      for (int j = 0; j < 16; ++j) if (n + j < p.N) op[j] = __float2bfloat16_rn(v[j]);
+    }
+  }
+}
+
+// GEGLU epilogue: h and g are the matching 16-column chunks of the two halves of an N tile; `n` is the
+// output column (N_out = N/2).  Reference: diffusers GEGLU = proj(x).chunk(2) -> h * gelu(g).
+__device__ __forceinline__ void epilogue_geglu16(const GemmKParams& p, const RowInfo& ri, int n_h, int n_g, int n_out,
+                                                 float (&h)[16], float (&g)[16]) {
+  if (!ri.valid) return;
+  float v[16];
+#pragma unroll
+  for (int j = 0; j < 16; ++j) {
+    float hh = h[j] * p.alpha, gg = g[j] * p.alpha;
+    if (p.flags & B200SD_GEMM_BIAS) {
+      hh += __ldg(p.bias + n_h + j);
+      gg += __ldg(p.bias + n_g + j);
+    }
+    v[j] = hh * gelu_erf_f(gg);
+  }
+  bf16* op = reinterpret_cast<bf16*>(p.out) + ri.out_off + n_out;
+  uint4 o0, o1;
+  o0.x = pack_bf16x2(v[0], v[1]);   o0.y = pack_bf16x2(v[2], v[3]);
+  o0.z = pack_bf16x2(v[4], v[5]);   o0.w = pack_bf16x2(v[6], v[7]);
+  o1.x = pack_bf16x2(v[8], v[9]);   o1.y = pack_bf16x2(v[10], v[11]);
+  o1.z = pack_bf16x2(v[12], v[13]); o1.w = pack_bf16x2(v[14], v[15]);
+  reinterpret_cast<uint4*>(op)[0] = o0;
+  reinterpret_cast<uint4*>(op)[1] = o1;
+}
+
+template <int BN>
+__global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_constant__ GemmKParams p) {
+  constexpr int B_STAGE_BYTES = BN * 128;
+  constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
+  constexpr int NSTAGE = gemm_stages(BN);
+  constexpr int TMEM_COLS = tmem_cols_for(BN);
+  constexpr uint32_t IDESC = umma_idesc_bf16(BM, BN, 0);
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + NSTAGE * STAGE_BYTES);
+  uint64_t* empty_bar = full_bar + NSTAGE;
+  uint64_t* tfull_bar = empty_bar + NSTAGE;
+  uint64_t* tempty_bar = tfull_bar + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < NSTAGE; ++i) {
+      mbar_init(&full_bar[i], 1);
+      mbar_init(&empty_bar[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&tfull_bar[i], 1);
+      mbar_init(&tempty_bar[i], 128);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_slot, TMEM_COLS);
+    tmem_relinquish();
+  }
+  if (warp == 0 && lane == 0) {
+    for (int s = 0; s < p.nseg; ++s) {
+      tma_prefetch_desc(&p.tmA[s]);
+      tma_prefetch_desc(&p.tmB[s]);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int total_work = p.num_m_tiles * p.num_n_tiles * p.splits;
+
+  if (warp == 0) {
+    // ===================== TMA producer (one lane) =====================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int work = blockIdx.x; work < total_work; work += gridDim.x) {
+        const TileCoord t = decode_work(p, work);
+        const int kb0 = t.ks * p.kb_per_split;
+        const int kb1 = min(kb0 + p.kb_per_split, p.kb_total);
+        int seg = 0;
+        while (seg + 1 < p.nseg && kb0 >= p.seg_kb_start[seg + 1]) ++seg;
+        int local = kb0 - p.seg_kb_start[seg];
+        int tap = local / p.seg_cb[seg];
+        int cb = local - tap * p.seg_cb[seg];
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          mbar_arrive_expect_tx(&full_bar[stage], STAGE_BYTES);
+          uint8_t* sa = smem + stage * STAGE_BYTES;
+          uint8_t* sb = sa + A_STAGE_BYTES;
+          if (p.spatial) {
+            tma_load_5d(sa, &p.tmA[seg], &full_bar[stage], cb * BK, t.w0 + p.tap_dw[seg][tap],
+                        t.h0 + p.tap_dh[seg][tap], t.n0, p.tap_phase[seg][tap]);
+          } else {
+            tma_load_2d(sa, &p.tmA[seg], &full_bar[stage], cb * BK, t.m0);
+          }
+          tma_load_3d(sb, &p.tmB[seg], &full_bar[stage], cb * BK, tap, t.nt * BN);
+          if (++stage == NSTAGE) { stage = 0; phase ^= 1; }
+          if (++cb == p.seg_cb[seg]) {
+            cb = 0;
+            if (++tap == p.seg_taps[seg]) { tap = 0; ++seg; }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    int stage = 0;
+    uint32_t phase = 0;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int work = blockIdx.x; work < total_work; work += gridDim.x) {
+      const int ks = work / (p.num_m_tiles * p.num_n_tiles);
+      const int kb0 = ks * p.kb_per_split;
+      const int nkb = min(kb0 + p.kb_per_split, p.kb_total) - kb0;
+      mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + acc * BN;
+      for (int i = 0; i < nkb; ++i) {
+        mbar_wait(&full_bar[stage], phase);
+        tc_fence_after();
+        if (lane == 0) {
+          const uint32_t a_addr = smem_u32(smem + stage * STAGE_BYTES);
+          const uint32_t b_addr = a_addr + A_STAGE_BYTES;
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k) {
+            const uint64_t da = umma_smem_desc_sw128(a_addr + k * 32, 16, 1024);
+            const uint64_t db = umma_smem_desc_sw128(b_addr + k * 32, 16, 1024);
+            umma_bf16_ss(d_tmem, da, db, IDESC, (i | k) != 0 ? 1u : 0u);
+          }
+          umma_commit(&empty_bar[stage]);
+          if (i == nkb - 1) umma_commit(&tfull_bar[acc]);
+        }
+        __syncwarp();
+        if (++stage == NSTAGE) { stage = 0; phase ^= 1; }
+      }
+      acc ^= 1;
+      if (acc == 0) acc_phase ^= 1;
+    }
+  } else {
+    // ===================== epilogue warps (TMEM lane quadrant = warp % 4) =====================
+    const int q = warp & 3;
+    const int r = q * 32 + lane;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int work = blockIdx.x; work < total_work; work += gridDim.x) {
+      const TileCoord t = decode_work(p, work);
+      const RowInfo ri = row_info(p, t, r);
+      mbar_wait(&tfull_bar[acc], acc_phase);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN;
+      if (p.splits > 1) {
+        float* dst = p.partial +
+                     (static_cast<long long>((t.ks * p.num_n_tiles + t.nt)) * p.num_m_tiles + t.mt) * (BM * BN) +
+                     static_cast<long long>(r) * BN;
+#pragma unroll 1
+        for (int c = 0; c < BN / 16; ++c) {
+          uint32_t u[16];
+          tmem_ld16(taddr + c * 16, u);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            reinterpret_cast<uint4*>(dst + c * 16)[j] = make_uint4(u[4 * j], u[4 * j + 1], u[4 * j + 2], u[4 * j + 3]);
+        }
+      } else if (p.flags & B200SD_GEMM_GEGLU) {
+        if constexpr (BN % 32 == 0) {
+#pragma unroll 1
+          for (int c = 0; c < BN / 32; ++c) {
+            uint32_t uh[16], ug[16];
+            tmem_ld16(taddr + c * 16, uh);
+            tmem_ld16(taddr + BN / 2 + c * 16, ug);
+            tmem_ld_wait();
+            float h[16], g[16];
+#pragma unroll
+            for (int j = 0; j < 16; ++j) { h[j] = __uint_as_float(uh[j]); g[j] = __uint_as_float(ug[j]); }
+            epilogue_geglu16(p, ri, t.nt * BN + c * 16, t.nt * BN + BN / 2 + c * 16, t.nt * (BN / 2) + c * 16, h, g);
+          }
+        }
+      } else {
+#pragma unroll 1
+        for (int c = 0; c < BN / 16; ++c) {
+          uint32_t u[16];
+          tmem_ld16(taddr + c * 16, u);
+          tmem_ld_wait();
+          float v[16];
+#pragma unroll
+          for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(u[j]);
+          epilogue_store16(p, ri, t.nt * BN + c * 16, v);
+        }
+      }
+      tc_fence_before();
+      mbar_arrive(&tempty_bar[acc]);
+      acc ^= 1;
+      if (acc == 0) acc_phase ^= 1;
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  if (warp == 1) tmem_dealloc(tmem_base, TMEM_COLS);
+}
+
+// Split-K reduction + epilogue.  grid = (tiles, BN/16 or BN/32 for GEGLU), block = 128 (thread = tile row).
+template <int BN>
+__global__ void __launch_bounds__(128) gemm_splitk_reduce_kernel(const __grid_constant__ GemmKParams p) {
+  const int tile = blockIdx.x;  // nt * num_m_tiles + mt
+  const int c = blockIdx.y;
+  const int r = threadIdx.x;
+  const TileCoord t = decode_work(p, tile);  // ks == 0
+  const RowInfo ri = row_info(p, t, r);
+  const long long tile_elems = static_cast<long long>(BM) * BN;
+  const long long split_stride = static_cast<long long>(p.num_m_tiles) * p.num_n_tiles * tile_elems;
+  const float* src = p.partial + static_cast<long long>(tile) * tile_elems + static_cast<long long>(r) * BN;
+  if (p.flags & B200SD_GEMM_GEGLU) {
+    float h[16], g[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) { h[j] = 0.f; g[j] = 0.f; }
+    for (int s = 0; s < p.splits; ++s) {
+      const float4* ph = reinterpret_cast<const float4*>(src + s * split_stride + c * 16);
+      const float4* pg = reinterpret_cast<const float4*>(src + s * split_stride + BN / 2 + c * 16);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        float4 a = ph[j], b = pg[j];
+        h[4 * j] += a.x; h[4 * j + 1] += a.y; h[4 * j + 2] += a.z; h[4 * j + 3] += a.w;
+        g[4 * j] += b.x; g[4 * j + 1] += b.y; g[4 * j + 2] += b.z; g[4 * j + 3] += b.w;
+      }
+    }
+    epilogue_geglu16(p, ri, t.nt * BN + c * 16, t.nt * BN + BN / 2 + c * 16, t.nt * (BN / 2) + c * 16, h, g);
+  } else {
+    float v[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) v[j] = 0.f;
+    for (int s = 0; s < p.splits; ++s) {
+      const float4* ps = reinterpret_cast<const float4*>(src + s * split_stride + c * 16);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        float4 a = ps[j];
+        v[4 * j] += a.x; v[4 * j + 1] += a.y; v[4 * j + 2] += a.z; v[4 * j + 3] += a.w;
+      }
+    }
+    epilogue_store16(p, ri, t.nt * BN + c * 16, v);
+  }
+}
+
+struct GemmPlan {
+  GemmKParams kp;
+  int block_n;
+  int grid;
+  int reduce_grid_x, reduce_grid_y;
+};
+
+template <int BN>
+int prepare_gemm_bn() {  // called at plan time (outside any stream capture)
+  static bool attr_set = false;
+  if (!attr_set) {
+    B200SD_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     gemm_smem_bytes(BN)));
+    attr_set = true;
+  }
+  return 0;
+}
+int prepare_gemm(int bn) {
+  switch (bn) {
+    case 32: return prepare_gemm_bn<32>();
+    case 64: return prepare_gemm_bn<64>();
+    case 128: return prepare_gemm_bn<128>();
+    case 160: return prepare_gemm_bn<160>();
+    case 256: return prepare_gemm_bn<256>();
+  }
+  return fail(B200SD_ERR_INVALID, "gemm: unsupported block_n %d", bn);
+}
+
+template <int BN>
+int launch_gemm_bn(const GemmPlan& pl, cudaStream_t s) {
+  gemm_tc_kernel<BN><<<pl.grid, GEMM_THREADS, gemm_smem_bytes(BN), s>>>(pl.kp);
+  B200SD_CUDA(cudaGetLastError());
+  if (pl.kp.splits > 1) {
+    gemm_splitk_reduce_kernel<BN><<<dim3(pl.reduce_grid_x, pl.reduce_grid_y), 128, 0, s>>>(pl.kp);
+    B200SD_CUDA(cudaGetLastError());
+  }
+  return 0;
+}
+
+int launch_gemm(const void* plan, cudaStream_t s) {
+  const GemmPlan& pl = *static_cast<const GemmPlan*>(plan);
+  switch (pl.block_n) {
+    case 32: return launch_gemm_bn<32>(pl, s);
+    case 64: return launch_gemm_bn<64>(pl, s);
+    case 128: return launch_gemm_bn<128>(pl, s);
+    case 160: return launch_gemm_bn<160>(pl, s);
+    case 256: return launch_gemm_bn<256>(pl, s);
+  }
+  return fail(B200SD_ERR_INVALID, "gemm: unsupported block_n %d", pl.block_n);
+}
+
+int ilog2(int v) {
+  int l = 0;
+  while ((1 << (l + 1)) <= v) ++l;
+  return l;
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------------------------
+// Tiling / split-K choice (pure host arithmetic, also used by the workspace-size entry point)
+// ------------------------------------------------------------------------------------------------------
+int choose_gemm_tiling(const b200sd_gemm& g, GemmTiling* t) {
+  B200SD_CHECK_ARG(g.nseg >= 1 && g.nseg <= B200SD_MAX_SEG, "gemm: nseg=%d out of range", g.nseg);
+  B200SD_CHECK_ARG(g.N >= 1, "gemm: N=%d", g.N);
+  int kb_total = 0;
+  for (int s = 0; s < g.nseg; ++s) {
+    const b200sd_gemm_seg& sg = g.seg[s];
+    B200SD_CHECK_ARG(sg.channels >= 8 && sg.channels % 8 == 0, "gemm: segment %d channels=%d must be a multiple of 8",
+                     s, sg.channels);
+    B200SD_CHECK_ARG(sg.taps >= 1 && sg.taps <= B200SD_MAX_TAPS, "gemm: segment %d taps=%d", s, sg.taps);
+    kb_total += sg.taps * ((sg.channels + BK - 1) / BK);
+  }
+  int bn = g.block_n;
+  const bool geglu = (g.flags & B200SD_GEMM_GEGLU) != 0;
+  if (bn == 0) {
+    if (g.N <= 32 && !geglu) bn = 32;
+    else if (g.N <= 64 && !geglu) bn = 64;
+    else if (g.N % 160 == 0 && g.N % 128 != 0) bn = 160;
+    else if (g.N % 128 == 0) bn = 128;
+    else if (g.N % 160 == 0) bn = 160;
+    else bn = 128;
+  }
+  B200SD_CHECK_ARG(bn == 32 || bn == 64 || bn == 128 || bn == 160 || bn == 256, "gemm: block_n=%d unsupported", bn);
+  if (geglu) {
+    B200SD_CHECK_ARG(bn % 32 == 0 && g.N % bn == 0, "gemm: GEGLU needs N %% block_n == 0 and block_n %% 32 == 0 (N=%d, bn=%d)",
+                     g.N, bn);
+  }
+  t->block_n = bn;
+  t->kb_total = kb_total;
+  t->num_n_tiles = (g.N + bn - 1) / bn;
+  if (g.spatial) {
+    B200SD_CHECK_ARG(g.NB >= 1 && g.H >= 1 && g.W >= 1, "gemm: spatial dims NB=%d H=%d W=%d", g.NB, g.H, g.W);
+    // choose (bw, bh, bn) powers of two with product 128 maximising the fraction of useful rows
+    double best = -1.0;
+    int best_w = 0, best_h = 0, best_n = 0;
+    for (int lw = 7; lw >= 0; --lw) {
+      for (int lh = 7 - lw; lh >= 0; --lh) {
+        int ln = 7 - lw - lh;
+        long long tw = (g.W + (1 << lw) - 1) >> lw, th = (g.H + (1 << lh) - 1) >> lh, tn = (g.NB + (1 << ln) - 1) >> ln;
+        double util = static_cast<double>(g.W) * g.H * g.NB / (static_cast<double>(tw * th * tn) * 128.0);
+        if (util > best + 1e-9) { best = util; best_w = lw; best_h = lh; best_n = ln; }
+      }
+    }
+    t->bw_log2 = best_w; t->bh_log2 = best_h; t->bn_log2 = best_n;
+    t->tiles_w = (g.W + (1 << best_w) - 1) >> best_w;
+    t->tiles_h = (g.H + (1 << best_h) - 1) >> best_h;
+    t->tiles_nb = (g.NB + (1 << best_n) - 1) >> best_n;
+    t->num_m_tiles = t->tiles_w * t->tiles_h * t->tiles_nb;
+  } else {
+    B200SD_CHECK_ARG(g.M >= 1, "gemm: M=%d", g.M);
+    t->bw_log2 = t->bh_log2 = t->bn_log2 = 0;
+    t->tiles_w = t->tiles_h = t->tiles_nb = 0;
+    t->num_m_tiles = (g.M + BM - 1) / BM;
+  }
+  // split-K: minimise  waves(tiles*s) * (kb per split + fixed per-tile cost)  + reduce cost
+  const int sms = sm_count();
+  const long long tiles = static_cast<long long>(t->num_m_tiles) * t->num_n_tiles;
+  int splits = g.splits;
+  if (splits <= 0) {
+    double best_cost = 1e30;
+    int best_s = 1;
+    const int max_s = std::min(32, std::max(1, kb_total / 4));
+    for (int s = 1; s <= max_s; ++s) {
+      int per = (kb_total + s - 1) / s;
+      int s_eff = (kb_total + per - 1) / per;
+      if (s_eff != s) continue;
+      long long waves = (tiles * s + sms - 1) / sms;
+      double cost = static_cast<double>(waves) * (per + 6.0) + (s > 1 ? 10.0 + 1.5 * s : 0.0);
+      if (cost < best_cost - 1e-9) { best_cost = cost; best_s = s; }
+    }
+    splits = best_s;
+  }
+  B200SD_CHECK_ARG(splits >= 1 && splits <= kb_total, "gemm: splits=%d invalid for %d k-blocks", splits, kb_total);
+  int per = (kb_total + splits - 1) / splits;
+  splits = (kb_total + per - 1) / per;
+  t->splits = splits;
+  t->kb_per_split = per;
+  return 0;
+}
+
+int plan_gemm(const b200sd_gemm& g, PlannedOp* out) {
+  GemmTiling t;
+  int rc = choose_gemm_tiling(g, &t);
+  if (rc) return rc;
+  GemmPlan* pl = new (std::nothrow) GemmPlan();
+  if (!pl) return fail(B200SD_ERR_CUDA, "out of host memory");
+  GemmKParams& kp = pl->kp;
+  memset(&kp, 0, sizeof(kp));
+  const int bn = t.block_n;
+  B200SD_CHECK_ARG(g.out != nullptr, "gemm: out is NULL");
+  B200SD_CHECK_ARG(g.ldw % 8 == 0, "gemm: ldw=%lld must be a multiple of 8", (long long)g.ldw);
+  kp.nseg = g.nseg;
+  int kb = 0;
+  for (int s = 0; s < g.nseg; ++s) {
+    const b200sd_gemm_seg& sg = g.seg[s];
+    B200SD_CHECK_ARG(sg.a && sg.w, "gemm: segment %d has NULL pointers", s);
+    B200SD_CHECK_ARG(sg.lda % 8 == 0 && sg.lda >= sg.channels, "gemm: segment %d lda=%lld invalid", s, (long long)sg.lda);
+    B200SD_CHECK_ARG((reinterpret_cast<uintptr_t>(sg.a) & 15) == 0 && (reinterpret_cast<uintptr_t>(sg.w) & 15) == 0,
+                     "gemm: segment %d pointers must be 16-byte aligned", s);
+    kp.seg_cb[s] = (sg.channels + BK - 1) / BK;
+    kp.seg_taps[s] = sg.taps;
+    kp.seg_kb_start[s] = kb;
+    kb += kp.seg_cb[s] * sg.taps;
+    for (int i = 0; i < sg.taps; ++i) {
+      kp.tap_phase[s][i] = sg.tap_phase[i];
+      kp.tap_dh[s][i] = sg.tap_dh[i];
+      kp.tap_dw[s][i] = sg.tap_dw[i];
+    }
+    // activation map
+    if (g.spatial) {
+      B200SD_CHECK_ARG(sg.Hs >= 1 && sg.Ws >= 1 && sg.phases >= 1, "gemm: segment %d spatial source dims invalid", s);
+      uint64_t dims[5] = {(uint64_t)sg.channels, (uint64_t)sg.Ws, (uint64_t)sg.Hs, (uint64_t)g.NB, (uint64_t)sg.phases};
+      uint64_t st[4] = {(uint64_t)sg.lda * 2, (uint64_t)sg.Ws * sg.lda * 2, (uint64_t)sg.Hs * sg.Ws * sg.lda * 2,
+                        (uint64_t)g.NB * sg.Hs * sg.Ws * sg.lda * 2};
+      uint32_t box[5] = {BK, 1u << t.bw_log2, 1u << t.bh_log2, 1u << t.bn_log2, 1};
+      rc = encode_tensor_map_bf16(&kp.tmA[s], sg.a, 5, dims, st, box);
+    } else {
+      uint64_t dims[2] = {(uint64_t)sg.channels, (uint64_t)g.M};
+      uint64_t st[1] = {(uint64_t)sg.lda * 2};
+      uint32_t box[2] = {BK, BM};
+      rc = encode_tensor_map_bf16(&kp.tmA[s], sg.a, 2, dims, st, box);
+    }
+    if (rc) { delete pl; return rc; }
+    // weight map: [N][taps][channels], row pitch ldw
+    {
+      uint64_t dims[3] = {(uint64_t)sg.channels, (uint64_t)sg.taps, (uint64_t)g.N};
+      uint64_t st[2] = {(uint64_t)sg.channels * 2, (uint64_t)g.ldw * 2};
+      uint32_t box[3] = {BK, 1, (uint32_t)bn};
+      rc = encode_tensor_map_bf16(&kp.tmB[s], sg.w, 3, dims, st, box);
+      if (rc) { delete pl; return rc; }
+    }
+  }
+  kp.seg_kb_start[g.nseg] = kb;
+  kp.kb_total = t.kb_total;
+  kp.kb_per_split = t.kb_per_split;
+  kp.splits = t.splits;
+  kp.spatial = g.spatial;
+  kp.N = g.N;
+  kp.NB = g.NB; kp.H = g.H; kp.W = g.W;
+  kp.M = g.spatial ? g.NB * g.H * g.W : g.M;
+  kp.bw_log2 = t.bw_log2; kp.bh_log2 = t.bh_log2; kp.bn_log2 = t.bn_log2;
+  kp.tiles_w = std::max(t.tiles_w, 1); kp.tiles_h = std::max(t.tiles_h, 1); kp.tiles_nb = std::max(t.tiles_nb, 1);
+  kp.num_m_tiles = t.num_m_tiles; kp.num_n_tiles = t.num_n_tiles;
+  kp.out = g.out; kp.ldc = g.ldc;
+  if (g.spatial) {
+    kp.OH = g.OH > 0 ? g.OH : g.H; kp.OW = g.OW > 0 ? g.OW : g.W;
+    kp.sy = g.sy > 0 ? g.sy : 1; kp.sx = g.sx > 0 ? g.sx : 1;
+    kp.oy = g.oy; kp.ox = g.ox;
+  }
+  kp.bias = g.bias; kp.rowvec = g.rowvec; kp.ld_rowvec = g.ld_rowvec; kp.rows_per_group = g.rows_per_group;
+  kp.residual = static_cast<const bf16*>(g.residual); kp.ldr = g.ldr;
+  kp.alpha = g.alpha == 0.0f ? 1.0f : g.alpha;
+  kp.flags = g.flags;
+  if ((g.flags & (B200SD_GEMM_BIAS | B200SD_GEMM_BIAS_ROW)) && !g.bias) { delete pl; return fail(B200SD_ERR_INVALID, "gemm: bias flag without bias pointer"); }
+  if ((g.flags & B200SD_GEMM_ROWVEC) && !g.rowvec) { delete pl; return fail(B200SD_ERR_INVALID, "gemm: rowvec flag without pointer"); }
+  if ((g.flags & B200SD_GEMM_RESIDUAL) && !g.residual) { delete pl; return fail(B200SD_ERR_INVALID, "gemm: residual flag without pointer"); }
+  if ((g.flags & B200SD_GEMM_GEGLU) && (g.flags & (B200SD_GEMM_RESIDUAL | B200SD_GEMM_ROWVEC | B200SD_GEMM_SILU | B200SD_GEMM_OUT_F32 | B200SD_GEMM_BIAS_ROW))) {
+    delete pl; return fail(B200SD_ERR_INVALID, "gemm: GEGLU epilogue only combines with BIAS");
+  }
+  if ((g.flags & B200SD_GEMM_GEGLU) && (g.ldc % 8 != 0)) { delete pl; return fail(B200SD_ERR_INVALID, "gemm: GEGLU needs ldc %% 8 == 0"); }
+  if (t.splits > 1) {
+    long long need = static_cast<long long>(t.splits) * t.num_m_tiles * t.num_n_tiles * BM * bn * 4;
+    if (!g.workspace || g.workspace_bytes < need) {
+      delete pl;
+      return fail(B200SD_ERR_INVALID, "gemm: split-K=%d needs %lld workspace bytes, got %lld", t.splits, need,
+                  (long long)g.workspace_bytes);
+    }
+    kp.partial = static_cast<float*>(g.workspace);
+  }
+  pl->block_n = bn;
+  rc = prepare_gemm(bn);
+  if (rc) { delete pl; return rc; }
+  long long total_work = static_cast<long long>(t.num_m_tiles) * t.num_n_tiles * t.splits;
+  pl->grid = static_cast<int>(std::min<long long>(total_work, sm_count()));
+  pl->reduce_grid_x = t.num_m_tiles * t.num_n_tiles;
+  pl->reduce_grid_y = (g.flags & B200SD_GEMM_GEGLU) ? bn / 32 : bn / 16;
+  out->kind = B200SD_OP_GEMM;
+  out->plan = pl;
+  out->launch = launch_gemm;
+  out->destroy = destroy_plan<GemmPlan>;
+  out->launches = t.splits > 1 ? 2 : 1;
+  (void)ilog2;
+  return 0;
+}
+
+}  // namespace b200sd
