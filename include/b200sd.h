@@ -173,7 +173,8 @@ enum { /* columns of one step-table row */
   B200SD_ST_CX = 4,          /* x' = CX*x + CE*eps + C0*x0 + C1*(x0 - x0_prev)                            */
   B200SD_ST_CE = 5,
   B200SD_ST_C0 = 6,
-  B200SD_ST_C1 = 7
+  B200SD_ST_C1 = 7,
+  B200SD_ST_GUIDANCE = 8     /* guidance scale (read when cfg_step.gs_from_table != 0)                     */
 };
 
 typedef struct b200sd_timestep_embed {
@@ -229,7 +230,7 @@ typedef struct b200sd_cfg_step {
   int32_t cfg;      /* 1: eps holds 2B rows and is combined; 0: eps is used as is                          */
   int32_t x_dtype, B, C, hw, Cpad, rep;
   int32_t nsteps;   /* rows in the table (next_in uses row step+1 if it exists)                            */
-  int32_t pad_;
+  int32_t gs_from_table; /* 1: take the guidance scale from the step table (column B200SD_ST_GUIDANCE)      */
 } b200sd_cfg_step;
 
 typedef struct b200sd_axpby {

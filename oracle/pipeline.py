@@ -1,0 +1,34 @@
+"""The reference's denoising loop restated over the oracle modules (test infrastructure).
+
+Follows pipelines/sd_unified_pipeline.py:465-523 line for line: CFG duplicate (:467-469), scale_model_input
+(:472), UNet (:475-482), chunk + `guidance_scale * (text - uncond) + uncond` (:484-486), scheduler.step (:489),
+latents / scaling_factor (:521), vae.decode (:523)."""
+from __future__ import annotations
+
+import torch
+
+
+def cfg_combine(noise_pred: torch.Tensor, guidance_scale: float) -> torch.Tensor:
+    uncond, text = noise_pred.chunk(2)
+    return guidance_scale * (text - uncond) + uncond
+
+
+@torch.no_grad()
+def denoise(unet, scheduler, latents, prompt_embeds, timesteps, guidance_scale, do_cfg=True, added_cond_kwargs=None,
+            return_eps=False):
+    eps_trace = []
+    for t in timesteps:
+        x_in = torch.cat([latents] * 2) if do_cfg else latents
+        x_in = scheduler.scale_model_input(x_in, t)
+        noise_pred = unet(x_in, t, prompt_embeds, added_cond_kwargs=added_cond_kwargs)
+        if return_eps:
+            eps_trace.append(noise_pred.clone())
+        if do_cfg:
+            noise_pred = cfg_combine(noise_pred, guidance_scale)
+        latents = scheduler.step(noise_pred, t, latents)
+    return (latents, eps_trace) if return_eps else latents
+
+
+@torch.no_grad()
+def decode(vae, latents):
+    return vae.decode(latents / vae.config["scaling_factor"])

@@ -1,0 +1,247 @@
+"""Restatement of the diffusers 0.27.2 schedulers the reference can select on this path
+(models/stable_diffusion.py:135-138 default Euler; :205-214 DDIM / euler / DPM++ 2M / DPM++ 2M Karras).
+
+Test infrastructure (see oracle/__init__.py).  Table construction repeats diffusers' numpy expressions so
+`timesteps` / `sigmas` are reproduced bit for bit; `step` keeps diffusers' operation order
+in fp32.  Scheduler hyper-parameters of SD checkpoints: scripts/convert_from_A1111.py:947-982.
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+SD15_SCHEDULER_CONFIG = dict(num_train_timesteps=1000, beta_start=0.00085, beta_end=0.012, beta_schedule="scaled_linear",
+                             steps_offset=1, clip_sample=False, set_alpha_to_one=False, skip_prk_steps=True,
+                             prediction_type="epsilon")
+SDXL_SCHEDULER_CONFIG = dict(num_train_timesteps=1000, beta_start=0.00085, beta_end=0.012, beta_schedule="scaled_linear",
+                             steps_offset=1, timestep_spacing="leading", interpolation_type="linear",
+                             use_karras_sigmas=False, prediction_type="epsilon", clip_sample=False,
+                             set_alpha_to_one=False, skip_prk_steps=True, sample_max_value=1.0)
+
+
+def _betas(cfg):
+    n = cfg["num_train_timesteps"]
+    if cfg.get("beta_schedule", "linear") == "scaled_linear":
+        return torch.linspace(cfg["beta_start"] ** 0.5, cfg["beta_end"] ** 0.5, n, dtype=torch.float32) ** 2
+    return torch.linspace(cfg["beta_start"], cfg["beta_end"], n, dtype=torch.float32)
+
+
+class _Base:
+    order = 1
+
+    def __init__(self, **config):
+        self.config = dict(config)
+        self.betas = _betas(self.config)
+        self.alphas = 1.0 - self.betas
+        self.alphas_cumprod = torch.cumprod(self.alphas, dim=0)
+        self.timesteps = None
+        self.sigmas = None
+        self.step_index = None
+        self.num_inference_steps = None
+
+    def _index_for_timestep(self, t):
+        idx = (self.timesteps == torch.as_tensor(t).to(self.timesteps.dtype)).nonzero()
+        pos = 1 if len(idx) > 1 else 0
+        return idx[pos].item()
+
+    def _init_step_index(self, t):
+        if self.step_index is None:
+            self.step_index = self._index_for_timestep(t)
+
+
+class EulerDiscreteOracle(_Base):
+    def __init__(self, **config):
+        super().__init__(**config)
+        self.spacing = self.config.get("timestep_spacing", "linspace")
+        sig = ((1 - self.alphas_cumprod) / self.alphas_cumprod) ** 0.5
+        self.sigmas = torch.cat([sig.flip(0), torch.zeros(1)])
+
+    @property
+    def init_noise_sigma(self):
+        m = self.sigmas.max()
+        if self.spacing in ("linspace", "trailing"):
+            return m
+        return (m ** 2 + 1) ** 0.5
+
+    def set_timesteps(self, n, device=None):
+        N = self.config["num_train_timesteps"]
+        self.num_inference_steps = n
+        if self.spacing == "linspace":
+            ts = np.linspace(0, N - 1, n, dtype=np.float32)[::-1].copy()
+        elif self.spacing == "leading":
+            ts = (np.arange(0, n) * (N // n)).round()[::-1].copy().astype(np.float32)
+            ts += self.config.get("steps_offset", 0)
+        else:
+            ts = (np.arange(N, 0, -N / n)).round().copy().astype(np.float32)
+            ts -= 1
+        sig = np.array(((1 - self.alphas_cumprod) / self.alphas_cumprod) ** 0.5)
+        sig = np.interp(ts, np.arange(0, len(sig)), sig)
+        sig = torch.from_numpy(sig).to(dtype=torch.float32)
+        self.timesteps = torch.from_numpy(ts.astype(np.float32))
+        self.sigmas = torch.cat([sig, torch.zeros(1)])
+        self.step_index = None
+
+    def scale_model_input(self, x, t):
+        self._init_step_index(t)
+        s = self.sigmas[self.step_index]
+        return x / ((s ** 2 + 1) ** 0.5)
+
+    def step(self, eps, t, x):
+        self._init_step_index(t)
+        x = x.to(torch.float32)
+        s = self.sigmas[self.step_index]
+        x0 = x - s * eps
+        d = (x - x0) / s
+        dt = self.sigmas[self.step_index + 1] - s
+        self.step_index += 1
+        return x + d * dt
+
+    def add_noise(self, x0, noise, timesteps):
+        idx = [self._index_for_timestep(t) for t in timesteps]
+        s = self.sigmas[idx].flatten().to(x0.dtype)
+        while s.dim() < x0.dim():
+            s = s.unsqueeze(-1)
+        return x0 + noise * s
+
+
+class DDIMOracle(_Base):
+    init_noise_sigma = 1.0
+
+    def __init__(self, **config):
+        super().__init__(**config)
+        self.final_alpha_cumprod = torch.tensor(1.0) if self.config.get("set_alpha_to_one", True) else self.alphas_cumprod[0]
+
+    def set_timesteps(self, n, device=None):
+        N = self.config["num_train_timesteps"]
+        self.num_inference_steps = n
+        spacing = self.config.get("timestep_spacing", "leading")
+        if spacing == "leading":
+            ts = (np.arange(0, n) * (N // n)).round()[::-1].copy().astype(np.int64)
+            ts += self.config.get("steps_offset", 0)
+        elif spacing == "linspace":
+            ts = np.linspace(0, N - 1, n).round()[::-1].copy().astype(np.int64)
+        else:
+            ts = np.round(np.arange(N, 0, -N / n)).astype(np.int64)
+            ts -= 1
+        self.timesteps = torch.from_numpy(ts)
+
+    def scale_model_input(self, x, t):
+        return x
+
+    def step(self, eps, t, x):
+        t = int(t)
+        prev_t = t - self.config["num_train_timesteps"] // self.num_inference_steps
+        a_t = self.alphas_cumprod[t]
+        a_p = self.alphas_cumprod[prev_t] if prev_t >= 0 else self.final_alpha_cumprod
+        b_t = 1 - a_t
+        x0 = (x - b_t ** 0.5 * eps) / a_t ** 0.5
+        if self.config.get("clip_sample", True):
+            x0 = x0.clamp(-self.config.get("clip_sample_range", 1.0), self.config.get("clip_sample_range", 1.0))
+        direction = (1 - a_p) ** 0.5 * eps
+        return a_p ** 0.5 * x0 + direction
+
+    def add_noise(self, x0, noise, timesteps):
+        a = self.alphas_cumprod[timesteps.long()].to(x0.dtype)
+        sa, sb = a ** 0.5, (1 - a) ** 0.5
+        while sa.dim() < x0.dim():
+            sa, sb = sa.unsqueeze(-1), sb.unsqueeze(-1)
+        return sa * x0 + sb * noise
+
+
+class DPMSolverMultistepOracle(_Base):
+    """DPM-Solver++(2M), midpoint, epsilon prediction, final sigma 0, optional Karras sigmas."""
+    init_noise_sigma = 1.0
+
+    def __init__(self, use_karras_sigmas=False, **config):
+        super().__init__(**config)
+        self.use_karras = use_karras_sigmas
+        self.m = [None, None]
+        self.lower_order_nums = 0
+
+    def set_timesteps(self, n, device=None):
+        N = self.config["num_train_timesteps"]
+        self.num_inference_steps = n
+        ts = np.linspace(0, N - 1, n + 1).round()[::-1][:-1].copy().astype(np.int64)
+        sig = np.array(((1 - self.alphas_cumprod) / self.alphas_cumprod) ** 0.5)
+        log_sig = np.log(sig)
+        if self.use_karras:
+            sflip = np.flip(sig).copy()
+            smin, smax = sflip[-1].item(), sflip[0].item()
+            ramp = np.linspace(0, 1, n)
+            rho = 7.0
+            sig = (smax ** (1 / rho) + ramp * (smin ** (1 / rho) - smax ** (1 / rho))) ** rho
+            ts = np.array([self._sigma_to_t(s, log_sig) for s in sig]).round()
+        else:
+            sig = np.interp(ts, np.arange(0, len(sig)), sig)
+        sig = np.concatenate([sig, [0.0]]).astype(np.float32)
+        self.sigmas = torch.from_numpy(sig)
+        self.timesteps = torch.from_numpy(ts).to(torch.int64)
+        self.m = [None, None]
+        self.lower_order_nums = 0
+        self.step_index = None
+
+    @staticmethod
+    def _sigma_to_t(sigma, log_sigmas):
+        log_sigma = np.log(np.maximum(sigma, 1e-10))
+        dists = log_sigma - log_sigmas[:, np.newaxis]
+        low_idx = np.cumsum((dists >= 0), axis=0).argmax(axis=0).clip(max=log_sigmas.shape[0] - 2)
+        high_idx = low_idx + 1
+        low, high = log_sigmas[low_idx], log_sigmas[high_idx]
+        w = np.clip((low - log_sigma) / (low - high), 0, 1)
+        t = (1 - w) * low_idx + w * high_idx
+        return t.reshape(np.shape(sigma))
+
+    @staticmethod
+    def _alpha_sigma(sigma):
+        alpha = 1 / ((sigma ** 2 + 1) ** 0.5)
+        return alpha, sigma * alpha
+
+    def scale_model_input(self, x, t):
+        return x
+
+    def step(self, eps, t, x):
+        self._init_step_index(t)
+        i = self.step_index
+        n = len(self.timesteps)
+        lower_final = i == n - 1  # final_sigmas_type == "zero" (default) always forces first order on the last step
+        a_s, s_s = self._alpha_sigma(self.sigmas[i])
+        x0 = (x - s_s * eps) / a_s
+        self.m = [self.m[1], x0]
+        x = x.to(torch.float32)
+        a_t, s_t = self._alpha_sigma(self.sigmas[i + 1])
+        lam_t = torch.log(a_t) - torch.log(s_t)
+        lam_s = torch.log(a_s) - torch.log(s_s)
+        h = lam_t - lam_s
+        if self.lower_order_nums < 1 or lower_final:
+            out = (s_t / s_s) * x - (a_t * (torch.exp(-h) - 1.0)) * x0
+        else:
+            a_s1, s_s1 = self._alpha_sigma(self.sigmas[i - 1])
+            lam_s1 = torch.log(a_s1) - torch.log(s_s1)
+            h0 = lam_s - lam_s1
+            r0 = h0 / h
+            D0, D1 = self.m[1], (1.0 / r0) * (self.m[1] - self.m[0])
+            out = (s_t / s_s) * x - (a_t * (torch.exp(-h) - 1.0)) * D0 - 0.5 * (a_t * (torch.exp(-h) - 1.0)) * D1
+        if self.lower_order_nums < 2:
+            self.lower_order_nums += 1
+        self.step_index += 1
+        return out
+
+    def add_noise(self, x0, noise, timesteps):
+        idx = [self._index_for_timestep(t) for t in timesteps]
+        a, s = self._alpha_sigma(self.sigmas[idx].flatten().to(x0.dtype))
+        while a.dim() < x0.dim():
+            a, s = a.unsqueeze(-1), s.unsqueeze(-1)
+        return a * x0 + s * noise
+
+
+def make_scheduler(name: str, config: dict):
+    """Name table of models/stable_diffusion.py:205-222 (hot-path subset)."""
+    if name == "euler":
+        return EulerDiscreteOracle(**config)
+    if name == "DDIM":
+        return DDIMOracle(**config)
+    if name == "DPM++ 2M":
+        return DPMSolverMultistepOracle(**config)
+    if name == "DPM++ 2M Karras":
+        return DPMSolverMultistepOracle(use_karras_sigmas=True, **config)
+    raise ValueError(f"Unknown scheduler name: {name}")

@@ -32,7 +32,7 @@ BF16, F32, F16 = 0, 1, 2
 # gemm flags
 GEMM_BIAS, GEMM_BIAS_ROW, GEMM_ROWVEC, GEMM_RESIDUAL, GEMM_SILU, GEMM_GEGLU, GEMM_OUT_F32 = 1, 2, 4, 8, 16, 32, 64
 # step-table columns
-ST_TIMESTEP, ST_IN_SCALE, ST_K1, ST_K2, ST_CX, ST_CE, ST_C0, ST_C1 = range(8)
+ST_TIMESTEP, ST_IN_SCALE, ST_K1, ST_K2, ST_CX, ST_CE, ST_C0, ST_C1, ST_GUIDANCE = range(9)
 
 ERR_INVALID, ERR_CUDA, ERR_NO_DEVICE, ERR_UNSUPPORTED = -1, -2, -3, -4
 
@@ -121,7 +121,7 @@ class CfgStep(C.Structure):
         ("eps", C.c_void_p), ("ld_eps", C.c_int64), ("x", C.c_void_p), ("x_out", C.c_void_p), ("x0_prev", C.c_void_p),
         ("next_in", C.c_void_p), ("step_table", C.c_void_p), ("step_counter", C.c_void_p),
         ("guidance_scale", C.c_float), ("cfg", C.c_int32), ("x_dtype", C.c_int32), ("B", C.c_int32), ("C", C.c_int32),
-        ("hw", C.c_int32), ("Cpad", C.c_int32), ("rep", C.c_int32), ("nsteps", C.c_int32), ("pad_", C.c_int32),
+        ("hw", C.c_int32), ("Cpad", C.c_int32), ("rep", C.c_int32), ("nsteps", C.c_int32), ("gs_from_table", C.c_int32),
     ]
 
 

@@ -423,7 +423,7 @@ int launch_softmax_rows(const void* plan, cudaStream_t s) {
 // ======================================================================================================
 struct CSParams {
   const bf16* eps; long long ld_eps; const void* x; void* x_out; float* x0_prev; bf16* next_in;
-  const float* table; const int* counter; float gs; int cfg, x_dtype, B, C, hw, Cpad, rep, nsteps;
+  const float* table; const int* counter; float gs; int cfg, x_dtype, B, C, hw, Cpad, rep, nsteps, gs_from_table;
 };
 __global__ void cfg_step_kernel(const CSParams p) {
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
@@ -433,6 +433,7 @@ __global__ void cfg_step_kernel(const CSParams p) {
   const float* row = p.table + static_cast<long long>(step) * B200SD_STEP_ROW;
   const float K1 = row[B200SD_ST_K1], K2 = row[B200SD_ST_K2], CX = row[B200SD_ST_CX], CE = row[B200SD_ST_CE],
               C0 = row[B200SD_ST_C0], C1 = row[B200SD_ST_C1];
+  const float gs = p.gs_from_table ? row[B200SD_ST_GUIDANCE] : p.gs;
   float next_scale = 1.0f;
   if (p.next_in && step + 1 < p.nsteps) next_scale = p.table[static_cast<long long>(step + 1) * B200SD_STEP_ROW + B200SD_ST_IN_SCALE];
   const bf16* eu = p.eps + (static_cast<long long>(b) * p.hw + pix) * p.ld_eps;
@@ -440,7 +441,7 @@ __global__ void cfg_step_kernel(const CSParams p) {
   for (int c = 0; c < p.C; ++c) {
     const float u = __bfloat162float(eu[c]);
     float e = u;
-    if (p.cfg) e = p.gs * (__bfloat162float(ec[c]) - u) + u;
+    if (p.cfg) e = gs * (__bfloat162float(ec[c]) - u) + u;
     const long long xi = (static_cast<long long>(b) * p.C + c) * p.hw + pix;
     const float x = load_as_float(p.x, xi, p.x_dtype);
     const float x0 = (x - K1 * e) * K2;
@@ -625,7 +626,7 @@ int plan_cfg_step(const b200sd_cfg_step& g, PlannedOp* out) {
   B200SD_CHECK_ARG(g.B >= 1 && g.C >= 1 && g.hw >= 1 && g.ld_eps >= g.C && g.nsteps >= 1, "cfg_step: bad shape");
   B200SD_CHECK_ARG(!g.next_in || (g.Cpad >= g.C && g.rep >= 1), "cfg_step: next_in needs Cpad/rep");
   CSParams p{static_cast<const bf16*>(g.eps), g.ld_eps, g.x, g.x_out, g.x0_prev, static_cast<bf16*>(g.next_in),
-             g.step_table, g.step_counter, g.guidance_scale, g.cfg, g.x_dtype, g.B, g.C, g.hw, g.Cpad, g.rep, g.nsteps};
+             g.step_table, g.step_counter, g.guidance_scale, g.cfg, g.x_dtype, g.B, g.C, g.hw, g.Cpad, g.rep, g.nsteps, g.gs_from_table};
   return finish_plan(out, B200SD_OP_CFG_STEP, p, launch_cfg_step);
 }
 

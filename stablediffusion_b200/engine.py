@@ -1,0 +1,162 @@
+"""The fused denoising loop: one CUDA-graph launch per sampler step.
+
+What the reference executes per step in Python + a few hundred library launches
+(pipelines/sd_unified_pipeline.py:465-489: cat([latents]*2), scale_model_input, UNet, chunk, CFG combine,
+scheduler.step) is here ONE captured op program:
+
+    [UNet ops on the already scaled / duplicated NHWC input]
+    -> CFG_STEP  (eps = u + s(c-u); scheduler update from the device step table; ALSO writes the next step's
+                  scaled, duplicated UNet input, so a1/a2 of SURVEY §8a never exist as separate work)
+    -> STEP_ADVANCE (++device step counter)
+
+Latents stay on the device in fp32 for the whole trajectory (the reference rounds them to fp16 every step —
+SURVEY App. B.1; keeping an fp32 master is strictly more accurate and is the documented deviation).
+
+Optional cond/uncond GPU-pair split: each rank of a pair runs the UNet on ONE half of the CFG
+batch, the eps halves are exchanged with one NCCL all-gather per step, and both ranks then run the same
+CFG_STEP so latents stay replicated.
+"""
+from __future__ import annotations
+
+from typing import Dict, Optional
+
+import torch
+
+from . import _native as N
+from . import lowering as L
+from .unet import B200UNet, UNetLowering, cfg_is_sdxl
+
+MAX_STEPS = 1000
+
+
+class DenoiseEngine:
+    def __init__(self, unet: B200UNet, B: int, h: int, w: int, do_cfg: bool, ctx_dim: int, uses_history: bool,
+                 pair_group=None, pair_rank: int = 0, use_graph: bool = True):
+        if unet.packed is None:
+            raise RuntimeError("UNet has no weights on a CUDA device")
+        self.unet, self.B, self.h, self.w, self.do_cfg = unet, B, h, w, do_cfg
+        self.device = unet.device
+        self.pair_group, self.pair_rank = pair_group, pair_rank
+        self.split = pair_group is not None
+        if self.split and not do_cfg:
+            raise ValueError("the cond/uncond pair split needs classifier-free guidance")
+        cfg = unet.config
+        C = cfg["in_channels"]
+        rep_total = 2 if do_cfg else 1
+        self.NB = B if self.split else rep_total * B      # UNet batch on THIS rank
+        NB = self.NB
+        pk = unet.packed
+        self.use_graph = use_graph
+
+        # ---- static device state ----------------------------------------------------------------------
+        pre = L.Builder(self.device, workspace_bytes=16)
+        self.latents = pre.empty([B, C, h, w], torch.float32)
+        self.ctx = pre.empty([NB, unet.ctx_len, ctx_dim])
+        self.table = pre.zeros([MAX_STEPS, N.STEP_ROW], torch.float32)
+        self.counter = pre.zeros([1], torch.int32)
+        self.unet_in_full = pre.empty([rep_total * B, h * w, pk.cin_pad])  # both CFG halves (identical rows)
+        self.hist = pre.zeros([B, C, h * w], torch.float32) if uses_history else None
+        pre.prep_latents(self.latents, self.unet_in_full, rep=rep_total, step_table=self.table, step_counter=self.counter)
+        self.prep = pre
+
+        # ---- the step program -------------------------------------------------------------------------
+        b = L.Builder(self.device)
+        self.b = b
+        unet_in = self.unet_in_full[:NB]  # with the pair split each rank feeds one (identical) half
+        kw = {}
+        if cfg_is_sdxl(cfg):
+            self.text_embeds = b.empty([NB, cfg["projection_class_embeddings_input_dim"] - 6 * cfg["addition_time_embed_dim"]])
+            self.time_ids = b.empty([NB, 6], torch.float32)
+            kw = dict(text_embeds=self.text_embeds, time_ids=self.time_ids)
+        low = UNetLowering(b, pk, NB, h, w, unet.ctx_len)
+        self.eps_full = b.empty([rep_total * B, h * w, cfg["out_channels"]])
+        eps_local = low.emit(unet_in, self.ctx, step_table=self.table, step_counter=self.counter, **kw)
+        self.eps_local = eps_local
+        self.unet_ops = b.prog.num_ops
+        if not self.split:
+            self.eps_for_step = eps_local
+            self._emit_tail(b, eps_local)
+            self.tail = None
+        else:
+            # UNet graph | NCCL all-gather of eps halves | CFG_STEP graph
+            tail = L.Builder(self.device, workspace_bytes=16)
+            self._emit_tail(tail, self.eps_full)
+            self.tail = tail
+        self.unet_flops = b.flops
+        self._captured = False
+        self._stream = torch.cuda.Stream(self.device)
+
+    def _emit_tail(self, b: L.Builder, eps):
+        b.cfg_step(eps, self.latents, self.latents, self.table, self.counter, 1.0, self.do_cfg, MAX_STEPS,
+                   x0_prev=self.hist, next_in=self.unet_in_full, rep=2 if self.do_cfg else 1, gs_from_table=True)
+        b.step_advance(self.counter)
+
+    @property
+    def launches_per_step(self) -> int:
+        return self.b.prog.num_launches + (self.tail.prog.num_launches if self.tail else 0)
+
+    # ---- one trajectory ---------------------------------------------------------------------------------
+    def load(self, latents, prompt_embeds, step_rows: torch.Tensor, guidance_scale: float, text_embeds=None, time_ids=None):
+        """Stage one request: latents (any float dtype, NCHW), context embeddings, the scheduler's table rows."""
+        n = step_rows.shape[0]
+        if n > MAX_STEPS:
+            raise ValueError(f"at most {MAX_STEPS} sampler steps")
+        rows = step_rows.clone()
+        rows[:, N.ST_GUIDANCE] = float(guidance_scale)
+        self.table[:n].copy_(rows, non_blocking=True)
+        self.counter.zero_()
+        if self.hist is not None:
+            self.hist.zero_()
+        self.latents.copy_(latents)
+        if self.split:  # rank 0 of a pair holds the uncond half, rank 1 the cond half ([negative; positive] order, :438)
+            half = prompt_embeds.shape[0] // 2
+            prompt_embeds = prompt_embeds[self.pair_rank * half:(self.pair_rank + 1) * half]
+            if text_embeds is not None:
+                text_embeds = text_embeds[self.pair_rank * half:(self.pair_rank + 1) * half]
+                time_ids = time_ids[self.pair_rank * half:(self.pair_rank + 1) * half]
+        self.ctx.copy_(prompt_embeds)
+        if text_embeds is not None:
+            self.text_embeds.copy_(text_embeds)
+            self.time_ids.copy_(time_ids)
+        self.n_steps = n
+
+    def run(self, n_steps: Optional[int] = None):
+        """Launches prep + n step graphs on the engine's stream (ordered after the caller's current stream)."""
+        n = self.n_steps if n_steps is None else n_steps
+        s = self._stream
+        s.wait_stream(torch.cuda.current_stream(self.device))
+        with torch.cuda.stream(s):
+            self.prep.prog.run(s.cuda_stream)
+            if self.use_graph and not self._captured:
+                self.b.prog.graph_capture(s.cuda_stream)
+                if self.tail is not None:
+                    self.tail.prog.graph_capture(s.cuda_stream)
+                self._captured = True
+            for _ in range(n):
+                self.step_once(s)
+        torch.cuda.current_stream(self.device).wait_stream(s)
+        return self.latents
+
+    def step_once(self, s):
+        if self.use_graph:
+            self.b.prog.graph_launch(s.cuda_stream)
+        else:
+            self.b.prog.run(s.cuda_stream)
+        if self.tail is not None:
+            import torch.distributed as dist
+
+            B = self.B
+            half = self.eps_full.view(2, B, *self.eps_full.shape[1:])
+            # one exchange per step: message = B*4*h*w*2 bytes
+            dist.all_gather_into_tensor(self.eps_full, self.eps_local.contiguous(), group=self.pair_group)
+            del half
+            if self.use_graph:
+                self.tail.prog.graph_launch(s.cuda_stream)
+            else:
+                self.tail.prog.run(s.cuda_stream)
+
+    def run_unet_timed(self):
+        """Per-op device times of one step program (profiling aid; leaves latents/counter advanced by one step)."""
+        s = self._stream
+        with torch.cuda.stream(s):
+            return self.b.prog.run_timed(s.cuda_stream)

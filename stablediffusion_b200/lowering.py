@@ -307,7 +307,8 @@ class Builder:
         self.prog.add(N.OP_PHASE_SPLIT, p, self.tag, (x, out))
         return out
 
-    def cfg_step(self, eps, x, x_out, step_table, step_counter, guidance_scale, cfg, nsteps, x0_prev=None, next_in=None, rep=2):
+    def cfg_step(self, eps, x, x_out, step_table, step_counter, guidance_scale, cfg, nsteps, x0_prev=None, next_in=None, rep=2,
+                 gs_from_table=False):
         B, Cc, h, w = x.shape
         p = N.CfgStep()
         p.eps, p.ld_eps = eps.data_ptr(), eps.shape[-1]
@@ -316,7 +317,7 @@ class Builder:
         p.guidance_scale, p.cfg, p.x_dtype = float(guidance_scale), int(bool(cfg)), dtype_code(x)
         p.B, p.C, p.hw = B, Cc, h * w
         p.Cpad = next_in.shape[-1] if next_in is not None else 0
-        p.rep, p.nsteps = rep, nsteps
+        p.rep, p.nsteps, p.gs_from_table = rep, nsteps, int(bool(gs_from_table))
         self.prog.add(N.OP_CFG_STEP, p, self.tag, (eps, x, x_out, step_table, step_counter, x0_prev, next_in))
         return x_out
 

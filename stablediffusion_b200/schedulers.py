@@ -1,0 +1,376 @@
+"""B200 schedulers: the replacement for `model.scheduler` on the reference's hot path
+(scale_model_input pipelines/sd_unified_pipeline.py:472, step :489, add_noise :502,841,890, set_timesteps via
+retrieve_timesteps :61-95; classes selected in models/stable_diffusion.py:135-138,199-227).
+
+Host side: the timestep / sigma tables are built with the same numpy expressions diffusers 0.27.2 uses, so
+integer timesteps are exact and float tables are bit-identical.  Every per-step scalar is
+folded into one row of a device "step table"
+    [t, in_scale, K1, K2, CX, CE, C0, C1]:   x0 = (x - K1*eps)*K2 ;  x' = CX*x + CE*eps + C0*x0 + C1*(x0 - x0_prev)
+which the fused CFG+step kernel (libb200sd OP_CFG_STEP) indexes with a device-side step counter — so one
+captured CUDA graph serves every sampler step.  The coefficient scalars are computed in torch fp32 in
+diffusers' operation order.
+
+Device side: `scale_model_input`, `step` and `add_noise` called the reference's way (un-fused, one call per
+step) run the same kernels through a tiny per-shape op program.
+"""
+from __future__ import annotations
+
+import math
+from typing import Dict, Optional
+
+import numpy as np
+import torch
+
+from . import _native as N
+from . import lowering as L
+from .config import Config, scheduler_config
+
+
+def _betas(cfg) -> torch.Tensor:
+    n = cfg["num_train_timesteps"]
+    if cfg.get("trained_betas") is not None:
+        return torch.tensor(cfg["trained_betas"], dtype=torch.float32)
+    sched = cfg.get("beta_schedule", "linear")
+    if sched == "scaled_linear":
+        return torch.linspace(cfg["beta_start"] ** 0.5, cfg["beta_end"] ** 0.5, n, dtype=torch.float32) ** 2
+    if sched == "linear":
+        return torch.linspace(cfg["beta_start"], cfg["beta_end"], n, dtype=torch.float32)
+    raise ValueError(f"{sched} is not implemented")
+
+
+class _SchedulerBase:
+    order = 1
+    _class_defaults: dict = {}
+
+    def __init__(self, **config):
+        c = scheduler_config()
+        c.update(self._class_defaults)
+        explicit = {k: v for k, v in config.items() if k != "_use_default_values"}
+        c.update(explicit)
+        # like diffusers' ConfigMixin: remember which entries are class defaults so that from_config() on ANOTHER
+        # scheduler class lets that class's own defaults win for them
+        c["_use_default_values"] = sorted(set(c) - set(explicit))
+        self.config = c
+        self.betas = _betas(c)
+        self.alphas = 1.0 - self.betas
+        self.alphas_cumprod = torch.cumprod(self.alphas, dim=0)
+        self.timesteps: Optional[torch.Tensor] = None   # on the device given to set_timesteps
+        self._timesteps_host: Optional[np.ndarray] = None
+        self.num_inference_steps: Optional[int] = None
+        self._step_index: Optional[int] = None
+        self._table: Optional[torch.Tensor] = None       # host fp32 [n, STEP_ROW]
+        self._dev: Dict[str, torch.Tensor] = {}
+        self._programs: Dict[tuple, dict] = {}
+        self.device = torch.device("cpu")
+
+    @classmethod
+    def from_config(cls, config, **kwargs):
+        """`XScheduler.from_config(self.scheduler.config)` (models/stable_diffusion.py:203-222): keys the class
+        does not know are ignored, class defaults fill the rest."""
+        dropped = set(config.get("_use_default_values", ())) | {"_use_default_values"}
+        c = {k: v for k, v in dict(config).items() if k not in dropped}
+        c.update(kwargs)
+        return cls(**c)
+
+    # ---- step-table plumbing -----------------------------------------------------------------------
+    def _finish_set_timesteps(self, device):
+        self.device = torch.device(device) if device is not None else torch.device("cpu")
+        self._step_index = None
+        self._dev.clear()
+        self._programs.clear()
+        self._table = self._build_table()
+
+    def step_table(self, device, start_index: int = 0) -> torch.Tensor:
+        """Device copy of the table rows [start_index:], plus the step counter (int32[1])."""
+        key = f"table{start_index}@{device}"
+        if key not in self._dev:
+            self._dev[key] = self._table[start_index:].contiguous().to(device)
+        return self._dev[key]
+
+    @property
+    def step_index(self):
+        return self._step_index
+
+    def index_for_timestep(self, timestep) -> int:
+        t = float(timestep)
+        idx = np.nonzero(self._timesteps_host.astype(np.float64) == t)[0]
+        if len(idx) == 0:
+            raise ValueError(f"timestep {t} is not in the schedule")
+        return int(idx[1] if len(idx) > 1 else idx[0])
+
+    def _init_step_index(self, timestep):
+        if self._step_index is None:
+            self._step_index = self.index_for_timestep(timestep)
+
+    # ---- un-fused device calls (the reference's call pattern) ----------------------------------------
+    def _elementwise(self, x, a, y=None, bcoef=0.0):
+        """out = a*x + b*y via the library's AXPBY kernel (shape-cached one-op program)."""
+        if x.device.type != "cuda":
+            raise RuntimeError("B200 schedulers operate on CUDA tensors only (no CPU path)")
+        x = x.contiguous()
+        b = L.Builder(x.device, workspace_bytes=16)
+        out = b.axpby(x, a, y=None if y is None else y.contiguous().to(x.dtype), b=bcoef)
+        b.prog.run(torch.cuda.current_stream(x.device).cuda_stream)
+        torch.cuda.current_stream(x.device).synchronize()
+        return out
+
+    def scale_model_input(self, sample, timestep=None):
+        return sample
+
+    def step(self, model_output, timestep, sample, return_dict=False, **unused):
+        """x_{t-1} from (already CFG-combined) eps — the un-fused call at pipeline :489."""
+        self._init_step_index(timestep)
+        dev = sample.device
+        if dev.type != "cuda":
+            raise RuntimeError("B200 schedulers operate on CUDA tensors only (no CPU path)")
+        B, C, h, w = sample.shape
+        key = ("step", B, C, h, w, sample.dtype, model_output.dtype)
+        st = self._programs.get(key)
+        if st is None:
+            b = L.Builder(dev, workspace_bytes=16)
+            st = dict(b=b)
+            st["eps_nchw"] = b.empty([B, C, h, w], model_output.dtype)
+            st["eps"] = b.empty([B, h * w, 8])
+            b.prep_latents(st["eps_nchw"], st["eps"], rep=1, fixed_scale=1.0)  # NCHW -> token-major bf16
+            st["x"] = b.empty([B, C, h, w], torch.float32)
+            st["counter"] = b.zeros([1], torch.int32)
+            st["hist"] = b.zeros([B, C, h * w], torch.float32) if self._uses_history else None
+            b.cfg_step(st["eps"], st["x"], st["x"], self.step_table(dev), st["counter"], 1.0, False,
+                       len(self._table), x0_prev=st["hist"])
+            self._programs[key] = st
+        st["eps_nchw"].copy_(model_output)
+        st["x"].copy_(sample)
+        st["counter"].fill_(self._step_index)
+        st["b"].prog.run(torch.cuda.current_stream(dev).cuda_stream)
+        self._step_index += 1
+        # diffusers casts the result to the model-output dtype; we return the sample's dtype when
+        # it is wider (fp32 latents are strictly more accurate) and the model dtype otherwise.
+        out_dtype = sample.dtype if sample.dtype == torch.float32 else model_output.dtype
+        prev = st["x"].to(out_dtype)
+        return (prev,)
+
+    _uses_history = False
+
+
+class B200EulerDiscreteScheduler(_SchedulerBase):
+    """EulerDiscreteScheduler (name `euler`, the default: models/stable_diffusion.py:100,135)."""
+    _class_defaults = dict(timestep_spacing="linspace", interpolation_type="linear", use_karras_sigmas=False,
+                           timestep_type="discrete", steps_offset=0)
+
+    def __init__(self, **config):
+        super().__init__(**config)
+        sig = ((1 - self.alphas_cumprod) / self.alphas_cumprod) ** 0.5
+        self.sigmas = torch.cat([sig.flip(0), torch.zeros(1)])
+
+    @property
+    def init_noise_sigma(self):
+        m = self.sigmas.max()
+        if self.config["timestep_spacing"] in ("linspace", "trailing"):
+            return m
+        return (m ** 2 + 1) ** 0.5
+
+    def set_timesteps(self, num_inference_steps, device=None):
+        c = self.config
+        ntrain = c["num_train_timesteps"]
+        n = self.num_inference_steps = int(num_inference_steps)
+        sp = c["timestep_spacing"]
+        if sp == "linspace":
+            ts = np.linspace(0, ntrain - 1, n, dtype=np.float32)[::-1].copy()
+        elif sp == "leading":
+            ts = (np.arange(0, n) * (ntrain // n)).round()[::-1].copy().astype(np.float32)
+            ts += c["steps_offset"]
+        elif sp == "trailing":
+            ts = (np.arange(ntrain, 0, -ntrain / n)).round().copy().astype(np.float32)
+            ts -= 1
+        else:
+            raise ValueError(f"{sp} is not supported")
+        sig = np.array(((1 - self.alphas_cumprod) / self.alphas_cumprod) ** 0.5)
+        sig = np.interp(ts, np.arange(0, len(sig)), sig)
+        sig = torch.from_numpy(sig).to(dtype=torch.float32)
+        self._timesteps_host = ts.astype(np.float32)
+        self.sigmas = torch.cat([sig, torch.zeros(1)])
+        self._finish_set_timesteps(device)
+        self.timesteps = torch.from_numpy(self._timesteps_host).to(self.device)
+
+    def _build_table(self):
+        n = self.num_inference_steps
+        tab = torch.zeros(n, N.STEP_ROW, dtype=torch.float32)
+        for i in range(n):
+            s, s_next = self.sigmas[i], self.sigmas[i + 1]
+            tab[i, N.ST_TIMESTEP] = float(self._timesteps_host[i])
+            tab[i, N.ST_IN_SCALE] = 1.0 / ((s ** 2 + 1) ** 0.5)
+            # x0 = x - s*eps ; d = (x - x0)/s ; x' = x + d*(s_next - s)  ==  x + eps*dt up to fp32 rounding
+            tab[i, N.ST_K1], tab[i, N.ST_K2] = s, 1.0
+            tab[i, N.ST_CX], tab[i, N.ST_CE] = 1.0, s_next - s
+        return tab
+
+    def scale_model_input(self, sample, timestep=None):
+        self._init_step_index(timestep)
+        s = self.sigmas[self._step_index]
+        return self._elementwise(sample, float(1.0 / ((s ** 2 + 1) ** 0.5)))
+
+    def add_noise(self, original_samples, noise, timesteps):
+        idx = [self.index_for_timestep(t) for t in timesteps.reshape(-1).tolist()]
+        if len(set(idx)) != 1:
+            raise ValueError("add_noise: per-sample timesteps must be equal on this path")
+        return self._elementwise(original_samples, 1.0, noise, float(self.sigmas[idx[0]]))
+
+
+class B200DDIMScheduler(_SchedulerBase):
+    """DDIMScheduler (name `DDIM`, BASELINE config 2), eta = 0."""
+    _class_defaults = dict(timestep_spacing="leading", clip_sample=True, set_alpha_to_one=True, steps_offset=0,
+                           thresholding=False)
+    init_noise_sigma = 1.0
+
+    def __init__(self, **config):
+        super().__init__(**config)
+        if self.config["clip_sample"] or self.config.get("thresholding"):
+            raise ValueError("clip_sample / thresholding DDIM is not part of the SD hot path (SD configs set clip_sample=False)")
+        self.final_alpha_cumprod = torch.tensor(1.0) if self.config["set_alpha_to_one"] else self.alphas_cumprod[0]
+
+    def set_timesteps(self, num_inference_steps, device=None):
+        c = self.config
+        ntrain = c["num_train_timesteps"]
+        n = self.num_inference_steps = int(num_inference_steps)
+        sp = c["timestep_spacing"]
+        if sp == "leading":
+            ts = (np.arange(0, n) * (ntrain // n)).round()[::-1].copy().astype(np.int64)
+            ts += c["steps_offset"]
+        elif sp == "linspace":
+            ts = np.linspace(0, ntrain - 1, n).round()[::-1].copy().astype(np.int64)
+        elif sp == "trailing":
+            ts = np.round(np.arange(ntrain, 0, -ntrain / n)).astype(np.int64)
+            ts -= 1
+        else:
+            raise ValueError(f"{sp} is not supported")
+        self._timesteps_host = ts
+        self._finish_set_timesteps(device)
+        self.timesteps = torch.from_numpy(ts).to(self.device)
+
+    def _build_table(self):
+        n = self.num_inference_steps
+        ntrain = self.config["num_train_timesteps"]
+        tab = torch.zeros(n, N.STEP_ROW, dtype=torch.float32)
+        for i in range(n):
+            t = int(self._timesteps_host[i])
+            prev_t = t - ntrain // n
+            a_t = self.alphas_cumprod[t]
+            a_p = self.alphas_cumprod[prev_t] if prev_t >= 0 else self.final_alpha_cumprod
+            tab[i, N.ST_TIMESTEP] = float(t)
+            tab[i, N.ST_IN_SCALE] = 1.0
+            tab[i, N.ST_K1] = (1 - a_t) ** 0.5          # x0 = (x - sqrt(1-a_t) eps) / sqrt(a_t)
+            tab[i, N.ST_K2] = 1.0 / (a_t ** 0.5)
+            tab[i, N.ST_CE] = (1 - a_p) ** 0.5          # x' = sqrt(a_p) x0 + sqrt(1-a_p) eps
+            tab[i, N.ST_C0] = a_p ** 0.5
+        return tab
+
+    def add_noise(self, original_samples, noise, timesteps):
+        ts = set(int(t) for t in timesteps.reshape(-1).tolist())
+        if len(ts) != 1:
+            raise ValueError("add_noise: per-sample timesteps must be equal on this path")
+        a = self.alphas_cumprod[ts.pop()]
+        return self._elementwise(original_samples, float(a ** 0.5), noise, float((1 - a) ** 0.5))
+
+
+class B200DPMSolverMultistepScheduler(_SchedulerBase):
+    """DPMSolverMultistepScheduler as `DPM++ 2M` / `DPM++ 2M Karras` (models/stable_diffusion.py:211-214):
+    dpmsolver++, order 2, midpoint, final sigma zero."""
+    _class_defaults = dict(timestep_spacing="linspace", algorithm_type="dpmsolver++", solver_order=2, solver_type="midpoint",
+                           lower_order_final=True, use_karras_sigmas=False, final_sigmas_type="zero", steps_offset=0)
+    init_noise_sigma = 1.0
+    _uses_history = True
+
+    def __init__(self, **config):
+        super().__init__(**config)
+        c = self.config
+        if c["algorithm_type"] != "dpmsolver++" or c["solver_order"] != 2 or c["solver_type"] != "midpoint":
+            raise ValueError("only dpmsolver++ / order 2 / midpoint (DPM++ 2M) is on the hot path; the SDE variant is a 'next' row")
+        if c["timestep_spacing"] != "linspace" or c["final_sigmas_type"] != "zero":
+            raise ValueError("DPM++ 2M: only linspace spacing with final sigma zero is supported")
+
+    @staticmethod
+    def _sigma_to_t(sigma, log_sigmas):
+        log_sigma = np.log(np.maximum(sigma, 1e-10))
+        dists = log_sigma - log_sigmas[:, np.newaxis]
+        low_idx = np.cumsum((dists >= 0), axis=0).argmax(axis=0).clip(max=log_sigmas.shape[0] - 2)
+        high_idx = low_idx + 1
+        low, high = log_sigmas[low_idx], log_sigmas[high_idx]
+        w = np.clip((low - log_sigma) / (low - high), 0, 1)
+        t = (1 - w) * low_idx + w * high_idx
+        return t.reshape(np.shape(sigma))
+
+    def set_timesteps(self, num_inference_steps, device=None):
+        c = self.config
+        ntrain = c["num_train_timesteps"]
+        n = self.num_inference_steps = int(num_inference_steps)
+        ts = np.linspace(0, ntrain - 1, n + 1).round()[::-1][:-1].copy().astype(np.int64)
+        sig = np.array(((1 - self.alphas_cumprod) / self.alphas_cumprod) ** 0.5)
+        log_sig = np.log(sig)
+        if c["use_karras_sigmas"]:
+            sflip = np.flip(sig).copy()
+            smin, smax = sflip[-1].item(), sflip[0].item()
+            rho = 7.0
+            ramp = np.linspace(0, 1, n)
+            sig = (smax ** (1 / rho) + ramp * (smin ** (1 / rho) - smax ** (1 / rho))) ** rho
+            ts = np.array([self._sigma_to_t(s, log_sig) for s in sig]).round()
+        else:
+            sig = np.interp(ts, np.arange(0, len(sig)), sig)
+        sig = np.concatenate([sig, [0.0]]).astype(np.float32)
+        self.sigmas = torch.from_numpy(sig)
+        self._timesteps_host = ts.astype(np.int64)
+        self._finish_set_timesteps(device)
+        self.timesteps = torch.from_numpy(self._timesteps_host).to(self.device)
+
+    @staticmethod
+    def _alpha_sigma(sigma):
+        alpha = 1 / ((sigma ** 2 + 1) ** 0.5)
+        return alpha, sigma * alpha
+
+    def _build_table(self):
+        n = self.num_inference_steps
+        tab = torch.zeros(n, N.STEP_ROW, dtype=torch.float32)
+        for i in range(n):
+            a_s, s_s = self._alpha_sigma(self.sigmas[i])
+            a_t, s_t = self._alpha_sigma(self.sigmas[i + 1])
+            lam_t = torch.log(a_t) - torch.log(s_t)
+            lam_s = torch.log(a_s) - torch.log(s_s)
+            h = lam_t - lam_s
+            coef = a_t * (torch.exp(-h) - 1.0)
+            tab[i, N.ST_TIMESTEP] = float(self._timesteps_host[i])
+            tab[i, N.ST_IN_SCALE] = 1.0
+            tab[i, N.ST_K1], tab[i, N.ST_K2] = s_s, 1.0 / a_s       # x0 = (x - sigma_hat*eps)/alpha
+            tab[i, N.ST_CX] = s_t / s_s
+            tab[i, N.ST_C0] = -coef
+            first_order = (i == 0) or (i == n - 1)                  # lower_order_nums < 1, or final step (sigma -> 0)
+            if not first_order:
+                a_s1, s_s1 = self._alpha_sigma(self.sigmas[i - 1])
+                lam_s1 = torch.log(a_s1) - torch.log(s_s1)
+                r0 = (lam_s - lam_s1) / h
+                tab[i, N.ST_C1] = -0.5 * coef * (1.0 / r0)
+        return tab
+
+    def add_noise(self, original_samples, noise, timesteps):
+        idx = [self.index_for_timestep(t) for t in timesteps.reshape(-1).tolist()]
+        if len(set(idx)) != 1:
+            raise ValueError("add_noise: per-sample timesteps must be equal on this path")
+        a, s = self._alpha_sigma(self.sigmas[idx[0]])
+        return self._elementwise(original_samples, float(a), noise, float(s))
+
+
+SCHEDULER_CLASSES = {
+    "euler": (B200EulerDiscreteScheduler, {}),
+    "DDIM": (B200DDIMScheduler, {}),
+    "DPM++ 2M": (B200DPMSolverMultistepScheduler, {}),
+    "DPM++ 2M Karras": (B200DPMSolverMultistepScheduler, dict(use_karras_sigmas=True)),
+}
+# names the reference accepts (models/stable_diffusion.py:205-222) that are not on the hot path yet
+NEXT_ROW_SCHEDULERS = ("euler_a", "DPM++ 2M SDE Karras", "PNDM", "uni_pc")
+
+
+def make_scheduler(name: str, config) -> _SchedulerBase:
+    if name in SCHEDULER_CLASSES:
+        cls, extra = SCHEDULER_CLASSES[name]
+        return cls.from_config(config, **extra)
+    if name in NEXT_ROW_SCHEDULERS:
+        raise ValueError(f"scheduler '{name}' has no B200 kernel yet (no CPU fallback is provided)")
+    raise ValueError(f"Unknown scheduler name: {name}")
