@@ -1,0 +1,251 @@
+"""`SDModelWrapper` with the public surface of the reference's models/stable_diffusion.py:40-335, but whose
+`.base`, `.vae` and `.scheduler` are the B200-native objects (B200UNet / B200VAE / B200*Scheduler).
+
+Loading (reference :106-156 `load_hf_checkpoint`): an HF-layout folder — `unet/`, `vae/`, `text_encoder/`,
+`tokenizer/`, `scheduler/` (+ `text_encoder_2/`, `tokenizer_2/` for SDXL) — with fp16-variant safetensors
+(`diffusion_pytorch_model.fp16.safetensors`), i.e. exactly what scripts/convert_from_A1111.py:1381-1386 writes.
+Weights are converted to bf16 and re-laid-out for the kernels at load.  There is no network in this build:
+hub ids (`OnMoon/...`, `runwayml/...`) must already be local folders, otherwise loading raises.
+Text encoders / tokenizers stay torch + transformers objects: they are outside the hot path.
+"""
+from __future__ import annotations
+
+import os
+from typing import Dict, List, Optional, Union
+
+import torch
+
+from ..config import UNET_DEFAULTS, VAE_DEFAULTS, Config, load_json_config, scheduler_config, unet_config, vae_config
+from ..lora import parse_lora_state_dict
+from ..random_init import random_state_dict
+from ..schedulers import B200EulerDiscreteScheduler, make_scheduler
+from ..unet import B200UNet, unet_param_shapes
+from ..vae import B200VAE, vae_param_shapes
+
+
+def _load_safetensors(folder: str, stem: str) -> Dict[str, torch.Tensor]:
+    from safetensors.torch import load_file
+
+    for name in (f"{stem}.fp16.safetensors", f"{stem}.safetensors"):
+        p = os.path.join(folder, name)
+        if os.path.exists(p):
+            return load_file(p)
+    raise FileNotFoundError(f"no {stem}[.fp16].safetensors under {folder}")
+
+
+def _resolve_local(ckpt_path: str) -> str:
+    if os.path.isdir(ckpt_path):
+        return ckpt_path
+    raise FileNotFoundError(
+        f"checkpoint '{ckpt_path}' is not a local folder; this build has no network access to the HF hub "
+        "(models/stable_diffusion.py:110-152 would download it)")
+
+
+class _ImageProcessor:
+    """The part of diffusers' VaeImageProcessor the pipeline uses (`preprocess`, pipeline :238): tensors or PIL images
+    -> float tensor (B,3,H,W) in [-1,1], H and W rounded down to a multiple of the VAE scale factor."""
+
+    def __init__(self, vae_scale_factor: int, do_normalize: bool = True):
+        self.f = vae_scale_factor
+        self.do_normalize = do_normalize
+
+    def preprocess(self, image, height=None, width=None, **unused):
+        import numpy as np
+
+        if isinstance(image, torch.Tensor):
+            x = image if image.dim() == 4 else image[None]
+            return x  # tensors are taken as already in [-1, 1] (diffusers does the same for tensor input in [-1,1])
+        imgs = image if isinstance(image, list) else [image]
+        arrs = []
+        for im in imgs:
+            w, h = im.size
+            w, h = (width or w) // self.f * self.f, (height or h) // self.f * self.f
+            im = im.convert("RGB").resize((w, h))
+            arrs.append(np.asarray(im, dtype=np.float32) / 255.0)
+        x = torch.from_numpy(np.stack(arrs)).permute(0, 3, 1, 2)
+        return 2.0 * x - 1.0 if self.do_normalize else x
+
+
+class SDModelWrapper:
+    def __init__(self, ckpt_path: Optional[str] = None, vae=None, base=None, text_encoder=None, tokenizer=None,
+                 scheduler=None, text_encoder_2=None, tokenizer_2=None, refiner=None, model_name: Optional[str] = None,
+                 model_type: Optional[str] = None, device: str = "cuda"):
+        """Same argument list as the reference (:41-55).  Components passed explicitly are used as they are;
+        everything else is loaded from `ckpt_path` (default names as in the reference :79-88)."""
+        self.type = model_type or "sd15"
+        if self.type == "sd15":
+            for a in ("text_encoder_2", "tokenizer_2"):
+                if hasattr(self, a):
+                    delattr(self, a)
+        else:
+            self.text_encoder_2 = text_encoder_2
+            self.tokenizer_2 = tokenizer_2
+        if model_name is not None and isinstance(model_name, str):
+            ckpt_path = f"OnMoon/{self.type}_{model_name}"
+        if ckpt_path is None and base is None:
+            ckpt_path = "stabilityai/stable-diffusion-xl-base-1.0" if self.type == "sdxl" else "runwayml/stable-diffusion-v1-5"
+        self.vae, self.base, self.text_encoder, self.tokenizer, self.scheduler = vae, base, text_encoder, tokenizer, scheduler
+        if refiner is not None:
+            self.refiner = refiner
+        if base is None:
+            self.load_hf_checkpoint(ckpt_path)
+        if self.scheduler is None:
+            self.scheduler = B200EulerDiscreteScheduler(**scheduler_config(self.type))
+        self.device = torch.device("cpu")
+        self.to(device)
+        self.vae_scale_factor = 2 ** (len(self.vae.config.block_out_channels) - 1)
+        self.lora_loader = None  # diffusers' LoraLoaderMixin is replaced by stablediffusion_b200.lora (merge at load)
+        self.image_processor = _ImageProcessor(self.vae_scale_factor)
+        self.mask_processor = _ImageProcessor(self.vae_scale_factor, do_normalize=False)
+        self.scheduler_name = "euler"
+        self.name = model_name or None
+        self.path = ckpt_path
+
+    # ---- construction without a checkpoint (benchmarks / tests: random-init weights of the named architecture) ----
+    @classmethod
+    def from_random(cls, model_type: str = "sd15", seed: int = 0, device: str = "cuda", unet_overrides=None,
+                    vae_overrides=None, with_vae_encoder: bool = False):
+        ucfg = unet_config(model_type, **(unet_overrides or {}))
+        vcfg = vae_config(model_type, **(vae_overrides or {}))
+        usd = random_state_dict(unet_param_shapes(ucfg), seed=seed)
+        vsd = random_state_dict(vae_param_shapes(vcfg, decoder=True, encoder=with_vae_encoder), seed=seed + 1)
+        base = B200UNet(ucfg, usd, device=device)
+        vae = B200VAE(vcfg, vsd, device=device)
+        sched = B200EulerDiscreteScheduler(**scheduler_config(model_type))
+        return cls(vae=vae, base=base, scheduler=sched, model_type=model_type, device=device)
+
+    def load_hf_checkpoint(self, ckpt_path):
+        if hasattr(self, "path") and self.path == ckpt_path:
+            return
+        root = _resolve_local(ckpt_path)
+        vcfg = load_json_config(os.path.join(root, "vae"), VAE_DEFAULTS)
+        self.vae = B200VAE(vcfg, _load_safetensors(os.path.join(root, "vae"), "diffusion_pytorch_model"), device="cpu")
+        ucfg = load_json_config(os.path.join(root, "unet"), UNET_DEFAULTS)
+        self.base = B200UNet(ucfg, _load_safetensors(os.path.join(root, "unet"), "diffusion_pytorch_model"), device="cpu")
+        from transformers import CLIPTextModel, CLIPTextModelWithProjection, CLIPTokenizer
+
+        self.text_encoder = CLIPTextModel.from_pretrained(root, subfolder="text_encoder", torch_dtype=torch.bfloat16)
+        self.tokenizer = CLIPTokenizer.from_pretrained(root, subfolder="tokenizer")
+        scfg = load_json_config(os.path.join(root, "scheduler"), {}, "scheduler_config.json")
+        self.scheduler = B200EulerDiscreteScheduler(**scfg)
+        if hasattr(self, "text_encoder_2"):
+            self.text_encoder_2 = CLIPTextModelWithProjection.from_pretrained(root, subfolder="text_encoder_2", torch_dtype=torch.bfloat16)
+            self.tokenizer_2 = CLIPTokenizer.from_pretrained(root, subfolder="tokenizer_2")
+        self.path = ckpt_path
+        print(f"StableDiffusion model successfully loaded from '{ckpt_path}' checkpoint")
+
+    def reload(self, ckpt_path=None, model_name=None, model_type=None):
+        self.__init__(ckpt_path=ckpt_path, model_name=model_name, model_type=model_type, device=self.device)
+
+    def to(self, device):
+        self.vae.to(device)
+        self.base.to(device)
+        if self.text_encoder is not None:
+            self.text_encoder.to(device)
+        if getattr(self, "text_encoder_2", None) is not None:
+            self.text_encoder_2.to(device)
+        self.device = torch.device(device)
+
+    def set_scheduler(self, scheduler_name):
+        if hasattr(self, "scheduler_name") and self.scheduler_name == scheduler_name:
+            return
+        self.scheduler = make_scheduler(scheduler_name, self.scheduler.config)  # raises ValueError on unknown names (:224)
+        self.scheduler_name = scheduler_name
+        print(f"Scheduler has successfully changed to '{scheduler_name}'")
+
+    # ---- LoRA (reference :230-335).  Adapters are merged into the packed weights, not run as extra GEMMs. ----
+    def load_loras(self, loras, lora_dir: Optional[str] = None):
+        if isinstance(loras, str):
+            loras = {loras: 1.0}
+        elif isinstance(loras, list):
+            loras = {name: 1.0 for name in loras}
+        current = [] if self.get_list_adapters() == {} else self.get_list_adapters()["base"]
+        self.delete_adapters(current)
+        for lora_name in list(loras.keys()):
+            fname = f"{self.type}_{lora_name}.safetensors"  # hub naming of the reference (:242-245), resolved locally
+            path = os.path.join(lora_dir or os.environ.get("B200SD_LORA_DIR", "."), fname)
+            if not os.path.exists(path):
+                raise FileNotFoundError(f"LoRA file {path} not found (no network: 'OnMoon/loras' cannot be downloaded)")
+            self.load_lora_weights(path, adapter_name=lora_name)
+        print(f"LoRA adapters has successfully changed to:\n{loras}")
+        self.set_adapters(list(loras.keys()), list(loras.values()))
+
+    def load_lora_weights(self, pretrained_model_name_or_path_or_dict: Union[str, Dict[str, torch.Tensor]],
+                          adapter_name: Optional[str] = None, **kwargs):
+        if isinstance(pretrained_model_name_or_path_or_dict, dict):
+            sd = pretrained_model_name_or_path_or_dict
+        else:
+            from safetensors.torch import load_file
+
+            p = pretrained_model_name_or_path_or_dict
+            if os.path.isdir(p):
+                p = os.path.join(p, "pytorch_lora_weights.safetensors")  # train_lora_pipeline.py:497-528 output name
+            sd = load_file(p)
+        modules = sorted({k.rsplit(".", 1)[0] for k in unet_param_shapes(self.base.config) if k.endswith(".weight")})
+        parsed = parse_lora_state_dict(sd, unet_modules=modules)  # raises ValueError("Invalid LoRA checkpoint.") (:264-266)
+        adapter_name = adapter_name or f"default_{len(self.base.peft_config)}"
+        self.base.add_lora(adapter_name, parsed["unet"])
+        for part, enc_name in (("text_encoder", "text_encoder"), ("text_encoder_2", "text_encoder_2")):
+            enc = getattr(self, enc_name, None)
+            if parsed[part] and enc is not None:
+                self._merge_text_encoder_lora(enc, parsed[part], adapter_name)
+
+    def _merge_text_encoder_lora(self, enc, layers, adapter_name):
+        """Text-encoder LoRA (outside the hot path): kept as (module, delta) pairs and applied to the torch weights."""
+        store = enc.__dict__.setdefault("_b200_lora", {})
+        mods = dict(enc.named_modules())
+        from ..lora import lora_delta
+
+        ent = []
+        for path, e in layers.items():
+            path = path.replace("lora_te_", "").replace("lora_te1_", "").replace("lora_te2_", "")
+            m = mods.get(path) or mods.get(path.replace("_", "."))
+            if m is None:
+                continue
+            ent.append((m, lora_delta(e)))
+        store[adapter_name] = dict(layers=ent, weight=0.0)
+        enc.peft_config = {k: True for k in store}
+
+    def _apply_text_encoder_weights(self, enc, names, weights):
+        store = getattr(enc, "_b200_lora", None)
+        if not store:
+            return
+        want = {n: (1.0 if w is None else float(w)) for n, w in zip(names, weights)}
+        for name, st in store.items():
+            new_w = want.get(name, 0.0)
+            if new_w != st["weight"]:
+                for m, delta in st["layers"]:
+                    m.weight.data += ((new_w - st["weight"]) * delta).to(m.weight.device, m.weight.dtype)
+                st["weight"] = new_w
+
+    def set_adapters(self, adapter_names: Union[List[str], str], adapter_weights: Optional[List[float]] = None):
+        names = [adapter_names] if isinstance(adapter_names, str) else list(adapter_names)
+        weights = adapter_weights if adapter_weights is not None else [1.0] * len(names)
+        self.base.set_adapters(names, weights)
+        for enc_name in ("text_encoder", "text_encoder_2"):
+            enc = getattr(self, enc_name, None)
+            if enc is not None:
+                self._apply_text_encoder_weights(enc, names, weights)
+
+    def delete_adapters(self, adapter_names: Union[List[str], str]):
+        if isinstance(adapter_names, str):
+            adapter_names = [adapter_names]
+        self.base.delete_adapters(adapter_names)
+        for enc_name in ("text_encoder", "text_encoder_2"):
+            enc = getattr(self, enc_name, None)
+            store = getattr(enc, "_b200_lora", None) if enc is not None else None
+            if store:
+                self._apply_text_encoder_weights(enc, [], [])
+                for n in adapter_names:
+                    store.pop(n, None)
+                enc.peft_config = {k: True for k in store}
+
+    def get_list_adapters(self) -> Dict[str, List[str]]:
+        out = {}
+        if len(self.base.peft_config) > 0:
+            out["base"] = list(self.base.peft_config.keys())
+        for enc_name in ("text_encoder", "text_encoder_2"):
+            enc = getattr(self, enc_name, None)
+            if enc is not None and getattr(enc, "_b200_lora", None):
+                out[enc_name] = list(enc._b200_lora.keys())
+        return out
