@@ -82,7 +82,7 @@ class DenoiseEngine:
             tail = L.Builder(self.device, workspace_bytes=16)
             self._emit_tail(tail, self.eps_full)
             self.tail = tail
-        self.unet_flops = b.flops
+        self.unet_flops, self.gemm_flops, self.attn_flops = b.flops, b.gemm_flops, b.attn_flops
         self._captured = False
         self._stream = torch.cuda.Stream(self.device)
 
@@ -103,6 +103,7 @@ class DenoiseEngine:
             raise ValueError(f"at most {MAX_STEPS} sampler steps")
         rows = step_rows.clone()
         rows[:, N.ST_GUIDANCE] = float(guidance_scale)
+        rows[0, N.ST_C1] = 0.0  # a multistep solver has no history on the first executed step (img2img starts mid-table)
         self.table[:n].copy_(rows, non_blocking=True)
         self.counter.zero_()
         if self.hist is not None:

@@ -59,8 +59,13 @@ class Builder:
         self._ws = torch.empty(workspace_bytes, dtype=torch.uint8, device=self.device)
         self._gn_ws = torch.empty(1 << 20, dtype=torch.uint8, device=self.device)
         self.prog.keep(self._ws, self._gn_ws)
-        self.flops = 0  # algorithmic 2*MAC of the GEMM/attention ops added (no padding)
+        self.gemm_flops = 0  # algorithmic 2*MAC of the GEMM ops added
+        self.attn_flops = 0  # algorithmic 4*B*heads*Nq*Nkv*d of the attention ops added
         self.tag = 0
+
+    @property
+    def flops(self):
+        return self.gemm_flops + self.attn_flops
 
     # ---- memory -------------------------------------------------------------------------------------
     def empty(self, shape: Sequence[int], dtype=torch.bfloat16) -> torch.Tensor:
@@ -146,7 +151,7 @@ class Builder:
                 raise ValueError("linear: residual shape mismatch")
         self._epilogue(g, bias, rowvec, residual, ldr, silu, geglu, out_f32, bias_row, alpha, rows_per_group)
         self._finish_gemm(g, (a, w, out, bias, residual, rowvec, a2))
-        self.flops += 2 * M * Nn * (K + K2)
+        self.gemm_flops += 2 * M * Nn * (K + K2)
         return out
 
     def conv(self, x, w, out=None, taps=TAPS_3X3_S1, phases=1, out_hw=None, bias=None, rowvec=None, residual=None,
@@ -203,7 +208,7 @@ class Builder:
         ldr = residual.shape[-1] if residual is not None else 0
         self._epilogue(g, bias, rowvec, residual, ldr, silu, False, False, False, 1.0, 0)
         self._finish_gemm(g, (x, w, out, bias, residual, rowvec) + tuple(extra or ()))
-        self.flops += 2 * NB * H * W * Cout * ktot
+        self.gemm_flops += 2 * NB * H * W * Cout * ktot
         return out
 
     # ---- normalisation ------------------------------------------------------------------------------
@@ -252,7 +257,7 @@ class Builder:
         p.ldq, p.ldk, p.ldv, p.ldo = q.stride(1), k.stride(1), v.stride(1), out.stride(1)
         p.B, p.heads, p.Nq, p.Nkv, p.d, p.scale = B, heads, Nq, Nkv, d, float(scale)
         self.prog.add(N.OP_ATTENTION, p, self.tag, (q, k, v, out))
-        self.flops += 4 * B * heads * Nq * Nkv * d
+        self.attn_flops += 4 * B * heads * Nq * Nkv * d
         return out
 
     def softmax_rows(self, x, scale, out=None):

@@ -311,8 +311,8 @@ class B200VAE:
             self.packed = PackedVAE(self.config, self._master, self.device)
         return self
 
-    def _decode_program(self, NB, h, w, in_dtype):
-        key = ("dec", NB, h, w, in_dtype)
+    def _decode_program(self, NB, h, w, in_dtype, scale=1.0):
+        key = ("dec", NB, h, w, in_dtype, float(scale))
         if key in self._programs:
             return self._programs[key]
         b = L.Builder(self.device)
@@ -320,7 +320,7 @@ class B200VAE:
         st = dict(b=b)
         st["z"] = b.empty([NB, lc, h, w], in_dtype)
         z_in = b.empty([NB, h * w, _pad8(lc)])
-        b.prep_latents(st["z"], z_in, rep=1, fixed_scale=1.0)
+        b.prep_latents(st["z"], z_in, rep=1, fixed_scale=float(scale))
         img = VAELowering(b, self.packed).decode(z_in, NB, h, w)
         co = self.config["out_channels"]
         st["out"] = b.empty([NB, co, 8 * h, 8 * w], in_dtype)
@@ -329,11 +329,12 @@ class B200VAE:
         return st
 
     @torch.no_grad()
-    def decode(self, z, return_dict=False, **unused):
+    def decode(self, z, return_dict=False, scale: float = 1.0, **unused):
+        """`scale` multiplies z first (the pipeline passes 1/scaling_factor so the un-scale of reference :521 is fused)."""
         if self.packed is None:
             raise RuntimeError("B200VAE has no weights on a CUDA device")
         NB, _, h, w = z.shape
-        st = self._decode_program(NB, h, w, z.dtype)
+        st = self._decode_program(NB, h, w, z.dtype, scale)
         st["z"].copy_(z)
         st["b"].prog.run(torch.cuda.current_stream(self.device).cuda_stream)
         return (st["out"].clone(),)

@@ -101,3 +101,154 @@ def test_unet_sd15_768_vs_oracle(cuda_device):
 def test_unet_sdxl_vs_oracle(cuda_device):
     cfg, ours, oracle = _make_unet(cuda_device, "sdxl")
     _unet_case(cuda_device, cfg, ours, oracle, 2, 64, 64, 958.0, oracle_on_gpu=True)
+
+
+# ---------------------------------------------------------------------------------------------------
+# VAE, fused loop, full pipeline
+# ---------------------------------------------------------------------------------------------------
+def _psnr(a, b, peak=2.0):
+    mse = (a.float() - b.float()).pow(2).mean().item()
+    return 10.0 * math.log10(peak * peak / max(mse, 1e-20))
+
+
+def _make_vae(dev, seed=5, encoder=False):
+    from oracle.vae import AutoencoderKLOracle
+    from stablediffusion_b200.config import vae_config
+    from stablediffusion_b200.random_init import random_state_dict
+    from stablediffusion_b200.vae import B200VAE, vae_param_shapes
+
+    cfg = vae_config()
+    sd = _bf16_round_sd(random_state_dict(vae_param_shapes(cfg, True, True), seed=seed))
+    oracle = AutoencoderKLOracle()
+    oracle.load_state_dict(sd, strict=True)
+    if not encoder:
+        sd = {k: v for k, v in sd.items() if not (k.startswith("encoder") or k.startswith("quant_conv"))}
+    return cfg, B200VAE(cfg, sd, device=dev), oracle.eval()
+
+
+@pytest.mark.parametrize("B,h,w", [(1, 32, 32), (2, 64, 64)])
+def test_vae_decode_vs_oracle(cuda_device, B, h, w):
+    dev = cuda_device
+    cfg, ours, oracle = _make_vae(dev)
+    z = torch.randn(B, 4, h, w, generator=torch.Generator().manual_seed(3))
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.backends.cudnn.allow_tf32 = False
+    with torch.no_grad():
+        ref = oracle.to(dev).decode(z.to(torch.bfloat16).float().to(dev) ).float().cpu()
+    out = ours.decode(z.to(dev), return_dict=False)[0].float().cpu()
+    assert out.shape == (B, 3, 8 * h, 8 * w)
+    rl2 = _rel_l2(out, ref)
+    psnr = _psnr(out, ref, peak=(ref.max() - ref.min()).item())
+    print(f"VAE PARITY {B}x{h}x{w}: rel-L2 {rl2:.4g} PSNR {psnr:.1f} dB")
+    assert rl2 <= 2e-2 and psnr >= 30.0
+
+
+def test_vae_encode_vs_oracle(cuda_device):
+    dev = cuda_device
+    cfg, ours, oracle = _make_vae(dev, encoder=True)
+    x = (torch.rand(1, 3, 256, 256, generator=torch.Generator().manual_seed(2)) * 2 - 1).to(torch.bfloat16).float()
+    with torch.no_grad():
+        ref = oracle.to(dev).encode(x.to(dev))
+    d = ours.encode(x.to(dev)).latent_dist
+    rl2 = _rel_l2(d.mean.cpu(), ref.mean.cpu())
+    print(f"VAE ENCODE PARITY: mean rel-L2 {rl2:.4g}, std rel-L2 {_rel_l2(d.std.cpu(), ref.std.cpu()):.4g}")
+    assert rl2 <= 2e-2
+
+
+@pytest.mark.parametrize("sched_name,steps", [("euler", 12), ("DDIM", 12), ("DPM++ 2M", 12), ("DPM++ 2M Karras", 8)])
+def test_fused_loop_vs_oracle(cuda_device, sched_name, steps):
+    """Whole trajectory: B200 fused loop (graph replay) vs the oracle's restatement of the reference loop."""
+    from oracle import pipeline as OP
+    from oracle import schedulers as OS
+    from stablediffusion_b200.models.stable_diffusion import SDModelWrapper
+    from stablediffusion_b200.pipelines.sd_unified_pipeline import StableDiffusionUnifiedPipeline
+    from stablediffusion_b200.vae import B200VAE
+
+    dev = cuda_device
+    cfg, ours, oracle = _make_unet(dev, **SMALL_UNET)
+    vcfg, vae, _ = _make_vae(dev)
+    model = SDModelWrapper(vae=vae, base=ours, device=str(dev))
+    model.set_scheduler(sched_name)
+    g = torch.Generator().manual_seed(21)
+    B = 2
+    lat = torch.randn(B, 4, 16, 16, generator=g)
+    pe = torch.randn(B, 77, 64, generator=g).to(torch.bfloat16)
+    ne = torch.randn(B, 77, 64, generator=g).to(torch.bfloat16)
+    pipe = StableDiffusionUnifiedPipeline(do_cfg=True, device=str(dev), output_type="latents")
+    out = pipe(model, prompt_embeds=pe.to(dev), negative_prompt_embeds=ne.to(dev), num_inference_steps=steps,
+               guidance_scale=7.5, latents=lat.to(dev), height=128, width=128).float().cpu()
+    osched = OS.make_scheduler(sched_name, dict(OS.SD15_SCHEDULER_CONFIG))
+    osched.set_timesteps(steps)
+    assert torch.equal(osched.timesteps.cpu(), model.scheduler.timesteps.cpu()), "timestep tables differ"
+    x0 = lat * float(osched.init_noise_sigma)
+    ref = OP.denoise(oracle.cpu(), osched, x0, torch.cat([ne, pe]).float(), osched.timesteps, 7.5)
+    rl2 = _rel_l2(out, ref)
+    print(f"LOOP PARITY {sched_name} x{steps}: rel-L2 {rl2:.4g}")
+    assert torch.isfinite(out).all() and rl2 <= 5e-2
+
+
+def test_unfused_reference_call_pattern_matches_fused(cuda_device):
+    """Driving the B200 objects exactly like the reference loop (pipeline :465-489) gives the fused result."""
+    from stablediffusion_b200.models.stable_diffusion import SDModelWrapper
+    from stablediffusion_b200.pipelines.sd_unified_pipeline import StableDiffusionUnifiedPipeline
+
+    dev = cuda_device
+    cfg, ours, _ = _make_unet(dev, **SMALL_UNET)
+    vcfg, vae, _ = _make_vae(dev)
+    model = SDModelWrapper(vae=vae, base=ours, device=str(dev))
+    g = torch.Generator().manual_seed(4)
+    lat = torch.randn(1, 4, 16, 16, generator=g).to(dev)
+    pe = torch.randn(1, 77, 64, generator=g).to(dev, torch.bfloat16)
+    ne = torch.randn(1, 77, 64, generator=g).to(dev, torch.bfloat16)
+    pipe = StableDiffusionUnifiedPipeline(do_cfg=True, device=str(dev), output_type="latents")
+    fused = pipe(model, prompt_embeds=pe, negative_prompt_embeds=ne, num_inference_steps=6, guidance_scale=5.0,
+                 latents=lat, height=128, width=128)
+    sch = model.scheduler
+    sch.set_timesteps(6, device=dev)
+    latents = lat.float() * float(sch.init_noise_sigma)
+    ctx = torch.cat([ne, pe])
+    for t in sch.timesteps:
+        inp = torch.cat([latents] * 2)
+        inp = sch.scale_model_input(inp, t)
+        noise_pred = model.base(inp, t, ctx, return_dict=False)[0]
+        u, c = noise_pred.chunk(2)
+        noise_pred = 5.0 * (c - u) + u
+        latents = sch.step(noise_pred, t, latents, return_dict=False)[0]
+    rl2 = _rel_l2(latents.cpu(), fused.cpu())
+    print(f"UNFUSED vs FUSED rel-L2 {rl2:.4g}")
+    assert rl2 <= 2e-2
+
+
+def test_pipeline_sd15_txt2img_20_euler(cuda_device):
+    """BASELINE config 1 end to end (random-init SD1.5 + VAE): final image PSNR vs the fp32 oracle."""
+    from oracle import pipeline as OP
+    from oracle import schedulers as OS
+    from stablediffusion_b200.models.stable_diffusion import SDModelWrapper
+    from stablediffusion_b200.pipelines.sd_unified_pipeline import StableDiffusionUnifiedPipeline
+
+    dev = cuda_device
+    cfg, ours, oracle = _make_unet(dev)
+    vcfg, vae, ovae = _make_vae(dev)
+    model = SDModelWrapper(vae=vae, base=ours, device=str(dev))
+    g = torch.Generator().manual_seed(1234)
+    lat = torch.randn(1, 4, 64, 64, generator=g)
+    pe = torch.randn(1, 77, 768, generator=g).to(torch.bfloat16)
+    ne = torch.randn(1, 77, 768, generator=g).to(torch.bfloat16)
+    pipe = StableDiffusionUnifiedPipeline(do_cfg=True, device=str(dev))
+    img = pipe(model, prompt_embeds=pe.to(dev), negative_prompt_embeds=ne.to(dev), num_inference_steps=20,
+               guidance_scale=7.5, latents=lat.to(dev)).float().cpu()
+    assert img.shape == (1, 3, 512, 512)
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.backends.cudnn.allow_tf32 = False
+    osched = OS.make_scheduler("euler", dict(OS.SD15_SCHEDULER_CONFIG))
+    osched.set_timesteps(20)
+    x0 = (lat * float(osched.init_noise_sigma)).to(dev)
+    zl = OP.denoise(oracle.to(dev), osched, x0, torch.cat([ne, pe]).float().to(dev), osched.timesteps, 7.5)
+    with torch.no_grad():
+        ref = ovae.to(dev).decode(zl / 0.18215).float().cpu()
+    lat_ours = StableDiffusionUnifiedPipeline(do_cfg=True, device=str(dev), output_type="latents")(
+        model, prompt_embeds=pe.to(dev), negative_prompt_embeds=ne.to(dev), num_inference_steps=20, guidance_scale=7.5,
+        latents=lat.to(dev)).float().cpu()
+    psnr = _psnr(img, ref, peak=(ref.max() - ref.min()).item())
+    print(f"E2E SD1.5 20 Euler: latent rel-L2 {_rel_l2(lat_ours, zl.cpu()):.4g}, image PSNR {psnr:.1f} dB, launches/step {pipe.last_engine.launches_per_step}")
+    assert torch.isfinite(img).all() and psnr >= 30.0

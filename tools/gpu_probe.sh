@@ -10,13 +10,14 @@ nvidia-smi --query-gpu=name,driver_version,memory.total --format=csv >> "$OUT" 2
 python -m pytest "$FILE" -m gpu --collect-only -q 2>/dev/null | grep "::" | sed 's/\[.*//' | sort -u > gpurun_out/probe_tests.txt
 while read -r t; do
   start=$(date +%s)
-  timeout 300 python -m pytest "$t" -m gpu -q --no-header -p no:cacheprovider -rfE --tb=line > gpurun_out/probe_last.log 2>&1
+  timeout 300 python -m pytest "$t" -m gpu -q -s --no-header -p no:cacheprovider -rfE --tb=short > gpurun_out/probe_last.log 2>&1
   rc=$?
   end=$(date +%s)
   echo "$t rc=$rc $((end - start))s : $(tail -1 gpurun_out/probe_last.log)" >> "$OUT"
+  grep -E "PARITY|E2E|UNFUSED|launches per" gpurun_out/probe_last.log | cut -c1-300 >> "$OUT"
   if [ $rc -ne 0 ]; then
     echo "----- $t" >> gpurun_out/probe_failures.log
-    grep -E "^(FAILED|ERROR)|Error|out of tolerance|rel-L2|trap|illegal|launch fail" gpurun_out/probe_last.log | cut -c1-400 | head -40 >> gpurun_out/probe_failures.log
+    grep -E "^(FAILED|ERROR|E  )|Error|out of tolerance|rel-L2|trap|illegal|launch fail" gpurun_out/probe_last.log | cut -c1-300 | head -40 >> gpurun_out/probe_failures.log
   fi
 done < gpurun_out/probe_tests.txt
 echo "== summary"; cat "$OUT"; echo "== failures"; head -c 6000 gpurun_out/probe_failures.log
