@@ -1,0 +1,181 @@
+"""CPU tests of the host side: scheduler tables (bit-exact vs oracle and golden fixtures), the fused step-table
+coefficients (emulated in fp32 exactly as the CUDA kernel evaluates them), LoRA parsing/merging, weight packing,
+config semantics, pipeline index arithmetic."""
+import math
+import os
+
+import pytest
+import torch
+
+from oracle import schedulers as OS
+from stablediffusion_b200 import _native as N
+from stablediffusion_b200.config import scheduler_config, unet_config
+from stablediffusion_b200.schedulers import (B200DDIMScheduler, B200DPMSolverMultistepScheduler, B200EulerDiscreteScheduler,
+                                             make_scheduler)
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+CFG = dict(OS.SD15_SCHEDULER_CONFIG)
+
+
+@pytest.mark.parametrize("name,n", [("euler", 20), ("euler", 30), ("euler", 50), ("DDIM", 20), ("DDIM", 50), ("DPM++ 2M", 20),
+                                    ("DPM++ 2M", 50), ("DPM++ 2M Karras", 25)])
+def test_timestep_tables_bit_exact(name, n):
+    gold = torch.load(os.path.join(GOLDEN, "scheduler_tables.pt"))[f"{name}/{n}"]
+    s = make_scheduler(name, B200EulerDiscreteScheduler(**CFG).config)
+    s.set_timesteps(n)
+    o = OS.make_scheduler(name, CFG)
+    o.set_timesteps(n)
+    for ref in (gold["timesteps"], o.timesteps):
+        assert s.timesteps.dtype == ref.dtype and torch.equal(s.timesteps, ref)          # int64 exact / fp32 bit pattern
+    if gold["sigmas"] is not None and hasattr(s, "sigmas"):
+        assert torch.equal(s.sigmas, gold["sigmas"]) and torch.equal(s.sigmas, o.sigmas)  # fp32 bit-exact
+    assert float(s.init_noise_sigma) == gold["init_noise_sigma"]
+
+
+def test_sdxl_euler_leading_table():
+    gold = torch.load(os.path.join(GOLDEN, "scheduler_tables.pt"))["sdxl-euler/30"]
+    s = B200EulerDiscreteScheduler(**scheduler_config("sdxl"))
+    s.set_timesteps(30)
+    assert torch.equal(s.timesteps, gold["timesteps"]) and torch.equal(s.sigmas, gold["sigmas"])
+    assert float(s.init_noise_sigma) == gold["init_noise_sigma"]
+
+
+def _emulate_kernel(tab_row, x, eps, hist):
+    """fp32 evaluation in the order of cfg_step_kernel (csrc/bandwidth.cu)."""
+    K1, K2, CX, CE, C0, C1 = [tab_row[i] for i in (N.ST_K1, N.ST_K2, N.ST_CX, N.ST_CE, N.ST_C0, N.ST_C1)]
+    x0 = (x - K1 * eps) * K2
+    xn = CX * x + CE * eps + C0 * x0
+    if hist is not None and C1 != 0:
+        xn = xn + C1 * (x0 - hist)
+    return xn, x0
+
+
+@pytest.mark.parametrize("name,n", [("euler", 20), ("DDIM", 50), ("DPM++ 2M", 20), ("DPM++ 2M Karras", 10), ("DPM++ 2M", 1)])
+def test_step_table_reproduces_oracle_trajectory(name, n):
+    s = make_scheduler(name, B200EulerDiscreteScheduler(**CFG).config)
+    s.set_timesteps(n)
+    o = OS.make_scheduler(name, CFG)
+    o.set_timesteps(n)
+    g = torch.Generator().manual_seed(0)
+    x = torch.randn(2, 4, 8, 8, generator=g) * float(o.init_noise_sigma)
+    xo, hist = x.clone(), torch.zeros_like(x)
+    for i, t in enumerate(o.timesteps):
+        eps = torch.randn(2, 4, 8, 8, generator=g)
+        assert s._table[i, N.ST_TIMESTEP].item() == float(t)
+        scaled = o.scale_model_input(xo, t)
+        torch.testing.assert_close(x * s._table[i, N.ST_IN_SCALE], scaled, rtol=2e-5, atol=2e-5)
+        xo = o.step(eps, t, xo)
+        x, hist = _emulate_kernel(s._table[i], x, eps, hist if s._uses_history else None)
+        torch.testing.assert_close(x, xo, rtol=2e-5, atol=2e-5)
+
+
+def test_from_config_uses_target_class_defaults():
+    e = B200EulerDiscreteScheduler(**CFG)                       # SD1.5's PNDM-style config: no timestep_spacing key
+    assert e.config.timestep_spacing == "linspace"
+    d = B200DDIMScheduler.from_config(e.config)
+    assert d.config.timestep_spacing == "leading" and d.config.steps_offset == 1 and d.config.clip_sample is False
+    m = make_scheduler("DPM++ 2M Karras", d.config)
+    assert isinstance(m, B200DPMSolverMultistepScheduler) and m.config.use_karras_sigmas and m.config.beta_schedule == "scaled_linear"
+    with pytest.raises(ValueError, match="Unknown scheduler name"):
+        make_scheduler("nope", e.config)
+    with pytest.raises(ValueError, match="no B200 kernel yet"):
+        make_scheduler("euler_a", e.config)                      # a 'next' row: fails loudly, no CPU fallback
+
+
+def test_geglu_interleave_and_conv_packing():
+    from stablediffusion_b200.packing import conv_weight_to_gemm, geglu_block_n, geglu_interleave
+
+    C = 320
+    w = torch.arange(8 * C, dtype=torch.float32)[:, None].repeat(1, 2)
+    bn = geglu_block_n(8 * C)
+    p = geglu_interleave(w, bn)
+    half = bn // 2
+    for t in range(8 * C // bn):
+        assert torch.equal(p[t * bn:t * bn + half, 0], torch.arange(t * half, (t + 1) * half, dtype=torch.float32))
+        assert torch.equal(p[t * bn + half:(t + 1) * bn, 0], 4 * C + torch.arange(t * half, (t + 1) * half, dtype=torch.float32))
+    w4 = torch.randn(6, 5, 3, 3)
+    g = conv_weight_to_gemm(w4)
+    assert g.shape == (6, 45) and torch.equal(g[:, (1 * 3 + 2) * 5 + 4], w4[:, 4, 1, 2])   # [co][kh][kw][ci]
+
+
+def _fake_lora(paths, r=4, dims=None, seed=0, fmt="diffusers", alpha=None):
+    g = torch.Generator().manual_seed(seed)
+    sd = {}
+    for p in paths:
+        o, i = dims[p]
+        A, B = torch.randn(r, i, generator=g) / r, torch.randn(o, r, generator=g) * 0.02
+        if fmt == "diffusers":     # train_lora_pipeline.py:497-528 -> save_lora_weights
+            sd[f"unet.{p}.lora.down.weight"], sd[f"unet.{p}.lora.up.weight"] = A, B
+        elif fmt == "peft":
+            sd[f"unet.{p}.lora_A.weight"], sd[f"unet.{p}.lora_B.weight"] = A, B
+        else:                      # A1111 / kohya
+            k = "lora_unet_" + p.replace(".", "_")
+            sd[f"{k}.lora_down.weight"], sd[f"{k}.lora_up.weight"] = A, B
+            sd[f"{k}.alpha"] = torch.tensor(float(alpha))
+    return sd
+
+
+@pytest.mark.parametrize("fmt,alpha", [("diffusers", None), ("peft", None), ("kohya", 2.0)])
+def test_lora_merge_equals_unmerged_forward(fmt, alpha):
+    """merged-weights forward == PEFT-semantics unmerged forward, fp32, rel <= 1e-5 (SURVEY §4 test plan)."""
+    from oracle.lora import attach_unmerged
+    from stablediffusion_b200.lora import merged_state_dict, parse_lora_state_dict
+    from stablediffusion_b200.unet import unet_param_shapes
+    from tests.golden.make_golden import SMALL_UNET, build_small_unet
+
+    shapes = unet_param_shapes(unet_config(**SMALL_UNET))
+    targets = [k[:-7] for k in shapes if k.endswith((".to_q.weight", ".to_k.weight", ".to_v.weight", ".to_out.0.weight"))]
+    dims = {p: tuple(shapes[p + ".weight"]) for p in targets}
+    modules = sorted({k.rsplit(".", 1)[0] for k in shapes if k.endswith(".weight")})
+    a1 = parse_lora_state_dict(_fake_lora(targets, 4, dims, 1, fmt, alpha), unet_modules=modules)["unet"]
+    a2 = parse_lora_state_dict(_fake_lora(targets[:6], 2, dims, 2, "diffusers"), unet_modules=modules)["unet"]
+    assert len(a1) == len(targets) == 6 * 8 // 2 * 1 or len(a1) == len(targets)
+    adapters, weights = {"style": a1, "char": a2}, {"style": 0.8, "char": 0.5}
+    base = build_small_unet()
+    merged = build_small_unet()
+    merged.load_state_dict(merged_state_dict(base.state_dict(), adapters, weights), strict=True)
+    attach_unmerged(base, adapters, weights)
+    g = torch.Generator().manual_seed(3)
+    x, c = torch.randn(1, 4, 16, 16, generator=g), torch.randn(1, 77, 64, generator=g)
+    with torch.no_grad():
+        a, b = base(x, torch.tensor(500.0), c), merged(x, torch.tensor(500.0), c)
+    assert ((a - b).norm() / a.norm()).item() <= 1e-5
+    plain = build_small_unet()
+    with torch.no_grad():
+        assert ((plain(x, torch.tensor(500.0), c) - a).norm() / a.norm()).item() > 1e-4   # the adapters do something
+
+
+def test_invalid_lora_checkpoint_raises():
+    from stablediffusion_b200.lora import parse_lora_state_dict
+
+    with pytest.raises(ValueError, match="Invalid LoRA checkpoint"):
+        parse_lora_state_dict({"unet.conv_in.weight": torch.zeros(1)})
+
+
+def test_img2img_timestep_slice():
+    """reference :722-761: N=50, strength 0.6 -> 30 steps starting at index 20."""
+    from stablediffusion_b200.pipelines.sd_unified_pipeline import StableDiffusionUnifiedPipeline
+
+    class M:
+        pass
+
+    p = StableDiffusionUnifiedPipeline(device="cuda")
+    p.model = M()
+    p.model.scheduler = B200EulerDiscreteScheduler(**CFG)
+    p.model.scheduler.set_timesteps(50)
+    ts, n = p.get_timesteps(50, 0.6)
+    assert n == 30 and len(ts) == 30 and torch.equal(ts, p.model.scheduler.timesteps[20:])
+    ts, n = p.get_timesteps(50, 1.0)
+    assert n == 50
+    ts, n = p.get_timesteps(50, 0.0)
+    assert n == 0 and len(ts) == 0
+
+
+def test_param_shapes_match_oracle_strictly():
+    from oracle.unet import SD15_UNET, SDXL_UNET, UNet2DConditionOracle
+    from stablediffusion_b200.unet import unet_param_shapes
+
+    for mt, oc in (("sd15", SD15_UNET), ("sdxl", SDXL_UNET)):
+        with torch.device("meta"):
+            osd = {k: tuple(v.shape) for k, v in UNet2DConditionOracle(**oc).state_dict().items()}
+        assert osd == {k: tuple(v) for k, v in unet_param_shapes(unet_config(mt)).items()}
