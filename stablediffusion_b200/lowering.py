@@ -62,6 +62,7 @@ class Builder:
         self.gemm_flops = 0  # algorithmic 2*MAC of the GEMM ops added
         self.attn_flops = 0  # algorithmic 4*B*heads*Nq*Nkv*d of the attention ops added
         self.tag = 0
+        self.meta = {}  # op index -> short description (profiling aid)
 
     @property
     def flops(self):
@@ -87,7 +88,8 @@ class Builder:
             ws = self._ws if need <= self._ws.numel() else self.empty([need], torch.uint8)
             g.workspace = ws.data_ptr()
             g.workspace_bytes = ws.numel()
-        self.prog.add(N.OP_GEMM, g, self.tag, keep)
+        idx = self.prog.add(N.OP_GEMM, g, self.tag, keep)
+        self.meta[idx] = self._pending_meta
 
     @staticmethod
     def _epilogue(g: N.Gemm, bias, rowvec, residual, ldr, silu, geglu, out_f32, bias_row, alpha, rows_per_group):
@@ -150,6 +152,7 @@ class Builder:
             if rm != M or rn != n_out:
                 raise ValueError("linear: residual shape mismatch")
         self._epilogue(g, bias, rowvec, residual, ldr, silu, geglu, out_f32, bias_row, alpha, rows_per_group)
+        self._pending_meta = dict(op='linear', M=M, N=Nn, K=K + K2, flops=2 * M * Nn * (K + K2), geglu=geglu)
         self._finish_gemm(g, (a, w, out, bias, residual, rowvec, a2))
         self.gemm_flops += 2 * M * Nn * (K + K2)
         return out
@@ -207,6 +210,7 @@ class Builder:
         g.splits, g.block_n = splits, block_n
         ldr = residual.shape[-1] if residual is not None else 0
         self._epilogue(g, bias, rowvec, residual, ldr, silu, False, False, False, 1.0, 0)
+        self._pending_meta = dict(op=f'conv{len(taps)}', M=NB * H * W, N=Cout, K=ktot, flops=2 * NB * H * W * Cout * ktot, hw=(H, W))
         self._finish_gemm(g, (x, w, out, bias, residual, rowvec) + tuple(extra or ()))
         self.gemm_flops += 2 * NB * H * W * Cout * ktot
         return out
@@ -229,7 +233,8 @@ class Builder:
         p.NB, p.HW, p.groups, p.silu, p.eps = NB, HW, groups, int(bool(silu)), float(eps)
         p.gamma, p.beta, p.out = gamma.data_ptr(), beta.data_ptr(), out.data_ptr()
         p.partials, p.partials_bytes = self._gn_ws.data_ptr(), self._gn_ws.numel()
-        self.prog.add(N.OP_GROUPNORM, p, self.tag, (x1, x2, gamma, beta, out))
+        idx = self.prog.add(N.OP_GROUPNORM, p, self.tag, (x1, x2, gamma, beta, out))
+        self.meta[idx] = dict(op='groupnorm', NB=NB, HW=HW, C=C1 + C2, bytes=4 * NB * HW * (C1 + C2))
         return out
 
     def layernorm(self, x, gamma, beta, eps, out=None):
@@ -239,7 +244,8 @@ class Builder:
         p = N.LayerNorm()
         p.x, p.out, p.ldx, p.ldo, p.rows, p.C, p.eps = xp, out.data_ptr(), ldx, out.stride(0), rows, Cc, float(eps)
         p.gamma, p.beta = gamma.data_ptr(), beta.data_ptr()
-        self.prog.add(N.OP_LAYERNORM, p, self.tag, (x, gamma, beta, out))
+        idx = self.prog.add(N.OP_LAYERNORM, p, self.tag, (x, gamma, beta, out))
+        self.meta[idx] = dict(op='layernorm', rows=rows, C=Cc, bytes=4 * rows * Cc)
         return out
 
     # ---- attention ----------------------------------------------------------------------------------
@@ -256,7 +262,8 @@ class Builder:
         p.q, p.k, p.v, p.out = q.data_ptr(), k.data_ptr(), v.data_ptr(), out.data_ptr()
         p.ldq, p.ldk, p.ldv, p.ldo = q.stride(1), k.stride(1), v.stride(1), out.stride(1)
         p.B, p.heads, p.Nq, p.Nkv, p.d, p.scale = B, heads, Nq, Nkv, d, float(scale)
-        self.prog.add(N.OP_ATTENTION, p, self.tag, (q, k, v, out))
+        idx = self.prog.add(N.OP_ATTENTION, p, self.tag, (q, k, v, out))
+        self.meta[idx] = dict(op='attention', B=B, heads=heads, Nq=Nq, Nkv=Nkv, d=d, flops=4 * B * heads * Nq * Nkv * d)
         self.attn_flops += 4 * B * heads * Nq * Nkv * d
         return out
 
