@@ -76,7 +76,23 @@ __global__ void gn_stats_kernel(const GNParams p) {
 #pragma unroll
   for (int j = 0; j < 8; ++j) { s[j] = 0.f; ss[j] = 0.f; }
   const int pix_end = min((chunk + 1) * p.ppc, p.HW);
-  for (int pix = chunk * p.ppc + r; pix < pix_end; pix += p.R) {
+  int pix = chunk * p.ppc + r;
+  for (; pix + 3 * p.R < pix_end; pix += 4 * p.R) {  // 4 independent 16-byte loads in flight per thread
+    uint4 v4[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) v4[u] = ldg_stream(gn_src(p, n, pix + u * p.R, c0));
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      uint32_t w[4] = {v4[u].x, v4[u].y, v4[u].z, v4[u].w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        float2 f = unpack_bf16x2(w[j]);
+        s[2 * j] += f.x; ss[2 * j] += f.x * f.x;
+        s[2 * j + 1] += f.y; ss[2 * j + 1] += f.y * f.y;
+      }
+    }
+  }
+  for (; pix < pix_end; pix += p.R) {
     uint4 v = ldg_stream(gn_src(p, n, pix, c0));
     uint32_t w[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
@@ -117,19 +133,32 @@ __global__ void gn_apply_kernel(const GNParams p) {
   float* srstd = smean + p.groups;
   const int chunk = blockIdx.x, n = blockIdx.y;
   const int tid = threadIdx.x;
-  if (tid < p.groups) {
-    double S = 0.0, SS = 0.0;
-    const float* src = p.partials + (static_cast<long long>(n) * p.chunks * p.groups + tid) * 2;
-    for (int c = 0; c < p.chunks; ++c) {
-      S += src[static_cast<long long>(c) * p.groups * 2];
-      SS += src[static_cast<long long>(c) * p.groups * 2 + 1];
+  {
+    // all threads cooperate: thread -> (group, part); parts stride over the chunk partials, then a shared-memory fold
+    double* red = reinterpret_cast<double*>(srstd + p.groups);  // [parts][groups][2]
+    const int parts = blockDim.x / p.groups;
+    const int g = tid % p.groups, part = tid / p.groups;
+    if (part < parts) {
+      double S = 0.0, SS = 0.0;
+      const float* src = p.partials + (static_cast<long long>(n) * p.chunks * p.groups + g) * 2;
+      for (int c = part; c < p.chunks; c += parts) {
+        const float2 v = *reinterpret_cast<const float2*>(src + static_cast<long long>(c) * p.groups * 2);
+        S += v.x; SS += v.y;
+      }
+      red[(part * p.groups + g) * 2] = S;
+      red[(part * p.groups + g) * 2 + 1] = SS;
     }
-    const double cnt = static_cast<double>(p.HW) * p.cpg;
-    const double mean = S / cnt;
-    double var = SS / cnt - mean * mean;
-    if (var < 0.0) var = 0.0;
-    smean[tid] = static_cast<float>(mean);
-    srstd[tid] = static_cast<float>(1.0 / sqrt(var + static_cast<double>(p.eps)));
+    __syncthreads();
+    if (tid < p.groups) {
+      double S = 0.0, SS = 0.0;
+      for (int q = 0; q < parts; ++q) { S += red[(q * p.groups + tid) * 2]; SS += red[(q * p.groups + tid) * 2 + 1]; }
+      const double cnt = static_cast<double>(p.HW) * p.cpg;
+      const double mean = S / cnt;
+      double var = SS / cnt - mean * mean;
+      if (var < 0.0) var = 0.0;
+      smean[tid] = static_cast<float>(mean);
+      srstd[tid] = static_cast<float>(1.0 / sqrt(var + static_cast<double>(p.eps)));
+    }
   }
   __syncthreads();
   for (int c = tid; c < p.C; c += blockDim.x) {
@@ -145,8 +174,7 @@ __global__ void gn_apply_kernel(const GNParams p) {
 #pragma unroll
   for (int j = 0; j < 8; ++j) { a[j] = sa[c0 + j]; b[j] = sb[c0 + j]; }
   const int pix_end = min((chunk + 1) * p.ppc, p.HW);
-  for (int pix = chunk * p.ppc + r; pix < pix_end; pix += p.R) {
-    uint4 v = ldg_stream(gn_src(p, n, pix, c0));
+  auto apply_store = [&](const uint4& v, int pix) {
     uint32_t w[4] = {v.x, v.y, v.z, v.w};
     uint32_t o[4];
 #pragma unroll
@@ -159,7 +187,16 @@ __global__ void gn_apply_kernel(const GNParams p) {
     }
     bf16* dst = p.out + (static_cast<long long>(n) * p.HW + pix) * p.C + c0;
     *reinterpret_cast<uint4*>(dst) = make_uint4(o[0], o[1], o[2], o[3]);
+  };
+  int pix = chunk * p.ppc + r;
+  for (; pix + 3 * p.R < pix_end; pix += 4 * p.R) {
+    uint4 v4[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) v4[u] = ldg_stream(gn_src(p, n, pix + u * p.R, c0));
+#pragma unroll
+    for (int u = 0; u < 4; ++u) apply_store(v4[u], pix + u * p.R);
   }
+  for (; pix < pix_end; pix += p.R) apply_store(ldg_stream(gn_src(p, n, pix, c0)), pix);
 }
 
 struct GNPlan { GNParams p; int threads; size_t smem; };
@@ -180,43 +217,54 @@ int launch_groupnorm(const void* plan, cudaStream_t s) {
 struct LNParams {
   const bf16* x; bf16* out; long long ldx, ldo; int rows, C; float eps; const float* gamma; const float* beta;
 };
-constexpr int LN_MAXV = 8;  // 8 vectors * 32 lanes * 8 elements = 2048 channels
-__global__ void __launch_bounds__(256) layernorm_kernel(const LNParams p) {
-  const int row = blockIdx.x * 8 + (threadIdx.x >> 5);
+constexpr int LN_MAXV = 8;  // up to 8 vectors (64 channels) per lane
+// A row is owned by `lpr` lanes (8, 16 or 32): with C = 320 a warp normalises 4 rows at once with all lanes busy,
+// and every lane has VPL independent 16-byte loads in flight.
+template <int VPL>
+__global__ void __launch_bounds__(256) layernorm_kernel(const LNParams p, int lpr) {
   const int lane = threadIdx.x & 31;
-  if (row >= p.rows) return;
+  const int rows_per_warp = 32 / lpr;
+  const int sub = lane / lpr, sl = lane % lpr;
+  const int warp_global = blockIdx.x * 8 + (threadIdx.x >> 5);
+  const int row = warp_global * rows_per_warp + sub;
+  const bool active = row < p.rows;
   const int nvec = p.C >> 3;
-  const bf16* xr = p.x + static_cast<long long>(row) * p.ldx;
-  float v[LN_MAXV][8];
+  const bf16* xr = p.x + static_cast<long long>(active ? row : 0) * p.ldx;
+  uint4 raw[VPL];
+#pragma unroll
+  for (int i = 0; i < VPL; ++i) {
+    const int vi = sl + lpr * i;
+    raw[i] = (active && vi < nvec) ? ldg_stream(xr + vi * 8) : make_uint4(0, 0, 0, 0);
+  }
+  float v[VPL][8];
   float sum = 0.f;
 #pragma unroll
-  for (int i = 0; i < LN_MAXV; ++i) {
-    const int vi = lane + 32 * i;
-    if (vi < nvec) {
-      uint4 u = ldg_stream(xr + vi * 8);
-      uint32_t w[4] = {u.x, u.y, u.z, u.w};
+  for (int i = 0; i < VPL; ++i) {
+    uint32_t w[4] = {raw[i].x, raw[i].y, raw[i].z, raw[i].w};
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        float2 f = unpack_bf16x2(w[j]);
-        v[i][2 * j] = f.x; v[i][2 * j + 1] = f.y;
-        sum += f.x + f.y;
-      }
+    for (int j = 0; j < 4; ++j) {
+      float2 f = unpack_bf16x2(w[j]);
+      v[i][2 * j] = f.x; v[i][2 * j + 1] = f.y;
+      sum += f.x + f.y;
     }
   }
-  const float mean = warp_sum(sum) / static_cast<float>(p.C);
+  for (int o = lpr >> 1; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+  const float mean = sum / static_cast<float>(p.C);
   float sq = 0.f;
 #pragma unroll
-  for (int i = 0; i < LN_MAXV; ++i) {
-    if (lane + 32 * i < nvec) {
+  for (int i = 0; i < VPL; ++i) {
+    if (sl + lpr * i < nvec) {
 #pragma unroll
       for (int j = 0; j < 8; ++j) { float d = v[i][j] - mean; sq += d * d; }
     }
   }
-  const float rstd = rsqrtf(warp_sum(sq) / static_cast<float>(p.C) + p.eps);
+  for (int o = lpr >> 1; o > 0; o >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, o);
+  const float rstd = rsqrtf(sq / static_cast<float>(p.C) + p.eps);
+  if (!active) return;
   bf16* orow = p.out + static_cast<long long>(row) * p.ldo;
 #pragma unroll
-  for (int i = 0; i < LN_MAXV; ++i) {
-    const int vi = lane + 32 * i;
+  for (int i = 0; i < VPL; ++i) {
+    const int vi = sl + lpr * i;
     if (vi < nvec) {
       const float4* g4 = reinterpret_cast<const float4*>(p.gamma + vi * 8);
       const float4* b4 = reinterpret_cast<const float4*>(p.beta + vi * 8);
@@ -234,7 +282,24 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const LNParams p) {
 }
 int launch_layernorm(const void* plan, cudaStream_t s) {
   const LNParams& p = *static_cast<const LNParams*>(plan);
-  layernorm_kernel<<<(p.rows + 7) / 8, 256, 0, s>>>(p);
+  const int nvec = p.C >> 3;
+  int lpr = 32;
+  for (int cand : {8, 16}) {
+    if (nvec % cand == 0 && nvec / cand <= LN_MAXV) { lpr = cand; break; }
+  }
+  const int vpl = (nvec + lpr - 1) / lpr;
+  const int rows_per_cta = 8 * (32 / lpr);
+  const int grid = (p.rows + rows_per_cta - 1) / rows_per_cta;
+  switch (vpl) {
+    case 1: layernorm_kernel<1><<<grid, 256, 0, s>>>(p, lpr); break;
+    case 2: layernorm_kernel<2><<<grid, 256, 0, s>>>(p, lpr); break;
+    case 3: layernorm_kernel<3><<<grid, 256, 0, s>>>(p, lpr); break;
+    case 4: layernorm_kernel<4><<<grid, 256, 0, s>>>(p, lpr); break;
+    case 5: layernorm_kernel<5><<<grid, 256, 0, s>>>(p, lpr); break;
+    case 6: layernorm_kernel<6><<<grid, 256, 0, s>>>(p, lpr); break;
+    case 7: layernorm_kernel<7><<<grid, 256, 0, s>>>(p, lpr); break;
+    default: layernorm_kernel<8><<<grid, 256, 0, s>>>(p, lpr); break;
+  }
   B200SD_CUDA(cudaGetLastError());
   return 0;
 }
@@ -538,10 +603,10 @@ bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 
 }  // namespace
 
 int groupnorm_chunks(int NB, int HW, int C) {
-  (void)C;
-  if (NB < 1 || HW < 1) return 1;
-  int target = (2 * 148 + NB - 1) / NB;
-  int max_chunks = std::max(1, HW / 16);
+  if (NB < 1 || HW < 1 || C < 8) return 1;
+  int target = (6 * 148 + NB - 1) / NB;
+  const int R = std::max(1, 256 / (C / 8));           // pixel rows a CTA walks in parallel
+  int max_chunks = std::max(1, HW / (4 * R));         // keep >= 4 loads per thread so one unrolled batch covers a chunk
   return std::max(1, std::min(target, max_chunks));
 }
 
@@ -568,7 +633,8 @@ int plan_groupnorm(const b200sd_groupnorm& g, PlannedOp* out) {
   p.R = std::max(1, 256 / p.cols);
   pl.threads = p.cols * p.R;
   if (pl.threads < g.groups) { p.R = (g.groups + p.cols - 1) / p.cols; pl.threads = p.cols * p.R; }
-  pl.smem = (2 * static_cast<size_t>(C) + 2 * g.groups) * sizeof(float);
+  pl.smem = (2 * static_cast<size_t>(C) + 2 * g.groups) * sizeof(float) + 8 +
+            static_cast<size_t>(pl.threads / g.groups + 1) * g.groups * 2 * sizeof(double);
   const long long need = static_cast<long long>(g.NB) * groupnorm_chunks(g.NB, g.HW, C) * g.groups * 2 * 4;
   B200SD_CHECK_ARG(g.partials_bytes >= need, "groupnorm: partials workspace %lld < %lld bytes", (long long)g.partials_bytes, need);
   return finish_plan(out, B200SD_OP_GROUPNORM, pl, launch_groupnorm, 2);

@@ -535,9 +535,8 @@ int choose_gemm_tiling(const b200sd_gemm& g, GemmTiling* t) {
   if (bn == 0) {
     if (g.N <= 32 && !geglu) bn = 32;
     else if (g.N <= 64 && !geglu) bn = 64;
-    else if (g.N % 160 == 0 && g.N % 128 != 0) bn = 160;
+    else if (g.N % 160 == 0) bn = 160;  // 9 KB of operands per 80 MMA cycles: below the 128 B/clk smem limit that BN=128 sits on
     else if (g.N % 128 == 0) bn = 128;
-    else if (g.N % 160 == 0) bn = 160;
     else bn = 128;
   }
   B200SD_CHECK_ARG(bn == 32 || bn == 64 || bn == 128 || bn == 160 || bn == 256, "gemm: block_n=%d unsupported", bn);

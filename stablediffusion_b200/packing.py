@@ -6,7 +6,7 @@ import torch
 
 def geglu_block_n(n_total: int) -> int:
     """N tile used for a GEGLU projection of width n_total (= 8*C); must match the library's auto choice."""
-    if n_total % 128 == 0:
+    if n_total % 128 == 0:   # 64 output columns per tile = two 32-column staging blocks of the TMA-store epilogue
         return 128
     if n_total % 160 == 0:
         return 160
