@@ -14,6 +14,7 @@
 // but the tensor-map extent is d, so columns >= d arrive as zeros and never touch HBM.
 #include <algorithm>
 #include <new>
+#include <type_traits>
 
 #include "common.cuh"
 #include "internal.h"
@@ -39,11 +40,18 @@ struct alignas(64) AttnParams {
 template <int DPAD>
 struct AttnCfg {
   static constexpr int DB = DPAD / 64;
-  static constexpr int NST = DPAD == 64 ? 3 : (DPAD == 128 ? 2 : 1);
+  // d <= 64 (the N = 4096 level of SD1.5, SDXL everywhere): 2 CTAs per SM so that two softmax warps share every SM
+  // sub-partition (the softmax, not the MMA, bounds this kernel: 16384 ex2 per 128x128 block = 1024 MUFU cycles).
+  static constexpr int OCC = DPAD == 64 ? 2 : 1;
+  static constexpr int NSTK = DPAD == 192 ? 1 : 2;          // K stages (freed as soon as S_j = Q K_j^T has completed)
+  static constexpr int NSTV = DPAD == 128 ? 2 : 1;          // V stages (freed when O += P_j V_j has completed)
+  static constexpr int SBUF = DPAD == 64 ? 1 : 2;           // S accumulators in TMEM
+  static constexpr int PBUF = DPAD == 64 ? 1 : 2;           // P tiles in shared memory
+  static constexpr int TMEM_COLS = DPAD == 64 ? 256 : 512;  // SBUF*128 columns of S, then O
   static constexpr int Q_BYTES = DB * TILE16K;
-  static constexpr int KV_BYTES = DB * TILE16K;           // each of K and V per stage
-  static constexpr int P_BYTES = 2 * TILE16K;             // 128 rows x 128 keys bf16
-  static constexpr int SMEM = Q_BYTES + NST * 2 * KV_BYTES + 2 * P_BYTES + 1024 + 256;
+  static constexpr int KV_BYTES = DB * TILE16K;             // one K (or V) stage
+  static constexpr int P_BYTES = 2 * TILE16K;               // 128 rows x 128 keys bf16
+  static constexpr int SMEM = Q_BYTES + (NSTK + NSTV) * KV_BYTES + PBUF * P_BYTES + 1024 + 256;
 };
 
 __device__ __forceinline__ float ex2_approx(float x) {
@@ -53,25 +61,26 @@ __device__ __forceinline__ float ex2_approx(float x) {
 }
 
 template <int DPAD>
-__global__ void __launch_bounds__(ATT_THREADS, 1) attention_kernel(const __grid_constant__ AttnParams p) {
+__global__ void __launch_bounds__(ATT_THREADS, AttnCfg<DPAD>::OCC) attention_kernel(const __grid_constant__ AttnParams p) {
   using Cfg = AttnCfg<DPAD>;
   constexpr int DB = Cfg::DB;
-  constexpr int NST = Cfg::NST;
+  constexpr int NSTK = Cfg::NSTK, NSTV = Cfg::NSTV, SBUF = Cfg::SBUF, PBUF = Cfg::PBUF;
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* sQ = smem;
-  uint8_t* sK = sQ + Cfg::Q_BYTES;                 // [NST][KV_BYTES]
-  uint8_t* sV = sK + NST * Cfg::KV_BYTES;          // [NST][KV_BYTES]
-  uint8_t* sP = sV + NST * Cfg::KV_BYTES;          // [2][P_BYTES]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sP + 2 * Cfg::P_BYTES);
-  uint64_t* q_full = bars;            // 1
-  uint64_t* k_full = bars + 1;        // NST
-  uint64_t* v_full = k_full + NST;    // NST
-  uint64_t* kv_empty = v_full + NST;  // NST
-  uint64_t* s_full = kv_empty + NST;  // 2
-  uint64_t* p_full = s_full + 2;      // 2
-  uint64_t* pv_done = p_full + 2;     // 1
+  uint8_t* sK = sQ + Cfg::Q_BYTES;                 // [NSTK][KV_BYTES]
+  uint8_t* sV = sK + NSTK * Cfg::KV_BYTES;         // [NSTV][KV_BYTES]
+  uint8_t* sP = sV + NSTV * Cfg::KV_BYTES;         // [PBUF][P_BYTES]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sP + PBUF * Cfg::P_BYTES);
+  uint64_t* q_full = bars;             // 1
+  uint64_t* k_full = bars + 1;         // NSTK
+  uint64_t* k_empty = k_full + NSTK;   // NSTK
+  uint64_t* v_full = k_empty + NSTK;   // NSTV
+  uint64_t* v_empty = v_full + NSTV;   // NSTV
+  uint64_t* s_full = v_empty + NSTV;   // SBUF
+  uint64_t* p_full = s_full + SBUF;    // PBUF
+  uint64_t* pv_done = p_full + PBUF;   // 1
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(pv_done + 1);
 
   const int warp = threadIdx.x >> 5;
@@ -83,36 +92,37 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attention_kernel(const __grid_
 
   if (threadIdx.x == 0) {
     mbar_init(q_full, 1);
-    for (int i = 0; i < NST; ++i) { mbar_init(&k_full[i], 1); mbar_init(&v_full[i], 1); mbar_init(&kv_empty[i], 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&s_full[i], 1); mbar_init(&p_full[i], 128); }
+    for (int i = 0; i < NSTK; ++i) { mbar_init(&k_full[i], 1); mbar_init(&k_empty[i], 1); }
+    for (int i = 0; i < NSTV; ++i) { mbar_init(&v_full[i], 1); mbar_init(&v_empty[i], 1); }
+    for (int i = 0; i < SBUF; ++i) mbar_init(&s_full[i], 1);
+    for (int i = 0; i < PBUF; ++i) mbar_init(&p_full[i], 128);
     mbar_init(pv_done, 1);
     fence_barrier_init();
   }
-  if (warp == 1) { tmem_alloc(tmem_slot, 512); tmem_relinquish(); }
+  if (warp == 1) { tmem_alloc(tmem_slot, Cfg::TMEM_COLS); tmem_relinquish(); }
   if (warp == 0 && lane == 0) { tma_prefetch_desc(&p.tmQ); tma_prefetch_desc(&p.tmK); tma_prefetch_desc(&p.tmV); }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  const uint32_t tmem_S = tmem_base;        // 2 x 128 columns
-  const uint32_t tmem_O = tmem_base + 256;  // up to 256 columns
+  const uint32_t tmem_S = tmem_base;               // SBUF x 128 columns
+  const uint32_t tmem_O = tmem_base + SBUF * BLK;  // round16(d) columns
 
   if (warp == 0) {
     // ===================== TMA producer =====================
     if (lane == 0) {
       mbar_arrive_expect_tx(q_full, Cfg::Q_BYTES);
       for (int db = 0; db < DB; ++db) tma_load_4d(sQ + db * TILE16K, &p.tmQ, q_full, db * 64, head, q0, batch);
-      int st = 0;
-      uint32_t ph = 0;
       for (int j = 0; j < nkv; ++j) {
-        mbar_wait(&kv_empty[st], ph ^ 1);
-        mbar_arrive_expect_tx(&k_full[st], Cfg::KV_BYTES);
+        const int sk = j % NSTK, sv = j % NSTV;
+        mbar_wait(&k_empty[sk], ((j / NSTK) & 1) ^ 1);
+        mbar_arrive_expect_tx(&k_full[sk], Cfg::KV_BYTES);
         for (int db = 0; db < DB; ++db)
-          tma_load_4d(sK + st * Cfg::KV_BYTES + db * TILE16K, &p.tmK, &k_full[st], db * 64, head, j * BLK, batch);
-        mbar_arrive_expect_tx(&v_full[st], Cfg::KV_BYTES);
+          tma_load_4d(sK + sk * Cfg::KV_BYTES + db * TILE16K, &p.tmK, &k_full[sk], db * 64, head, j * BLK, batch);
+        mbar_wait(&v_empty[sv], ((j / NSTV) & 1) ^ 1);
+        mbar_arrive_expect_tx(&v_full[sv], Cfg::KV_BYTES);
         for (int db = 0; db < DB; ++db)
-          tma_load_4d(sV + st * Cfg::KV_BYTES + db * TILE16K, &p.tmV, &v_full[st], db * 64, head, j * BLK, batch);
-        if (++st == NST) { st = 0; ph ^= 1; }
+          tma_load_4d(sV + sv * Cfg::KV_BYTES + db * TILE16K, &p.tmV, &v_full[sv], db * 64, head, j * BLK, batch);
       }
     }
   } else if (warp == 1) {
@@ -120,33 +130,35 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attention_kernel(const __grid_
     const uint32_t idesc_s = umma_idesc_bf16(BLK, BLK, 0);
     const uint32_t idesc_o = umma_idesc_bf16(BLK, p.n_pv, 1);
     const uint32_t q_addr = smem_u32(sQ);
-    auto issue_S = [&](int j) {  // S_j = Q K_j^T into S buffer j&1
-      const int st = j % NST;
-      mbar_wait(&k_full[st], (j / NST) & 1);
+    auto issue_S = [&](int j) {  // S_j = Q K_j^T into S buffer j % SBUF; K stage is released when it completes
+      const int st = j % NSTK;
+      mbar_wait(&k_full[st], (j / NSTK) & 1);
       tc_fence_after();
       if (lane == 0) {
         const uint32_t k_addr = smem_u32(sK + st * Cfg::KV_BYTES);
-        const uint32_t d_tmem = tmem_S + (j & 1) * BLK;
+        const uint32_t d_tmem = tmem_S + (j % SBUF) * BLK;
         for (int ks = 0; ks < p.ksteps_qk; ++ks) {
           const uint32_t off = (ks >> 2) * TILE16K + (ks & 3) * 32;
           umma_bf16_ss(d_tmem, umma_smem_desc_sw128(q_addr + off, 16, 1024),
                        umma_smem_desc_sw128(k_addr + off, 16, 1024), idesc_s, ks != 0 ? 1u : 0u);
         }
-        umma_commit(&s_full[j & 1]);
+        umma_commit(&s_full[j % SBUF]);
+        umma_commit(&k_empty[st]);
       }
       __syncwarp();
     };
+    constexpr bool EARLY = SBUF == 2;  // with two S buffers S_{j+1} is issued before P_j is waited for
     mbar_wait(q_full, 0);
     issue_S(0);
     for (int j = 0; j < nkv; ++j) {
-      if (NST >= 2 && j + 1 < nkv) issue_S(j + 1);
-      const int st = j % NST;
-      mbar_wait(&p_full[j & 1], (j >> 1) & 1);
-      mbar_wait(&v_full[st], (j / NST) & 1);
+      if (EARLY && j + 1 < nkv) issue_S(j + 1);
+      const int sv = j % NSTV, pb = j % PBUF;
+      mbar_wait(&p_full[pb], (j / PBUF) & 1);
+      mbar_wait(&v_full[sv], (j / NSTV) & 1);
       tc_fence_after();
       if (lane == 0) {
-        const uint32_t p_addr = smem_u32(sP + (j & 1) * Cfg::P_BYTES);
-        const uint32_t v_addr = smem_u32(sV + st * Cfg::KV_BYTES);
+        const uint32_t p_addr = smem_u32(sP + pb * Cfg::P_BYTES);
+        const uint32_t v_addr = smem_u32(sV + sv * Cfg::KV_BYTES);
 #pragma unroll
         for (int ks = 0; ks < BLK / 16; ++ks) {
           const uint64_t da = umma_smem_desc_sw128(p_addr + (ks >> 2) * TILE16K + (ks & 3) * 32, 16, 1024);
@@ -154,11 +166,11 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attention_kernel(const __grid_
           const uint64_t db = umma_smem_desc_sw128(v_addr + ks * 2048, TILE16K, 1024);
           umma_bf16_ss(tmem_O, da, db, idesc_o, (j | ks) != 0 ? 1u : 0u);
         }
-        umma_commit(&kv_empty[st]);
+        umma_commit(&v_empty[sv]);
         umma_commit(pv_done);
       }
       __syncwarp();
-      if (NST < 2 && j + 1 < nkv) issue_S(j + 1);
+      if (!EARLY && j + 1 < nkv) issue_S(j + 1);
     }
   } else {
     // ===================== softmax / correction / epilogue: thread <-> query row =====================
@@ -168,56 +180,73 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attention_kernel(const __grid_
     float m_run = -INFINITY;  // running max in the scaled log2 domain
     float l_run = 0.f;
     for (int j = 0; j < nkv; ++j) {
-      mbar_wait(&s_full[j & 1], (j >> 1) & 1);
+      const int sb = j % SBUF, pb = j % PBUF;
+      mbar_wait(&s_full[sb], (j / SBUF) & 1);
       tc_fence_after();
-      const uint32_t s_addr = tmem_S + lane_base + (j & 1) * BLK;
+      const uint32_t s_addr = tmem_S + lane_base + sb * BLK;
       const int kv_valid = min(BLK, p.Nkv - j * BLK);  // keys of this block that exist
-      // pass 1: row max
-      float mx = -INFINITY;
+      uint8_t* prow = sP + pb * Cfg::P_BYTES + r * 128;
+      float alpha = 1.0f;
+      bool waited_pv = false;
+      // The body is instantiated twice: the mask-free version runs on every full block (no per-element predicates).
+      auto block_body = [&](auto masked_tag) {
+        constexpr bool MASKED = decltype(masked_tag)::value;
+        // pass 1: row max
+        float mx = -INFINITY;
 #pragma unroll 1
-      for (int c = 0; c < BLK / 32; ++c) {
-        uint32_t u[32];
-        tmem_ld32(s_addr + c * 32, u);
-        tmem_ld_wait();
+        for (int c = 0; c < BLK / 32; ++c) {
+          uint32_t u[32];
+          tmem_ld32(s_addr + c * 32, u);
+          tmem_ld_wait();
 #pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          const float s = __uint_as_float(u[i]);
-          if (c * 32 + i < kv_valid) mx = fmaxf(mx, s);
+          for (int i = 0; i < 32; ++i) {
+            if (!MASKED || c * 32 + i < kv_valid) mx = fmaxf(mx, __uint_as_float(u[i]));
+          }
         }
-      }
-      const float m_new = fmaxf(m_run, mx * p.scale_log2);
-      const float alpha = ex2_approx(m_run - m_new);  // 0 on the first block (m_run = -inf)
-      // pass 2: probabilities -> bf16 -> swizzled smem (K-major, 128-byte rows, 16-byte chunk ^= row % 8)
-      uint8_t* prow = sP + (j & 1) * Cfg::P_BYTES + r * 128;
-      float rsum = 0.f;
+        const float m_new = fmaxf(m_run, mx * p.scale_log2);
+        alpha = ex2_approx(m_run - m_new);  // 0 on the first block (m_run = -inf)
+        if (PBUF == 1 && j > 0) {  // single P tile: PV_{j-1} must have consumed it before it is overwritten
+          mbar_wait(pv_done, (j - 1) & 1);
+          tc_fence_after();
+          waited_pv = true;
+        }
+        // pass 2: probabilities -> bf16 -> swizzled smem (K-major, 128-byte rows, 16-byte chunk ^= row % 8)
+        float rsum = 0.f;
 #pragma unroll 1
-      for (int c = 0; c < BLK / 32; ++c) {
-        uint32_t u[32];
-        tmem_ld32(s_addr + c * 32, u);
-        tmem_ld_wait();
-        uint32_t pk[16];
+        for (int c = 0; c < BLK / 32; ++c) {
+          uint32_t u[32];
+          tmem_ld32(s_addr + c * 32, u);
+          tmem_ld_wait();
+          uint32_t pk[16];
 #pragma unroll
-        for (int i = 0; i < 16; ++i) {
-          float p0 = ex2_approx(fmaf(__uint_as_float(u[2 * i]), p.scale_log2, -m_new));
-          float p1 = ex2_approx(fmaf(__uint_as_float(u[2 * i + 1]), p.scale_log2, -m_new));
-          if (c * 32 + 2 * i >= kv_valid) p0 = 0.f;
-          if (c * 32 + 2 * i + 1 >= kv_valid) p1 = 0.f;
-          rsum += p0 + p1;
-          pk[i] = pack_bf16x2(p0, p1);
-        }
-        uint8_t* pblk = prow + (c >> 1) * TILE16K;
+          for (int i = 0; i < 16; ++i) {
+            float p0 = ex2_approx(fmaf(__uint_as_float(u[2 * i]), p.scale_log2, -m_new));
+            float p1 = ex2_approx(fmaf(__uint_as_float(u[2 * i + 1]), p.scale_log2, -m_new));
+            if (MASKED) {
+              if (c * 32 + 2 * i >= kv_valid) p0 = 0.f;
+              if (c * 32 + 2 * i + 1 >= kv_valid) p1 = 0.f;
+            }
+            rsum += p0 + p1;
+            pk[i] = pack_bf16x2(p0, p1);
+          }
+          uint8_t* pblk = prow + (c >> 1) * TILE16K;
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          const int chunk = ((c & 1) * 4 + i) ^ (r & 7);
-          *reinterpret_cast<uint4*>(pblk + chunk * 16) = make_uint4(pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
+          for (int i = 0; i < 4; ++i) {
+            const int chunk = ((c & 1) * 4 + i) ^ (r & 7);
+            *reinterpret_cast<uint4*>(pblk + chunk * 16) = make_uint4(pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
+          }
         }
-      }
-      l_run = l_run * alpha + rsum;
-      m_run = m_new;
+        l_run = l_run * alpha + rsum;
+        m_run = m_new;
+      };
+      if (kv_valid == BLK) block_body(std::false_type{});
+      else block_body(std::true_type{});
       // correction: O *= alpha, only after PV_{j-1} has landed and only if some row of this warp moved
       if (j > 0) {
-        mbar_wait(pv_done, (j - 1) & 1);
-        tc_fence_after();
+        if (!waited_pv) {
+          mbar_wait(pv_done, (j - 1) & 1);
+          tc_fence_after();
+        }
         if (__any_sync(0xffffffffu, alpha != 1.0f)) {
           const uint32_t o_addr = tmem_O + lane_base;
 #pragma unroll 1
@@ -234,7 +263,7 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attention_kernel(const __grid_
       }
       fence_proxy_async_smem();  // P (generic-proxy stores) -> visible to the MMA's async-proxy reads
       tc_fence_before();
-      mbar_arrive(&p_full[j & 1]);
+      mbar_arrive(&p_full[pb]);
     }
     // ---- epilogue: O / l -> bf16 -> global ----
     mbar_wait(pv_done, (nkv - 1) & 1);
@@ -262,7 +291,7 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attention_kernel(const __grid_
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  if (warp == 1) tmem_dealloc(tmem_base, 512);
+  if (warp == 1) tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
 }
 
 struct AttnPlan {

@@ -30,19 +30,27 @@ constexpr int BK = 64;
 constexpr int A_STAGE_BYTES = BM * BK * 2;  // 16 KiB
 constexpr int GEMM_THREADS = 192;
 
+constexpr int RING_SLOTS = 4;              // epilogue staging ring: 4 x [128 rows x 32 bf16 columns] (SWIZZLE_64B)
+constexpr int RING_SLOT_BYTES = BM * 64;   // 8 KiB
+constexpr int RING_BYTES = RING_SLOTS * RING_SLOT_BYTES;
 __host__ __device__ constexpr int gemm_stages(int bn) {
-  return bn <= 64 ? 8 : (bn <= 160 ? 6 : 4);
+  return bn <= 64 ? 8 : (bn <= 128 ? 6 : (bn <= 160 ? 5 : 4));
 }
 __host__ __device__ constexpr int tmem_cols_for(int bn) {
   return 2 * bn <= 32 ? 32 : (2 * bn <= 64 ? 64 : (2 * bn <= 128 ? 128 : (2 * bn <= 256 ? 256 : 512)));
 }
 __host__ __device__ constexpr int gemm_smem_bytes(int bn) {
-  return gemm_stages(bn) * (A_STAGE_BYTES + bn * 128) + 1024 /*align slack*/ + 256 /*barriers*/;
+  return gemm_stages(bn) * (A_STAGE_BYTES + bn * 128) + RING_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
 }
+static_assert(gemm_smem_bytes(128) <= 232448 && gemm_smem_bytes(160) <= 232448 && gemm_smem_bytes(256) <= 232448 &&
+              gemm_smem_bytes(64) <= 232448, "shared memory budget");
 
 struct alignas(64) GemmKParams {
   CUtensorMap tmA[B200SD_MAX_SEG];
   CUtensorMap tmB[B200SD_MAX_SEG];
+  CUtensorMap tmC;  // output    (staged epilogue: 32-column boxes, SWIZZLE_64B)
+  CUtensorMap tmR;  // residual  (same geometry)
+  int staged;       // 1: epilogue goes registers -> swizzled smem ring -> TMA store (residual arrives by TMA load)
   int nseg;
   int seg_cb[B200SD_MAX_SEG];        // 64-wide channel blocks per tap
   int seg_taps[B200SD_MAX_SEG];
@@ -211,6 +219,48 @@ __device__ __forceinline__ void epilogue_store16(const GemmKParams& p, const Row
   }
 }
 
+// alpha, bias, row bias, time-embedding row vector, SiLU on 16 consecutive columns [n, n+16) — no residual, no store
+__device__ __forceinline__ void epilogue_math16(const GemmKParams& p, const RowInfo& ri, int n, float (&v)[16]) {
+  const int flags = p.flags;
+  const bool full = (n + 16 <= p.N);
+#pragma unroll
+  for (int j = 0; j < 16; ++j) v[j] *= p.alpha;
+  if (n >= p.N) return;
+  if (flags & B200SD_GEMM_BIAS) {
+    if (full) {
+      const float4* b4 = reinterpret_cast<const float4*>(p.bias + n);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        float4 b = __ldg(b4 + j);
+        v[4 * j + 0] += b.x; v[4 * j + 1] += b.y; v[4 * j + 2] += b.z; v[4 * j + 3] += b.w;
+      }
+    } else {
+      for (int j = 0; j < 16; ++j) if (n + j < p.N) v[j] += __ldg(p.bias + n + j);
+    }
+  }
+  if (ri.valid && (flags & B200SD_GEMM_BIAS_ROW)) {
+    float b = __ldg(p.bias + ri.m);
+#pragma unroll
+    for (int j = 0; j < 16; ++j) v[j] += b;
+  }
+  if (ri.valid && (flags & B200SD_GEMM_ROWVEC)) {
+    const float* rv = p.rowvec + static_cast<long long>(ri.group) * p.ld_rowvec + n;
+    if (full) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        float4 b = __ldg(reinterpret_cast<const float4*>(rv) + j);
+        v[4 * j + 0] += b.x; v[4 * j + 1] += b.y; v[4 * j + 2] += b.z; v[4 * j + 3] += b.w;
+      }
+    } else {
+      for (int j = 0; j < 16; ++j) if (n + j < p.N) v[j] += __ldg(rv + j);
+    }
+  }
+  if (flags & B200SD_GEMM_SILU) {
+#pragma unroll
+    for (int j = 0; j < 16; ++j) v[j] = silu_f(v[j]);
+  }
+}
+
 // GEGLU epilogue: h and g are the matching 16-column chunks of the two halves of an N tile; `n` is the
 // output column (N_out = N/2).  Reference: diffusers GEGLU = proj(x).chunk(2) -> h * gelu(g).
 __device__ __forceinline__ void epilogue_geglu16(const GemmKParams& p, const RowInfo& ri, int n_h, int n_g, int n_out,
@@ -246,11 +296,13 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + NSTAGE * STAGE_BYTES);
+  uint8_t* ring = smem + NSTAGE * STAGE_BYTES;  // epilogue staging ring (1 KiB aligned: stages are multiples of 1 KiB)
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(ring + RING_BYTES);
   uint64_t* empty_bar = full_bar + NSTAGE;
   uint64_t* tfull_bar = empty_bar + NSTAGE;
   uint64_t* tempty_bar = tfull_bar + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+  uint64_t* res_bar = tempty_bar + 2;  // [RING_SLOTS] residual sub-tile landed
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(res_bar + RING_SLOTS);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -264,6 +316,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
       mbar_init(&tfull_bar[i], 1);
       mbar_init(&tempty_bar[i], 128);
     }
+    for (int i = 0; i < RING_SLOTS; ++i) mbar_init(&res_bar[i], 1);
     fence_barrier_init();
   }
   if (warp == 1) {
@@ -275,6 +328,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
       tma_prefetch_desc(&p.tmA[s]);
       tma_prefetch_desc(&p.tmB[s]);
     }
+    if (p.staged) { tma_prefetch_desc(&p.tmC); tma_prefetch_desc(&p.tmR); }
   }
   tc_fence_before();
   __syncthreads();
@@ -357,6 +411,98 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
     const int r = q * 32 + lane;
     int acc = 0;
     uint32_t acc_phase = 0;
+    if (p.staged) {
+      // ---- staged epilogue: 32-column sub-tiles through a 4-slot swizzled smem ring; the residual sub-tile is
+      // prefetched by TMA two sub-tiles ahead, results leave by TMA store (coalesced, OOB rows/columns clipped).
+      const bool elected = (warp == 2 && lane == 0);
+      const bool geglu = (p.flags & B200SD_GEMM_GEGLU) != 0;
+      const bool has_res = (p.flags & B200SD_GEMM_RESIDUAL) != 0;
+      const int bn_out = geglu ? BN / 2 : BN;
+      const int nsub = bn_out / 32;
+      const int sw = (r >> 1) & 3;  // SWIZZLE_64B: 16-byte chunk index ^= (row / 2) % 4
+      auto issue_residual = [&](int qq) {
+        const int k = qq / nsub, sub = qq - k * nsub;
+        const long long w2 = static_cast<long long>(blockIdx.x) + static_cast<long long>(k) * gridDim.x;
+        if (w2 >= total_work) return;
+        const TileCoord tt = decode_work(p, static_cast<int>(w2));
+        const int slot = qq % RING_SLOTS;
+        mbar_arrive_expect_tx(&res_bar[slot], RING_SLOT_BYTES);
+        const int col0 = tt.nt * bn_out + sub * 32;
+        if (p.spatial) tma_load_4d(ring + slot * RING_SLOT_BYTES, &p.tmR, &res_bar[slot], col0, tt.w0, tt.h0, tt.n0);
+        else tma_load_2d(ring + slot * RING_SLOT_BYTES, &p.tmR, &res_bar[slot], col0, tt.m0);
+      };
+      int qseq = 0;
+      if (elected && has_res) { issue_residual(0); issue_residual(1); }
+      for (int work = blockIdx.x; work < total_work; work += gridDim.x) {
+        const TileCoord t = decode_work(p, work);
+        const RowInfo ri = row_info(p, t, r);
+        mbar_wait(&tfull_bar[acc], acc_phase);
+        tc_fence_after();
+        const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN;
+#pragma unroll 1
+        for (int sub = 0; sub < nsub; ++sub, ++qseq) {
+          const int slot = qseq % RING_SLOTS;
+          uint8_t* srow = ring + slot * RING_SLOT_BYTES + r * 64;
+          if (elected) {
+            bulk_wait_group_read<1>();  // every store but the latest has released its slot
+            if (has_res) issue_residual(qseq + 2);
+          }
+          if (has_res) mbar_wait(&res_bar[slot], (qseq / RING_SLOTS) & 1);
+#pragma unroll
+          for (int c2 = 0; c2 < 2; ++c2) {
+            float v[16];
+            if (geglu) {
+              uint32_t uh[16], ug[16];
+              tmem_ld16(taddr + sub * 32 + c2 * 16, uh);
+              tmem_ld16(taddr + BN / 2 + sub * 32 + c2 * 16, ug);
+              tmem_ld_wait();
+              const int n_h = t.nt * BN + sub * 32 + c2 * 16, n_g = n_h + BN / 2;
+#pragma unroll
+              for (int j = 0; j < 16; ++j) {
+                float hh = __uint_as_float(uh[j]) * p.alpha, gg = __uint_as_float(ug[j]) * p.alpha;
+                if (p.flags & B200SD_GEMM_BIAS) { hh += __ldg(p.bias + n_h + j); gg += __ldg(p.bias + n_g + j); }
+                v[j] = hh * gelu_erf_f(gg);
+              }
+            } else {
+              uint32_t u[16];
+              tmem_ld16(taddr + sub * 32 + c2 * 16, u);
+              tmem_ld_wait();
+#pragma unroll
+              for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(u[j]);
+              epilogue_math16(p, ri, t.nt * BN + sub * 32 + c2 * 16, v);
+            }
+            uint4* c0p = reinterpret_cast<uint4*>(srow + (((c2 * 2 + 0) ^ sw) * 16));
+            uint4* c1p = reinterpret_cast<uint4*>(srow + (((c2 * 2 + 1) ^ sw) * 16));
+            if (has_res) {
+              const uint4 r0 = *c0p, r1 = *c1p;
+              const uint32_t w[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                const float2 f = unpack_bf16x2(w[j]);
+                v[2 * j] += f.x; v[2 * j + 1] += f.y;
+              }
+            }
+            *c0p = make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
+            *c1p = make_uint4(pack_bf16x2(v[8], v[9]), pack_bf16x2(v[10], v[11]), pack_bf16x2(v[12], v[13]), pack_bf16x2(v[14], v[15]));
+          }
+          if (sub == nsub - 1) {  // accumulator fully read: hand the TMEM buffer back to the MMA warp
+            tc_fence_before();
+            mbar_arrive(&tempty_bar[acc]);
+          }
+          fence_proxy_async_smem();
+          named_bar_sync(1, 128);
+          if (elected) {
+            const int col0 = t.nt * bn_out + sub * 32;
+            if (p.spatial) tma_store_4d(&p.tmC, ring + slot * RING_SLOT_BYTES, col0, t.w0, t.h0, t.n0);
+            else tma_store_2d(&p.tmC, ring + slot * RING_SLOT_BYTES, col0, t.m0);
+            bulk_commit_group();
+          }
+        }
+        acc ^= 1;
+        if (acc == 0) acc_phase ^= 1;
+      }
+      if (elected) bulk_wait_group<0>();
+    } else
     for (int work = blockIdx.x; work < total_work; work += gridDim.x) {
       const TileCoord t = decode_work(p, work);
       const RowInfo ri = row_info(p, t, r);
@@ -685,6 +831,36 @@ int plan_gemm(const b200sd_gemm& g, PlannedOp* out) {
                   (long long)g.workspace_bytes);
     }
     kp.partial = static_cast<float*>(g.workspace);
+  }
+  // ---- staged (TMA-store) epilogue when the output is a plain bf16 tile grid --------------------------------
+  {
+    const bool geglu = (g.flags & B200SD_GEMM_GEGLU) != 0;
+    const int n_out = geglu ? g.N / 2 : g.N;
+    const int bn_out = geglu ? bn / 2 : bn;
+    const bool identity = !g.spatial || (kp.OH == g.H && kp.OW == g.W && kp.sy == 1 && kp.sx == 1 && kp.oy == 0 && kp.ox == 0);
+    const bool res = (g.flags & B200SD_GEMM_RESIDUAL) != 0;
+    bool ok = t.splits == 1 && !(g.flags & B200SD_GEMM_OUT_F32) && bn >= 64 && bn_out % 32 == 0 && g.ldc % 8 == 0 &&
+              (reinterpret_cast<uintptr_t>(g.out) & 15) == 0 && identity && n_out >= 32;
+    if (res) ok = ok && g.ldr % 8 == 0 && (reinterpret_cast<uintptr_t>(g.residual) & 15) == 0;
+    kp.staged = 0;
+    if (ok) {
+      auto make = [&](CUtensorMap* m, const void* base, long long ld) {
+        if (g.spatial) {
+          uint64_t dims[4] = {(uint64_t)n_out, (uint64_t)g.W, (uint64_t)g.H, (uint64_t)g.NB};
+          uint64_t st[3] = {(uint64_t)ld * 2, (uint64_t)g.W * ld * 2, (uint64_t)g.H * g.W * ld * 2};
+          uint32_t box[4] = {32, 1u << t.bw_log2, 1u << t.bh_log2, 1u << t.bn_log2};
+          return encode_tensor_map_bf16(m, base, 4, dims, st, box, 64);
+        }
+        uint64_t dims[2] = {(uint64_t)n_out, (uint64_t)g.M};
+        uint64_t st[1] = {(uint64_t)ld * 2};
+        uint32_t box[2] = {32, BM};
+        return encode_tensor_map_bf16(m, base, 2, dims, st, box, 64);
+      };
+      rc = make(&kp.tmC, g.out, g.ldc);
+      if (!rc) rc = make(&kp.tmR, res ? g.residual : g.out, res ? g.ldr : g.ldc);
+      if (rc) { delete pl; return rc; }
+      kp.staged = 1;
+    }
   }
   pl->block_n = bn;
   rc = prepare_gemm(bn);

@@ -33,7 +33,7 @@ int fail(int status, const char* fmt, ...);
 // ---- TMA tensor-map encoding through the driver entry point (no link-time libcuda dependency) --------
 // dims/strides innermost first; strides_bytes has rank-1 entries (dim 0 is contiguous).
 int encode_tensor_map_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims,
-                           const uint64_t* strides_bytes, const uint32_t* box);
+                           const uint64_t* strides_bytes, const uint32_t* box, int swizzle_bytes = 128);
 
 // ---- planned ops -------------------------------------------------------------------------------------
 struct PlannedOp {

@@ -56,8 +56,11 @@ static EncodeTiledFn get_encode_fn() {
 }
 
 int encode_tensor_map_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims,
-                           const uint64_t* strides_bytes, const uint32_t* box) {
+                           const uint64_t* strides_bytes, const uint32_t* box, int swizzle_bytes) {
   EncodeTiledFn fn = get_encode_fn();
+  CUtensorMapSwizzle sw = swizzle_bytes == 128 ? CU_TENSOR_MAP_SWIZZLE_128B
+                          : swizzle_bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B
+                          : swizzle_bytes == 32 ? CU_TENSOR_MAP_SWIZZLE_32B : CU_TENSOR_MAP_SWIZZLE_NONE;
   if (!fn) return fail(B200SD_ERR_NO_DEVICE, "cuTensorMapEncodeTiled unavailable (no CUDA driver): there is no CPU fallback");
   cuuint64_t gdim[5];
   cuuint64_t gstr[4];
@@ -74,7 +77,7 @@ int encode_tensor_map_bf16(CUtensorMap* out, const void* base, int rank, const u
     if (strides_bytes[i] % 16 != 0) return fail(B200SD_ERR_INVALID, "tensor map: stride[%d]=%llu not a multiple of 16 bytes", i, (unsigned long long)strides_bytes[i]);
   }
   CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, static_cast<cuuint32_t>(rank), const_cast<void*>(base), gdim, gstr,
-                  bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     std::string d;
