@@ -13,6 +13,7 @@ with CFG, DDIM 50 steps; data-parallel over the GPUs = independent prompt shards
 Synthetic prompts (random embeddings) and random-init weights of the named architecture: no network here.
 """
 import argparse
+import contextlib
 import json
 import os
 import subprocess
@@ -178,7 +179,8 @@ def run_b200(args, wl, rank, world, local_rank):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     model = SDModelWrapper.from_random(model_type, seed=0, device=str(dev))
-    model.set_scheduler(sampler)
+    with contextlib.redirect_stdout(sys.stderr):   # the wrapper mirrors the reference's print(); stdout carries ONE JSON line
+        model.set_scheduler(sampler)
     pipe = StableDiffusionUnifiedPipeline(do_cfg=True, device=str(dev))
     # every rank owns an independent prompt shard (weak scaling: B images per GPU); inputs differ per rank
     inp = synth_inputs(model_type, B, H, W, seed=1 + rank)

@@ -267,6 +267,34 @@ def test_attention(cuda_device, B, heads, Nq, Nkv, d):
     _check(out, ref, rtol=2 ** -6, atol_scale=2 ** -7, name=f"attention B{B} h{heads} {Nq}x{Nkv} d{d}")
 
 
+@pytest.mark.parametrize("Nkv,d", [(1024, 40), (1000, 64), (512, 80), (384, 160)])
+def test_attention_growing_scores(cuda_device, Nkv, d):
+    """Keys whose scores grow with the key index (and a few huge outliers late in the sequence): every KV block
+    outgrows the running softmax reference by far more than the lazy-rescale threshold, so the kernel's
+    redo-with-exact-max + O-rescale path runs on every block."""
+    dev = cuda_device
+    B, heads, Nq = 1, 4, 256
+    C = heads * d
+    q = _bf(torch.ones((B, Nq, C), device=dev) + 0.25 * _randn((B, Nq, C), dev, 1))
+    ramp = torch.linspace(0.0, 6.0, Nkv, device=dev).view(1, Nkv, 1)
+    k = _randn((B, Nkv, C), dev, 2) * 0.25 + ramp
+    k[:, Nkv - 37] += 3.0
+    k[:, Nkv // 2 + 5] += 2.0
+    k = _bf(k)
+    v = _bf(_randn((B, Nkv, C), dev, 3))
+    scale = d ** -0.5
+    b = _builder(dev)
+    out = b.attention(q, k, v, heads, d, scale)
+    _run(b)
+
+    def split(t, n):
+        return t.float().view(B, n, heads, d).transpose(1, 2)
+
+    ref = F.scaled_dot_product_attention(split(q, Nq), split(k, Nkv), split(v, Nkv), scale=scale)
+    ref = ref.transpose(1, 2).reshape(B, Nq, C)
+    _check(out, ref, rtol=2 ** -6, atol_scale=2 ** -7, name=f"attention growing scores Nkv{Nkv} d{d}")
+
+
 def test_attention_fused_qkv_views(cuda_device):
     dev = cuda_device
     B, heads, Nn, d = 2, 8, 1024, 80

@@ -60,7 +60,7 @@ ln("ln_65536x320", 65536, 320)
 flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 out = []
 for name, mk, flops, bytes_ in cases:
-    if a.only and a.only not in name:
+    if a.only and not any(o in name for o in a.only.split(',')):
         continue
     b = Builder(dev)
     mk(b)
