@@ -120,7 +120,7 @@ typedef struct b200sd_gemm {
   void* workspace;        /* fp32 split-K partials (may be NULL when splits==1)                           */
   int64_t workspace_bytes;
   int32_t block_n;        /* 0 = auto; else one of 32, 64, 128, 160, 256                                  */
-  int32_t pad_;
+  int32_t cta_pair;       /* 0 = auto; 1 = one CTA per 128-row tile; 2 = CTA pair (cta_group::2) per 256 rows */
 } b200sd_gemm;
 
 /* ---- GroupNorm (+SiLU) ---------------------------------------------------------------------------- */

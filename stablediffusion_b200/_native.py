@@ -55,7 +55,7 @@ class Gemm(C.Structure):
         ("bias", C.c_void_p), ("rowvec", C.c_void_p), ("ld_rowvec", C.c_int64),
         ("rows_per_group", C.c_int32), ("flags", C.c_int32), ("residual", C.c_void_p), ("ldr", C.c_int64),
         ("alpha", C.c_float), ("splits", C.c_int32), ("workspace", C.c_void_p), ("workspace_bytes", C.c_int64),
-        ("block_n", C.c_int32), ("pad_", C.c_int32),
+        ("block_n", C.c_int32), ("cta_pair", C.c_int32),
     ]
 
 

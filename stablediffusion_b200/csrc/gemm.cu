@@ -25,25 +25,33 @@ namespace b200sd {
 
 namespace {
 
-constexpr int BM = 128;
+constexpr int BM = 128;                     // rows per CTA tile (a CTA pair computes 256 x BN)
 constexpr int BK = 64;
 constexpr int A_STAGE_BYTES = BM * BK * 2;  // 16 KiB
-constexpr int GEMM_THREADS = 192;
+constexpr int GEMM_THREADS = 320;           // warp 0 TMA producer, warp 1 MMA issuer, warps 2-9 epilogue (2 per TMEM quadrant)
+constexpr int EPI_THREADS = 256;
 
-constexpr int RING_SLOTS = 4;              // epilogue staging ring: 4 x [128 rows x 32 bf16 columns] (SWIZZLE_64B)
+constexpr int RING_SLOTS = 8;              // epilogue staging ring: 8 x [128 rows x 32 bf16 columns] (SWIZZLE_64B)
 constexpr int RING_SLOT_BYTES = BM * 64;   // 8 KiB
 constexpr int RING_BYTES = RING_SLOTS * RING_SLOT_BYTES;
-__host__ __device__ constexpr int gemm_stages(int bn) {
-  return bn <= 64 ? 8 : (bn <= 128 ? 6 : (bn <= 160 ? 5 : 4));
+constexpr int RES_AHEAD = 4;               // residual sub-tiles in flight ahead of the epilogue (2 per warp group)
+constexpr int GEMM_SMEM_LIMIT = 232448;
+// per-CTA bytes of one pipeline stage: 128 rows of A, BN (one CTA) or BN/2 (CTA pair: each CTA holds half of B) rows of W
+__host__ __device__ constexpr int gemm_stage_bytes(int bn, int ncta) { return A_STAGE_BYTES + (bn / ncta) * 128; }
+__host__ __device__ constexpr int gemm_fixed_bytes(int bn) {
+  return RING_BYTES + 2 * bn * 4 /*bias, one row per accumulator*/ + 1024 /*align slack*/ + 512 /*barriers*/;
+}
+__host__ __device__ constexpr int gemm_stages(int bn, int ncta) {
+  int s = (GEMM_SMEM_LIMIT - gemm_fixed_bytes(bn)) / gemm_stage_bytes(bn, ncta);
+  return s > 8 ? 8 : s;
 }
 __host__ __device__ constexpr int tmem_cols_for(int bn) {
   return 2 * bn <= 32 ? 32 : (2 * bn <= 64 ? 64 : (2 * bn <= 128 ? 128 : (2 * bn <= 256 ? 256 : 512)));
 }
-__host__ __device__ constexpr int gemm_smem_bytes(int bn) {
-  return gemm_stages(bn) * (A_STAGE_BYTES + bn * 128) + RING_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+__host__ __device__ constexpr int gemm_smem_bytes(int bn, int ncta) {
+  return gemm_stages(bn, ncta) * gemm_stage_bytes(bn, ncta) + gemm_fixed_bytes(bn);
 }
-static_assert(gemm_smem_bytes(128) <= 232448 && gemm_smem_bytes(160) <= 232448 && gemm_smem_bytes(256) <= 232448 &&
-              gemm_smem_bytes(64) <= 232448, "shared memory budget");
+static_assert(gemm_stages(256, 1) >= 3 && gemm_stages(160, 1) >= 4 && gemm_stages(256, 2) >= 4, "pipeline depth");
 
 struct alignas(64) GemmKParams {
   CUtensorMap tmA[B200SD_MAX_SEG];
@@ -65,6 +73,8 @@ struct alignas(64) GemmKParams {
   int bw_log2, bh_log2, bn_log2;
   int tiles_w, tiles_h, tiles_nb;
   int num_m_tiles, num_n_tiles;
+  int ncta;         // 1: one CTA per 128 x BN tile; 2: CTA pair (cluster of 2, tcgen05 cta_group::2) per 256 x BN tile
+  int num_pm;       // ceil(num_m_tiles / ncta): M tiles of the work decomposition
   // epilogue
   void* out;
   long long ldc;
@@ -86,18 +96,15 @@ struct TileCoord {
   int w0, h0, n0;  // spatial
 };
 
-__device__ __forceinline__ TileCoord decode_work(const GemmKParams& p, int work) {
+__device__ __forceinline__ TileCoord decode_tile(const GemmKParams& p, int mt, int nt, int ks) {
   TileCoord t;
-  t.mt = work % p.num_m_tiles;
-  int rest = work / p.num_m_tiles;
-  t.nt = rest % p.num_n_tiles;
-  t.ks = rest / p.num_n_tiles;
+  t.mt = mt; t.nt = nt; t.ks = ks;
   t.m0 = t.mt * BM;
   if (p.spatial) {
     int tw = t.mt % p.tiles_w;
     int r2 = t.mt / p.tiles_w;
     int th = r2 % p.tiles_h;
-    int tn = r2 / p.tiles_h;
+    int tn = r2 / p.tiles_h;  // >= tiles_nb for the phantom tile of an odd pair: every row out of bounds
     t.w0 = tw << p.bw_log2;
     t.h0 = th << p.bh_log2;
     t.n0 = tn << p.bn_log2;
@@ -105,6 +112,12 @@ __device__ __forceinline__ TileCoord decode_work(const GemmKParams& p, int work)
     t.w0 = t.h0 = t.n0 = 0;
   }
   return t;
+}
+// work item -> tile of CTA `rank` of the pair (M fastest: CTAs running together share the weight tile in L2)
+__device__ __forceinline__ TileCoord decode_work(const GemmKParams& p, int work, int rank) {
+  const int pm = work % p.num_pm;
+  const int rest = work / p.num_pm;
+  return decode_tile(p, pm * p.ncta + rank, rest % p.num_n_tiles, rest / p.num_n_tiles);
 }
 
 struct RowInfo {
@@ -219,45 +232,30 @@ __device__ __forceinline__ void epilogue_store16(const GemmKParams& p, const Row
   }
 }
 
-// alpha, bias, row bias, time-embedding row vector, SiLU on 16 consecutive columns [n, n+16) — no residual, no store
-__device__ __forceinline__ void epilogue_math16(const GemmKParams& p, const RowInfo& ri, int n, float (&v)[16]) {
+// row bias, time-embedding row vector, SiLU on 32 consecutive columns [n, n+32) (alpha and bias already applied)
+__device__ __forceinline__ void epilogue_extra32(const GemmKParams& p, const RowInfo& ri, int n, float (&v)[32]) {
   const int flags = p.flags;
-  const bool full = (n + 16 <= p.N);
-#pragma unroll
-  for (int j = 0; j < 16; ++j) v[j] *= p.alpha;
-  if (n >= p.N) return;
-  if (flags & B200SD_GEMM_BIAS) {
-    if (full) {
-      const float4* b4 = reinterpret_cast<const float4*>(p.bias + n);
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        float4 b = __ldg(b4 + j);
-        v[4 * j + 0] += b.x; v[4 * j + 1] += b.y; v[4 * j + 2] += b.z; v[4 * j + 3] += b.w;
-      }
-    } else {
-      for (int j = 0; j < 16; ++j) if (n + j < p.N) v[j] += __ldg(p.bias + n + j);
-    }
-  }
   if (ri.valid && (flags & B200SD_GEMM_BIAS_ROW)) {
-    float b = __ldg(p.bias + ri.m);
+    const float b = __ldg(p.bias + ri.m);
 #pragma unroll
-    for (int j = 0; j < 16; ++j) v[j] += b;
+    for (int j = 0; j < 32; ++j) v[j] += b;
   }
-  if (ri.valid && (flags & B200SD_GEMM_ROWVEC)) {
+  if (ri.valid && (flags & B200SD_GEMM_ROWVEC) && n < p.N) {
     const float* rv = p.rowvec + static_cast<long long>(ri.group) * p.ld_rowvec + n;
-    if (full) {
+    if (n + 32 <= p.N) {
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        float4 b = __ldg(reinterpret_cast<const float4*>(rv) + j);
+      for (int j = 0; j < 8; ++j) {
+        const float4 b = __ldg(reinterpret_cast<const float4*>(rv) + j);
         v[4 * j + 0] += b.x; v[4 * j + 1] += b.y; v[4 * j + 2] += b.z; v[4 * j + 3] += b.w;
       }
     } else {
-      for (int j = 0; j < 16; ++j) if (n + j < p.N) v[j] += __ldg(rv + j);
+#pragma unroll
+      for (int j = 0; j < 32; ++j) if (n + j < p.N) v[j] += __ldg(rv + j);
     }
   }
   if (flags & B200SD_GEMM_SILU) {
 #pragma unroll
-    for (int j = 0; j < 16; ++j) v[j] = silu_f(v[j]);
+    for (int j = 0; j < 32; ++j) v[j] = silu_f(v[j]);
   }
 }
 
@@ -286,18 +284,20 @@ __device__ __forceinline__ void epilogue_geglu16(const GemmKParams& p, const Row
   reinterpret_cast<uint4*>(op)[1] = o1;
 }
 
-template <int BN>
+template <int BN, int NCTA>
 __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_constant__ GemmKParams p) {
-  constexpr int B_STAGE_BYTES = BN * 128;
+  constexpr int B_ROWS = BN / NCTA;                   // weight rows this CTA stages (a CTA pair splits the N tile)
+  constexpr int B_STAGE_BYTES = B_ROWS * 128;
   constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
-  constexpr int NSTAGE = gemm_stages(BN);
+  constexpr int NSTAGE = gemm_stages(BN, NCTA);
   constexpr int TMEM_COLS = tmem_cols_for(BN);
-  constexpr uint32_t IDESC = umma_idesc_bf16(BM, BN, 0);
+  constexpr uint32_t IDESC = umma_idesc_bf16(BM * NCTA, BN, 0);
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* ring = smem + NSTAGE * STAGE_BYTES;  // epilogue staging ring (1 KiB aligned: stages are multiples of 1 KiB)
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(ring + RING_BYTES);
+  float* bias_s = reinterpret_cast<float*>(ring + RING_BYTES);  // [2 accumulators][BN]
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(bias_s + 2 * BN);
   uint64_t* empty_bar = full_bar + NSTAGE;
   uint64_t* tfull_bar = empty_bar + NSTAGE;
   uint64_t* tempty_bar = tfull_bar + 2;
@@ -306,6 +306,9 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  const int rank = NCTA == 2 ? static_cast<int>(cluster_ctarank()) : 0;  // rank 0 = leader of the pair (issues the MMAs)
+  const int unit = blockIdx.x / NCTA;                                     // persistent work unit = CTA or CTA pair
+  const int num_units = gridDim.x / NCTA;
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < NSTAGE; ++i) {
@@ -314,14 +317,14 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tfull_bar[i], 1);
-      mbar_init(&tempty_bar[i], 128);
+      mbar_init(&tempty_bar[i], 8 * NCTA);  // one arrival per epilogue warp of every CTA that reads the accumulator
     }
     for (int i = 0; i < RING_SLOTS; ++i) mbar_init(&res_bar[i], 1);
     fence_barrier_init();
   }
   if (warp == 1) {
-    tmem_alloc(tmem_slot, TMEM_COLS);
-    tmem_relinquish();
+    if (NCTA == 2) { tmem_alloc_2cta(tmem_slot, TMEM_COLS); tmem_relinquish_2cta(); }
+    else { tmem_alloc(tmem_slot, TMEM_COLS); tmem_relinquish(); }
   }
   if (warp == 0 && lane == 0) {
     for (int s = 0; s < p.nseg; ++s) {
@@ -331,19 +334,19 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
     if (p.staged) { tma_prefetch_desc(&p.tmC); tma_prefetch_desc(&p.tmR); }
   }
   tc_fence_before();
-  __syncthreads();
+  if (NCTA == 2) cluster_sync_all(); else __syncthreads();  // barriers initialised cluster-wide before any remote arrive
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  const int total_work = p.num_m_tiles * p.num_n_tiles * p.splits;
+  const int total_work = p.num_pm * p.num_n_tiles * p.splits;
 
   if (warp == 0) {
-    // ===================== TMA producer (one lane) =====================
+    // ===================== TMA producer (one lane; in a pair BOTH CTAs load: own A rows, own half of W) =====================
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int work = blockIdx.x; work < total_work; work += gridDim.x) {
-        const TileCoord t = decode_work(p, work);
+      for (int work = unit; work < total_work; work += num_units) {
+        const TileCoord t = decode_work(p, work, rank);
         const int kb0 = t.ks * p.kb_per_split;
         const int kb1 = min(kb0 + p.kb_per_split, p.kb_total);
         int seg = 0;
@@ -353,16 +356,29 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
         int cb = local - tap * p.seg_cb[seg];
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
-          mbar_arrive_expect_tx(&full_bar[stage], STAGE_BYTES);
           uint8_t* sa = smem + stage * STAGE_BYTES;
           uint8_t* sb = sa + A_STAGE_BYTES;
-          if (p.spatial) {
-            tma_load_5d(sa, &p.tmA[seg], &full_bar[stage], cb * BK, t.w0 + p.tap_dw[seg][tap],
-                        t.h0 + p.tap_dh[seg][tap], t.n0, p.tap_phase[seg][tap]);
+          if (NCTA == 1) {
+            mbar_arrive_expect_tx(&full_bar[stage], STAGE_BYTES);
+            if (p.spatial) {
+              tma_load_5d(sa, &p.tmA[seg], &full_bar[stage], cb * BK, t.w0 + p.tap_dw[seg][tap],
+                          t.h0 + p.tap_dh[seg][tap], t.n0, p.tap_phase[seg][tap]);
+            } else {
+              tma_load_2d(sa, &p.tmA[seg], &full_bar[stage], cb * BK, t.m0);
+            }
+            tma_load_3d(sb, &p.tmB[seg], &full_bar[stage], cb * BK, tap, t.nt * BN);
           } else {
-            tma_load_2d(sa, &p.tmA[seg], &full_bar[stage], cb * BK, t.m0);
+            // the leader's full barrier collects the bytes of both CTAs (tx-count may go negative until it has armed)
+            if (rank == 0) mbar_arrive_expect_tx(&full_bar[stage], 2 * STAGE_BYTES);
+            const uint32_t fb = mapa_u32(smem_u32(&full_bar[stage]), 0);
+            if (p.spatial) {
+              tma_load_5d_2cta(sa, &p.tmA[seg], fb, cb * BK, t.w0 + p.tap_dw[seg][tap],
+                               t.h0 + p.tap_dh[seg][tap], t.n0, p.tap_phase[seg][tap]);
+            } else {
+              tma_load_2d_2cta(sa, &p.tmA[seg], fb, cb * BK, t.m0);
+            }
+            tma_load_3d_2cta(sb, &p.tmB[seg], fb, cb * BK, tap, t.nt * BN + rank * B_ROWS);
           }
-          tma_load_3d(sb, &p.tmB[seg], &full_bar[stage], cb * BK, tap, t.nt * BN);
           if (++stage == NSTAGE) { stage = 0; phase ^= 1; }
           if (++cb == p.seg_cb[seg]) {
             cb = 0;
@@ -372,129 +388,181 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
       }
     }
   } else if (warp == 1) {
-    // ===================== MMA issuer =====================
-    int stage = 0;
-    uint32_t phase = 0;
-    int acc = 0;
-    uint32_t acc_phase = 0;
-    for (int work = blockIdx.x; work < total_work; work += gridDim.x) {
-      const int ks = work / (p.num_m_tiles * p.num_n_tiles);
-      const int kb0 = ks * p.kb_per_split;
-      const int nkb = min(kb0 + p.kb_per_split, p.kb_total) - kb0;
-      mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
-      tc_fence_after();
-      const uint32_t d_tmem = tmem_base + acc * BN;
-      for (int i = 0; i < nkb; ++i) {
-        mbar_wait(&full_bar[stage], phase);
+    // ===================== MMA issuer (leader CTA only) =====================
+    if (rank == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (int work = unit; work < total_work; work += num_units) {
+        const int ks = work / (p.num_pm * p.num_n_tiles);
+        const int kb0 = ks * p.kb_per_split;
+        const int nkb = min(kb0 + p.kb_per_split, p.kb_total) - kb0;
+        mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
         tc_fence_after();
-        if (lane == 0) {
-          const uint32_t a_addr = smem_u32(smem + stage * STAGE_BYTES);
-          const uint32_t b_addr = a_addr + A_STAGE_BYTES;
+        const uint32_t d_tmem = tmem_base + acc * BN;
+        for (int i = 0; i < nkb; ++i) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          if (lane == 0) {
+            const uint32_t a_addr = smem_u32(smem + stage * STAGE_BYTES);
+            const uint32_t b_addr = a_addr + A_STAGE_BYTES;
 #pragma unroll
-          for (int k = 0; k < BK / 16; ++k) {
-            const uint64_t da = umma_smem_desc_sw128(a_addr + k * 32, 16, 1024);
-            const uint64_t db = umma_smem_desc_sw128(b_addr + k * 32, 16, 1024);
-            umma_bf16_ss(d_tmem, da, db, IDESC, (i | k) != 0 ? 1u : 0u);
+            for (int k = 0; k < BK / 16; ++k) {
+              const uint64_t da = umma_smem_desc_sw128(a_addr + k * 32, 16, 1024);
+              const uint64_t db = umma_smem_desc_sw128(b_addr + k * 32, 16, 1024);
+              if (NCTA == 2) umma_bf16_ss_2cta(d_tmem, da, db, IDESC, (i | k) != 0 ? 1u : 0u);
+              else umma_bf16_ss(d_tmem, da, db, IDESC, (i | k) != 0 ? 1u : 0u);
+            }
+            if (NCTA == 2) {
+              umma_commit_2cta(&empty_bar[stage], 3);   // frees the stage in both CTAs
+              if (i == nkb - 1) umma_commit_2cta(&tfull_bar[acc], 3);
+            } else {
+              umma_commit(&empty_bar[stage]);
+              if (i == nkb - 1) umma_commit(&tfull_bar[acc]);
+            }
           }
-          umma_commit(&empty_bar[stage]);
-          if (i == nkb - 1) umma_commit(&tfull_bar[acc]);
+          __syncwarp();
+          if (++stage == NSTAGE) { stage = 0; phase ^= 1; }
         }
-        __syncwarp();
-        if (++stage == NSTAGE) { stage = 0; phase ^= 1; }
+        acc ^= 1;
+        if (acc == 0) acc_phase ^= 1;
       }
-      acc ^= 1;
-      if (acc == 0) acc_phase ^= 1;
     }
   } else {
-    // ===================== epilogue warps (TMEM lane quadrant = warp % 4) =====================
+    // ===================== epilogue: 8 warps, two per TMEM lane quadrant (hardware rule: quadrant = warp_id % 4) ==========
+    // The two warp groups (warps 2-5, warps 6-9) take alternate 32-column sub-tiles of every accumulator, so the
+    // TMEM -> registers -> smem -> TMA-store chain of one sub-tile overlaps the next one's.
     const int q = warp & 3;
+    const int g = (warp - 2) >> 2;
     const int r = q * 32 + lane;
+    const int et = (warp - 2) * 32 + lane;  // 0..255
     int acc = 0;
     uint32_t acc_phase = 0;
+    auto release_acc = [&](int a) {  // this warp has read everything it needs from accumulator a
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) {
+        if (NCTA == 2) mbar_arrive_cluster(mapa_u32(smem_u32(&tempty_bar[a]), 0));
+        else mbar_arrive(&tempty_bar[a]);
+      }
+    };
     if (p.staged) {
-      // ---- staged epilogue: 32-column sub-tiles through a 4-slot swizzled smem ring; the residual sub-tile is
-      // prefetched by TMA two sub-tiles ahead, results leave by TMA store (coalesced, OOB rows/columns clipped).
-      const bool elected = (warp == 2 && lane == 0);
+      // ---- staged epilogue: sub-tiles go through an 8-slot swizzled smem ring; the residual sub-tile is prefetched by
+      // TMA RES_AHEAD sub-tiles ahead into the slot it is added in, results leave by TMA store (coalesced, OOB clipped).
+      const bool elected = (warp == 2 + 4 * g && lane == 0);
       const bool geglu = (p.flags & B200SD_GEMM_GEGLU) != 0;
       const bool has_res = (p.flags & B200SD_GEMM_RESIDUAL) != 0;
+      const bool has_bias = (p.flags & B200SD_GEMM_BIAS) != 0;
+      const bool extra = (p.flags & (B200SD_GEMM_BIAS_ROW | B200SD_GEMM_ROWVEC | B200SD_GEMM_SILU)) != 0;
       const int bn_out = geglu ? BN / 2 : BN;
       const int nsub = bn_out / 32;
       const int sw = (r >> 1) & 3;  // SWIZZLE_64B: 16-byte chunk index ^= (row / 2) % 4
       auto issue_residual = [&](int qq) {
         const int k = qq / nsub, sub = qq - k * nsub;
-        const long long w2 = static_cast<long long>(blockIdx.x) + static_cast<long long>(k) * gridDim.x;
+        const long long w2 = static_cast<long long>(unit) + static_cast<long long>(k) * num_units;
         if (w2 >= total_work) return;
-        const TileCoord tt = decode_work(p, static_cast<int>(w2));
+        const TileCoord tt = decode_work(p, static_cast<int>(w2), rank);
         const int slot = qq % RING_SLOTS;
         mbar_arrive_expect_tx(&res_bar[slot], RING_SLOT_BYTES);
         const int col0 = tt.nt * bn_out + sub * 32;
         if (p.spatial) tma_load_4d(ring + slot * RING_SLOT_BYTES, &p.tmR, &res_bar[slot], col0, tt.w0, tt.h0, tt.n0);
         else tma_load_2d(ring + slot * RING_SLOT_BYTES, &p.tmR, &res_bar[slot], col0, tt.m0);
       };
-      int qseq = 0;
-      if (elected && has_res) { issue_residual(0); issue_residual(1); }
-      for (int work = blockIdx.x; work < total_work; work += gridDim.x) {
-        const TileCoord t = decode_work(p, work);
+      if (elected && has_res) {
+        for (int qq = g; qq < RES_AHEAD; qq += 2) issue_residual(qq);
+      }
+      int qbase = 0;
+      for (int work = unit; work < total_work; work += num_units, qbase += nsub) {
+        const TileCoord t = decode_work(p, work, rank);
         const RowInfo ri = row_info(p, t, r);
+        const bool tile_exists = t.mt < p.num_m_tiles;
+        float* bs = bias_s + acc * BN;
+        if (has_bias) {  // bias row of this N tile -> smem while the MMAs of the tile are still running
+          for (int i = et; i < BN; i += EPI_THREADS) {
+            const int n = t.nt * BN + i;
+            bs[i] = n < p.N ? __ldg(p.bias + n) : 0.f;
+          }
+        }
+        named_bar_sync(3, EPI_THREADS);
+        int my_last = -1;
+        for (int sub = 0; sub < nsub; ++sub) if (((qbase + sub) & 1) == g) my_last = sub;
         mbar_wait(&tfull_bar[acc], acc_phase);
         tc_fence_after();
         const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN;
+        if (my_last < 0) release_acc(acc);
 #pragma unroll 1
-        for (int sub = 0; sub < nsub; ++sub, ++qseq) {
-          const int slot = qseq % RING_SLOTS;
+        for (int sub = 0; sub < nsub; ++sub) {
+          const int qq = qbase + sub;
+          if ((qq & 1) != g) continue;
+          const int slot = qq % RING_SLOTS;
           uint8_t* srow = ring + slot * RING_SLOT_BYTES + r * 64;
           if (elected) {
-            bulk_wait_group_read<1>();  // every store but the latest has released its slot
-            if (has_res) issue_residual(qseq + 2);
+            bulk_wait_group_read<1>();  // every store of this group but the latest has released its slot
+            if (has_res) issue_residual(qq + RES_AHEAD);
           }
-          if (has_res) mbar_wait(&res_bar[slot], (qseq / RING_SLOTS) & 1);
+          float v[32];
+          if (geglu) {
+            uint32_t uh[32], ug[32];
+            tmem_ld32(taddr + sub * 32, uh);
+            tmem_ld32(taddr + BN / 2 + sub * 32, ug);
+            tmem_ld_wait();
+            const float* bh = bs + sub * 32;
+            const float* bg = bh + BN / 2;
 #pragma unroll
-          for (int c2 = 0; c2 < 2; ++c2) {
-            float v[16];
-            if (geglu) {
-              uint32_t uh[16], ug[16];
-              tmem_ld16(taddr + sub * 32 + c2 * 16, uh);
-              tmem_ld16(taddr + BN / 2 + sub * 32 + c2 * 16, ug);
-              tmem_ld_wait();
-              const int n_h = t.nt * BN + sub * 32 + c2 * 16, n_g = n_h + BN / 2;
-#pragma unroll
-              for (int j = 0; j < 16; ++j) {
-                float hh = __uint_as_float(uh[j]) * p.alpha, gg = __uint_as_float(ug[j]) * p.alpha;
-                if (p.flags & B200SD_GEMM_BIAS) { hh += __ldg(p.bias + n_h + j); gg += __ldg(p.bias + n_g + j); }
-                v[j] = hh * gelu_erf_f(gg);
-              }
-            } else {
-              uint32_t u[16];
-              tmem_ld16(taddr + sub * 32 + c2 * 16, u);
-              tmem_ld_wait();
-#pragma unroll
-              for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(u[j]);
-              epilogue_math16(p, ri, t.nt * BN + sub * 32 + c2 * 16, v);
+            for (int j = 0; j < 32; ++j) {
+              float hh = __uint_as_float(uh[j]) * p.alpha, gg = __uint_as_float(ug[j]) * p.alpha;
+              if (has_bias) { hh += bh[j]; gg += bg[j]; }
+              v[j] = hh * gelu_erf_f(gg);
             }
-            uint4* c0p = reinterpret_cast<uint4*>(srow + (((c2 * 2 + 0) ^ sw) * 16));
-            uint4* c1p = reinterpret_cast<uint4*>(srow + (((c2 * 2 + 1) ^ sw) * 16));
-            if (has_res) {
-              const uint4 r0 = *c0p, r1 = *c1p;
-              const uint32_t w[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
+          } else {
+            uint32_t u[32];
+            tmem_ld32(taddr + sub * 32, u);
+            tmem_ld_wait();
+            if (p.alpha != 1.0f) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(u[j]) * p.alpha;
+            } else {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(u[j]);
+            }
+            if (has_bias) {
+              const float4* b4 = reinterpret_cast<const float4*>(bs + sub * 32);
 #pragma unroll
               for (int j = 0; j < 8; ++j) {
-                const float2 f = unpack_bf16x2(w[j]);
-                v[2 * j] += f.x; v[2 * j + 1] += f.y;
+                const float4 b = b4[j];
+                v[4 * j + 0] += b.x; v[4 * j + 1] += b.y; v[4 * j + 2] += b.z; v[4 * j + 3] += b.w;
               }
             }
-            *c0p = make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
-            *c1p = make_uint4(pack_bf16x2(v[8], v[9]), pack_bf16x2(v[10], v[11]), pack_bf16x2(v[12], v[13]), pack_bf16x2(v[14], v[15]));
+            if (extra) epilogue_extra32(p, ri, t.nt * BN + sub * 32, v);
           }
-          if (sub == nsub - 1) {  // accumulator fully read: hand the TMEM buffer back to the MMA warp
-            tc_fence_before();
-            mbar_arrive(&tempty_bar[acc]);
+          if (sub == my_last) release_acc(acc);  // accumulator fully read by this warp: hand it back to the MMA warp
+          if (has_res) {
+            mbar_wait(&res_bar[slot], (qq / RING_SLOTS) & 1);
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+              const uint4 rr = *reinterpret_cast<const uint4*>(srow + ((c ^ sw) * 16));
+              const uint32_t w[4] = {rr.x, rr.y, rr.z, rr.w};
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                const float2 f = unpack_bf16x2(w[j]);
+                v[8 * c + 2 * j] += f.x; v[8 * c + 2 * j + 1] += f.y;
+              }
+            }
           }
+#pragma unroll
+          for (int c = 0; c < 4; ++c)
+            *reinterpret_cast<uint4*>(srow + ((c ^ sw) * 16)) =
+                make_uint4(pack_bf16x2(v[8 * c], v[8 * c + 1]), pack_bf16x2(v[8 * c + 2], v[8 * c + 3]),
+                           pack_bf16x2(v[8 * c + 4], v[8 * c + 5]), pack_bf16x2(v[8 * c + 6], v[8 * c + 7]));
           fence_proxy_async_smem();
-          named_bar_sync(1, 128);
+          named_bar_sync(1 + g, 128);
           if (elected) {
-            const int col0 = t.nt * bn_out + sub * 32;
-            if (p.spatial) tma_store_4d(&p.tmC, ring + slot * RING_SLOT_BYTES, col0, t.w0, t.h0, t.n0);
-            else tma_store_2d(&p.tmC, ring + slot * RING_SLOT_BYTES, col0, t.m0);
+            if (tile_exists) {
+              const int col0 = t.nt * bn_out + sub * 32;
+              if (p.spatial) tma_store_4d(&p.tmC, ring + slot * RING_SLOT_BYTES, col0, t.w0, t.h0, t.n0);
+              else tma_store_2d(&p.tmC, ring + slot * RING_SLOT_BYTES, col0, t.m0);
+            }
             bulk_commit_group();
           }
         }
@@ -502,63 +570,70 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
         if (acc == 0) acc_phase ^= 1;
       }
       if (elected) bulk_wait_group<0>();
-    } else
-    for (int work = blockIdx.x; work < total_work; work += gridDim.x) {
-      const TileCoord t = decode_work(p, work);
-      const RowInfo ri = row_info(p, t, r);
-      mbar_wait(&tfull_bar[acc], acc_phase);
-      tc_fence_after();
-      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN;
-      if (p.splits > 1) {
-        float* dst = p.partial +
-                     (static_cast<long long>((t.ks * p.num_n_tiles + t.nt)) * p.num_m_tiles + t.mt) * (BM * BN) +
-                     static_cast<long long>(r) * BN;
+    } else {
+      // ---- direct epilogue (split-K partials, fp32 / strided / narrow outputs): 16-column chunks alternate between groups
+      for (int work = unit; work < total_work; work += num_units) {
+        const TileCoord t = decode_work(p, work, rank);
+        const RowInfo ri = row_info(p, t, r);
+        const bool tile_exists = t.mt < p.num_m_tiles;
+        mbar_wait(&tfull_bar[acc], acc_phase);
+        tc_fence_after();
+        const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN;
+        if (!tile_exists) {
+          // phantom tile of an odd pair: nothing to write
+        } else if (p.splits > 1) {
+          float* dst = p.partial +
+                       (static_cast<long long>((t.ks * p.num_n_tiles + t.nt)) * p.num_m_tiles + t.mt) * (BM * BN) +
+                       static_cast<long long>(r) * BN;
 #pragma unroll 1
-        for (int c = 0; c < BN / 16; ++c) {
-          uint32_t u[16];
-          tmem_ld16(taddr + c * 16, u);
-          tmem_ld_wait();
-#pragma unroll
-          for (int j = 0; j < 4; ++j)
-            reinterpret_cast<uint4*>(dst + c * 16)[j] = make_uint4(u[4 * j], u[4 * j + 1], u[4 * j + 2], u[4 * j + 3]);
-        }
-      } else if (p.flags & B200SD_GEMM_GEGLU) {
-        if constexpr (BN % 32 == 0) {
-#pragma unroll 1
-          for (int c = 0; c < BN / 32; ++c) {
-            uint32_t uh[16], ug[16];
-            tmem_ld16(taddr + c * 16, uh);
-            tmem_ld16(taddr + BN / 2 + c * 16, ug);
+          for (int c = g; c < BN / 16; c += 2) {
+            uint32_t u[16];
+            tmem_ld16(taddr + c * 16, u);
             tmem_ld_wait();
-            float h[16], g[16];
 #pragma unroll
-            for (int j = 0; j < 16; ++j) { h[j] = __uint_as_float(uh[j]); g[j] = __uint_as_float(ug[j]); }
-            epilogue_geglu16(p, ri, t.nt * BN + c * 16, t.nt * BN + BN / 2 + c * 16, t.nt * (BN / 2) + c * 16, h, g);
+            for (int j = 0; j < 4; ++j)
+              reinterpret_cast<uint4*>(dst + c * 16)[j] = make_uint4(u[4 * j], u[4 * j + 1], u[4 * j + 2], u[4 * j + 3]);
+          }
+        } else if (p.flags & B200SD_GEMM_GEGLU) {
+          if constexpr (BN % 32 == 0) {
+#pragma unroll 1
+            for (int c = g; c < BN / 32; c += 2) {
+              uint32_t uh[16], ug[16];
+              tmem_ld16(taddr + c * 16, uh);
+              tmem_ld16(taddr + BN / 2 + c * 16, ug);
+              tmem_ld_wait();
+              float h[16], gg[16];
+#pragma unroll
+              for (int j = 0; j < 16; ++j) { h[j] = __uint_as_float(uh[j]); gg[j] = __uint_as_float(ug[j]); }
+              epilogue_geglu16(p, ri, t.nt * BN + c * 16, t.nt * BN + BN / 2 + c * 16, t.nt * (BN / 2) + c * 16, h, gg);
+            }
+          }
+        } else {
+#pragma unroll 1
+          for (int c = g; c < BN / 16; c += 2) {
+            uint32_t u[16];
+            tmem_ld16(taddr + c * 16, u);
+            tmem_ld_wait();
+            float v[16];
+#pragma unroll
+            for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(u[j]);
+            epilogue_store16(p, ri, t.nt * BN + c * 16, v);
           }
         }
-      } else {
-#pragma unroll 1
-        for (int c = 0; c < BN / 16; ++c) {
-          uint32_t u[16];
-          tmem_ld16(taddr + c * 16, u);
-          tmem_ld_wait();
-          float v[16];
-#pragma unroll
-          for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(u[j]);
-          epilogue_store16(p, ri, t.nt * BN + c * 16, v);
-        }
+        release_acc(acc);
+        acc ^= 1;
+        if (acc == 0) acc_phase ^= 1;
       }
-      tc_fence_before();
-      mbar_arrive(&tempty_bar[acc]);
-      acc ^= 1;
-      if (acc == 0) acc_phase ^= 1;
     }
   }
 
   tc_fence_before();
-  __syncthreads();
+  if (NCTA == 2) cluster_sync_all(); else __syncthreads();  // the pair stays resident until both halves are done
   tc_fence_after();
-  if (warp == 1) tmem_dealloc(tmem_base, TMEM_COLS);
+  if (warp == 1) {
+    if (NCTA == 2) tmem_dealloc_2cta(tmem_base, TMEM_COLS);
+    else tmem_dealloc(tmem_base, TMEM_COLS);
+  }
 }
 
 // Split-K reduction + epilogue.  grid = (tiles, BN/16 or BN/32 for GEGLU), block = 128 (thread = tile row).
@@ -567,7 +642,7 @@ __global__ void __launch_bounds__(128) gemm_splitk_reduce_kernel(const __grid_co
   const int tile = blockIdx.x;  // nt * num_m_tiles + mt
   const int c = blockIdx.y;
   const int r = threadIdx.x;
-  const TileCoord t = decode_work(p, tile);  // ks == 0
+  const TileCoord t = decode_tile(p, tile % p.num_m_tiles, tile / p.num_m_tiles, 0);
   const RowInfo ri = row_info(p, t, r);
   const long long tile_elems = static_cast<long long>(BM) * BN;
   const long long split_stride = static_cast<long long>(p.num_m_tiles) * p.num_n_tiles * tile_elems;
@@ -606,52 +681,69 @@ __global__ void __launch_bounds__(128) gemm_splitk_reduce_kernel(const __grid_co
 struct GemmPlan {
   GemmKParams kp;
   int block_n;
+  int ncta;
   int grid;
   int reduce_grid_x, reduce_grid_y;
 };
 
-template <int BN>
+template <int BN, int NCTA>
 int prepare_gemm_bn() {  // called at plan time (outside any stream capture)
   static bool attr_set = false;
   if (!attr_set) {
-    B200SD_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     gemm_smem_bytes(BN)));
+    B200SD_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<BN, NCTA>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     gemm_smem_bytes(BN, NCTA)));
     attr_set = true;
   }
   return 0;
 }
-int prepare_gemm(int bn) {
+template <int NCTA>
+int prepare_gemm_n(int bn) {
   switch (bn) {
-    case 32: return prepare_gemm_bn<32>();
-    case 64: return prepare_gemm_bn<64>();
-    case 128: return prepare_gemm_bn<128>();
-    case 160: return prepare_gemm_bn<160>();
-    case 256: return prepare_gemm_bn<256>();
+    case 32: return prepare_gemm_bn<32, NCTA>();
+    case 64: return prepare_gemm_bn<64, NCTA>();
+    case 128: return prepare_gemm_bn<128, NCTA>();
+    case 160: return prepare_gemm_bn<160, NCTA>();
+    case 256: return prepare_gemm_bn<256, NCTA>();
   }
   return fail(B200SD_ERR_INVALID, "gemm: unsupported block_n %d", bn);
 }
+int prepare_gemm(int bn, int ncta) { return ncta == 2 ? prepare_gemm_n<2>(bn) : prepare_gemm_n<1>(bn); }
 
-template <int BN>
+template <int BN, int NCTA>
 int launch_gemm_bn(const GemmPlan& pl, cudaStream_t s) {
-  gemm_tc_kernel<BN><<<pl.grid, GEMM_THREADS, gemm_smem_bytes(BN), s>>>(pl.kp);
-  B200SD_CUDA(cudaGetLastError());
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(pl.grid);
+  cfg.blockDim = dim3(GEMM_THREADS);
+  cfg.dynamicSmemBytes = gemm_smem_bytes(BN, NCTA);
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = NCTA;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  B200SD_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<BN, NCTA>, pl.kp));
   if (pl.kp.splits > 1) {
     gemm_splitk_reduce_kernel<BN><<<dim3(pl.reduce_grid_x, pl.reduce_grid_y), 128, 0, s>>>(pl.kp);
     B200SD_CUDA(cudaGetLastError());
   }
   return 0;
 }
-
-int launch_gemm(const void* plan, cudaStream_t s) {
-  const GemmPlan& pl = *static_cast<const GemmPlan*>(plan);
+template <int NCTA>
+int launch_gemm_n(const GemmPlan& pl, cudaStream_t s) {
   switch (pl.block_n) {
-    case 32: return launch_gemm_bn<32>(pl, s);
-    case 64: return launch_gemm_bn<64>(pl, s);
-    case 128: return launch_gemm_bn<128>(pl, s);
-    case 160: return launch_gemm_bn<160>(pl, s);
-    case 256: return launch_gemm_bn<256>(pl, s);
+    case 32: return launch_gemm_bn<32, NCTA>(pl, s);
+    case 64: return launch_gemm_bn<64, NCTA>(pl, s);
+    case 128: return launch_gemm_bn<128, NCTA>(pl, s);
+    case 160: return launch_gemm_bn<160, NCTA>(pl, s);
+    case 256: return launch_gemm_bn<256, NCTA>(pl, s);
   }
   return fail(B200SD_ERR_INVALID, "gemm: unsupported block_n %d", pl.block_n);
+}
+int launch_gemm(const void* plan, cudaStream_t s) {
+  const GemmPlan& pl = *static_cast<const GemmPlan*>(plan);
+  return pl.ncta == 2 ? launch_gemm_n<2>(pl, s) : launch_gemm_n<1>(pl, s);
 }
 
 int ilog2(int v) {
@@ -679,15 +771,18 @@ int choose_gemm_tiling(const b200sd_gemm& g, GemmTiling* t) {
   int bn = g.block_n;
   const bool geglu = (g.flags & B200SD_GEMM_GEGLU) != 0;
   if (bn == 0) {
+    // Wider N tiles move fewer operand bytes per MMA cycle through the L2 -> SM fabric, which is what bounds the big
+    // convs (per k-block a CTA of a pair loads 16 KB of A + BN*64 B of W for 2*BN MMA cycles: 64 B/clk at BN=256,
+    // 83 B/clk at BN=160); 160 divides the 320/640/960/1920-wide layers that 256 does not.
     if (g.N <= 32 && !geglu) bn = 32;
     else if (g.N <= 64 && !geglu) bn = 64;
-    else if (g.N % 160 == 0) bn = 160;  // 9 KB of operands per 80 MMA cycles: below the 128 B/clk smem limit that BN=128 sits on
-    else if (g.N % 128 == 0) bn = 128;
+    else if (g.N % 256 == 0 || (!geglu && g.N >= 960 && g.N * 10 >= ((g.N + 255) / 256) * 256 * 9)) bn = 256;  // <= 10 % tail waste
+    else if (g.N % 160 == 0 && !geglu) bn = 160;
     else bn = 128;
   }
   B200SD_CHECK_ARG(bn == 32 || bn == 64 || bn == 128 || bn == 160 || bn == 256, "gemm: block_n=%d unsupported", bn);
   if (geglu) {
-    B200SD_CHECK_ARG(bn % 32 == 0 && g.N % bn == 0, "gemm: GEGLU needs N %% block_n == 0 and block_n %% 32 == 0 (N=%d, bn=%d)",
+    B200SD_CHECK_ARG(bn % 64 == 0 && g.N % bn == 0, "gemm: GEGLU needs N %% block_n == 0 and block_n %% 64 == 0 (N=%d, bn=%d)",
                      g.N, bn);
   }
   t->block_n = bn;
@@ -717,9 +812,17 @@ int choose_gemm_tiling(const b200sd_gemm& g, GemmTiling* t) {
     t->tiles_w = t->tiles_h = t->tiles_nb = 0;
     t->num_m_tiles = (g.M + BM - 1) / BM;
   }
-  // split-K: minimise  waves(tiles*s) * (kb per split + fixed per-tile cost)  + reduce cost
-  const int sms = sm_count();
-  const long long tiles = static_cast<long long>(t->num_m_tiles) * t->num_n_tiles;
+  // CTA pair (tcgen05 cta_group::2, 256-row tiles) halves the weight bytes every SM pulls through L2; a lone or an
+  // odd trailing M tile would leave one CTA of a pair idle.
+  int ncta = g.cta_pair;
+  B200SD_CHECK_ARG(ncta >= 0 && ncta <= 2, "gemm: cta_pair=%d (0 auto, 1, 2)", ncta);
+  if (ncta == 0) ncta = (t->num_m_tiles >= 2 && (t->num_m_tiles % 2 == 0 || t->num_m_tiles >= 9) && bn >= 64) ? 2 : 1;
+  B200SD_CHECK_ARG(ncta == 1 || bn % 32 == 0, "gemm: a CTA pair needs block_n %% 32 == 0 (got %d)", bn);
+  t->ncta = ncta;
+  t->num_pm = (t->num_m_tiles + ncta - 1) / ncta;
+  // split-K: minimise  waves(work*s) * (kb per split + fixed per-tile cost)  + reduce cost
+  const int units = std::max(1, sm_count() / ncta);
+  const long long tiles = static_cast<long long>(t->num_pm) * t->num_n_tiles;
   int splits = g.splits;
   if (splits <= 0) {
     double best_cost = 1e30;
@@ -729,7 +832,7 @@ int choose_gemm_tiling(const b200sd_gemm& g, GemmTiling* t) {
       int per = (kb_total + s - 1) / s;
       int s_eff = (kb_total + per - 1) / per;
       if (s_eff != s) continue;
-      long long waves = (tiles * s + sms - 1) / sms;
+      long long waves = (tiles * s + units - 1) / units;
       double cost = static_cast<double>(waves) * (per + 6.0) + (s > 1 ? 10.0 + 1.5 * s : 0.0);
       if (cost < best_cost - 1e-9) { best_cost = cost; best_s = s; }
     }
@@ -790,7 +893,7 @@ int plan_gemm(const b200sd_gemm& g, PlannedOp* out) {
     {
       uint64_t dims[3] = {(uint64_t)sg.channels, (uint64_t)sg.taps, (uint64_t)g.N};
       uint64_t st[2] = {(uint64_t)sg.channels * 2, (uint64_t)g.ldw * 2};
-      uint32_t box[3] = {BK, 1, (uint32_t)bn};
+      uint32_t box[3] = {BK, 1, (uint32_t)(bn / t.ncta)};  // a CTA pair stages half of the N tile per CTA
       rc = encode_tensor_map_bf16(&kp.tmB[s], sg.w, 3, dims, st, box);
       if (rc) { delete pl; return rc; }
     }
@@ -806,6 +909,7 @@ int plan_gemm(const b200sd_gemm& g, PlannedOp* out) {
   kp.bw_log2 = t.bw_log2; kp.bh_log2 = t.bh_log2; kp.bn_log2 = t.bn_log2;
   kp.tiles_w = std::max(t.tiles_w, 1); kp.tiles_h = std::max(t.tiles_h, 1); kp.tiles_nb = std::max(t.tiles_nb, 1);
   kp.num_m_tiles = t.num_m_tiles; kp.num_n_tiles = t.num_n_tiles;
+  kp.ncta = t.ncta; kp.num_pm = t.num_pm;
   kp.out = g.out; kp.ldc = g.ldc;
   if (g.spatial) {
     kp.OH = g.OH > 0 ? g.OH : g.H; kp.OW = g.OW > 0 ? g.OW : g.W;
@@ -863,10 +967,11 @@ int plan_gemm(const b200sd_gemm& g, PlannedOp* out) {
     }
   }
   pl->block_n = bn;
-  rc = prepare_gemm(bn);
+  pl->ncta = t.ncta;
+  rc = prepare_gemm(bn, t.ncta);
   if (rc) { delete pl; return rc; }
-  long long total_work = static_cast<long long>(t.num_m_tiles) * t.num_n_tiles * t.splits;
-  pl->grid = static_cast<int>(std::min<long long>(total_work, sm_count()));
+  long long total_work = static_cast<long long>(t.num_pm) * t.num_n_tiles * t.splits;
+  pl->grid = static_cast<int>(std::min<long long>(total_work, std::max(1, sm_count() / t.ncta))) * t.ncta;
   pl->reduce_grid_x = t.num_m_tiles * t.num_n_tiles;
   pl->reduce_grid_y = (g.flags & B200SD_GEMM_GEGLU) ? bn / 32 : bn / 16;
   out->kind = B200SD_OP_GEMM;

@@ -64,6 +64,7 @@ int plan_step_advance(const b200sd_step_advance& g, PlannedOp* out);
 struct GemmTiling {
   int block_n, splits, kb_total, kb_per_split;
   int num_m_tiles, num_n_tiles;
+  int ncta, num_pm;  // CTAs per tile row block (1, or 2 = cta_group::2 pair) and ceil(num_m_tiles / ncta)
   int bw_log2, bh_log2, bn_log2, tiles_w, tiles_h, tiles_nb;
 };
 int choose_gemm_tiling(const b200sd_gemm& g, GemmTiling* t);

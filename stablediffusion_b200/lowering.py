@@ -120,7 +120,7 @@ class Builder:
         g.alpha = alpha
 
     def linear(self, a, w, out=None, bias=None, residual=None, rowvec=None, rows_per_group=0, silu=False, geglu=False,
-               out_f32=False, bias_row=False, alpha=1.0, a2=None, splits=0, block_n=0):
+               out_f32=False, bias_row=False, alpha=1.0, a2=None, splits=0, block_n=0, cta_pair=0):
         """out[M,N] = a[M,K] @ w[N,K]^T (+ epilogue).  `a2` appends a second K segment ([M,K2], weights w[:, K:])."""
         ap, M, K, lda = _rows_view(a)
         wp, Nn, Kw, ldw = _rows_view(w)
@@ -145,7 +145,7 @@ class Builder:
         g.ldw = ldw
         g.M, g.N = M, Nn
         g.out, g.ldc = out.data_ptr(), out.stride(0)
-        g.splits, g.block_n = splits, block_n
+        g.splits, g.block_n, g.cta_pair = splits, block_n, cta_pair
         ldr = 0
         if residual is not None:
             _, rm, rn, ldr = _rows_view(residual)
@@ -158,7 +158,7 @@ class Builder:
         return out
 
     def conv(self, x, w, out=None, taps=TAPS_3X3_S1, phases=1, out_hw=None, bias=None, rowvec=None, residual=None,
-             silu=False, extra=None, out_scatter=None, splits=0, block_n=0):
+             silu=False, extra=None, out_scatter=None, splits=0, block_n=0, cta_pair=0):
         """Implicit-GEMM convolution on NHWC bf16.
 
         x: [NB,H,W,C] (phases == 1) or [4,NB,H/2,W/2,C] (after phase_split); w: [Cout, len(taps)*C (+ extra K)].
@@ -207,7 +207,7 @@ class Builder:
             g.OH, g.OW, g.sy, g.sx, g.oy, g.ox = out_scatter
         else:
             g.OH, g.OW, g.sy, g.sx, g.oy, g.ox = H, W, 1, 1, 0, 0
-        g.splits, g.block_n = splits, block_n
+        g.splits, g.block_n, g.cta_pair = splits, block_n, cta_pair
         ldr = residual.shape[-1] if residual is not None else 0
         self._epilogue(g, bias, rowvec, residual, ldr, silu, False, False, False, 1.0, 0)
         self._pending_meta = dict(op=f'conv{len(taps)}', M=NB * H * W, N=Cout, K=ktot, flops=2 * NB * H * W * Cout * ktot, hw=(H, W))

@@ -5,12 +5,13 @@ import torch
 
 
 def geglu_block_n(n_total: int) -> int:
-    """N tile used for a GEGLU projection of width n_total (= 8*C); must match the library's auto choice."""
-    if n_total % 128 == 0:   # 64 output columns per tile = two 32-column staging blocks of the TMA-store epilogue
+    """N tile used for a GEGLU projection of width n_total (= 8*C); must match the library's auto choice
+    (csrc/gemm.cu choose_gemm_tiling): block_n/2 output columns = whole 32-column staging blocks of the epilogue."""
+    if n_total % 256 == 0:
+        return 256
+    if n_total % 128 == 0:
         return 128
-    if n_total % 160 == 0:
-        return 160
-    raise ValueError(f"GEGLU width {n_total} is not a multiple of 128 or 160")
+    raise ValueError(f"GEGLU width {n_total} is not a multiple of 128")
 
 
 def geglu_interleave(t: torch.Tensor, block_n: int) -> torch.Tensor:

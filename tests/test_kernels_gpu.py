@@ -66,19 +66,21 @@ def _randn(shape, dev, seed, scale=1.0):
         (256, 640, 2560, 128, 3),    # explicit split-K, N tail of BN=128 on 640
     ],
 )
-def test_gemm_linear(cuda_device, M, N, K, block_n, splits):
+@pytest.mark.parametrize("cta_pair", [0, 1, 2])
+def test_gemm_linear(cuda_device, M, N, K, block_n, splits, cta_pair):
     dev = cuda_device
     a = _bf(_randn((M, K), dev, 1))
     w = _bf(_randn((N, K), dev, 2, 1.0 / math.sqrt(K)))
     bias = _randn((N,), dev, 3)
     b = _builder(dev)
-    out = b.linear(a, w, bias=bias, splits=splits, block_n=block_n)
+    out = b.linear(a, w, bias=bias, splits=splits, block_n=block_n, cta_pair=cta_pair)
     _run(b)
     ref = a.float() @ w.float().t() + bias
     _check(out, ref, name=f"gemm {M}x{N}x{K}")
 
 
-def test_gemm_epilogues(cuda_device):
+@pytest.mark.parametrize("cta_pair", [1, 2])
+def test_gemm_epilogues(cuda_device, cta_pair):
     dev = cuda_device
     M, N, K = 1024, 640, 320
     a = _bf(_randn((M, K), dev, 1))
@@ -87,12 +89,12 @@ def test_gemm_epilogues(cuda_device):
     res = _bf(_randn((M, N), dev, 4))
     rowvec = _randn((4, N), dev, 5)
     b = _builder(dev)
-    o1 = b.linear(a, w, bias=bias, residual=res)
-    o2 = b.linear(a, w, bias=bias, silu=True)
-    o3 = b.linear(a, w, rowvec=rowvec, rows_per_group=256)
-    o4 = b.linear(a, w, bias=bias, out_f32=True, alpha=0.5)
+    o1 = b.linear(a, w, bias=bias, residual=res, cta_pair=cta_pair)
+    o2 = b.linear(a, w, bias=bias, silu=True, cta_pair=cta_pair)
+    o3 = b.linear(a, w, rowvec=rowvec, rows_per_group=256, cta_pair=cta_pair)
+    o4 = b.linear(a, w, bias=bias, out_f32=True, alpha=0.5, cta_pair=cta_pair)
     rb = _randn((M,), dev, 6)
-    o5 = b.linear(a, w, bias=rb, bias_row=True)
+    o5 = b.linear(a, w, bias=rb, bias_row=True, cta_pair=cta_pair)
     _run(b)
     base = a.float() @ w.float().t()
     _check(o1, base + bias + res.float(), name="bias+residual")
@@ -116,8 +118,9 @@ def test_gemm_view_and_two_segments(cuda_device):
     _check(out, ref, name="two-segment linear")
 
 
-@pytest.mark.parametrize("M,C,splits", [(1024, 320, 1), (256, 1280, 1), (128, 640, 4)])
-def test_gemm_geglu(cuda_device, M, C, splits):
+@pytest.mark.parametrize("cta_pair", [1, 2])
+@pytest.mark.parametrize("M,C,splits", [(1024, 320, 1), (256, 1280, 1), (128, 640, 4), (4096, 320, 1)])
+def test_gemm_geglu(cuda_device, M, C, splits, cta_pair):
     from stablediffusion_b200.packing import geglu_interleave, geglu_block_n
 
     dev = cuda_device
@@ -128,7 +131,7 @@ def test_gemm_geglu(cuda_device, M, C, splits):
     wp = _bf(geglu_interleave(w, bn))
     bp = geglu_interleave(bias, bn).contiguous()
     b = _builder(dev)
-    out = b.linear(a, wp, bias=bp, geglu=True, block_n=bn, splits=splits)
+    out = b.linear(a, wp, bias=bp, geglu=True, block_n=bn, splits=splits, cta_pair=cta_pair)
     _run(b)
     proj = a.float() @ _bf(w).float().t() + bias
     h, g = proj.chunk(2, dim=-1)
@@ -161,18 +164,22 @@ def _pack_conv(w_oihw):
         (2, 64, 64, 320, 4),       # conv_out (N = 4, BN = 32)
     ],
 )
-def test_conv3x3(cuda_device, NB, H, W, Cin, Cout):
+@pytest.mark.parametrize("cta_pair", [1, 2])
+def test_conv3x3(cuda_device, NB, H, W, Cin, Cout, cta_pair):
+    if cta_pair == 2 and Cout < 32:
+        pytest.skip("a CTA pair needs block_n % 32 == 0")
     dev = cuda_device
     x = _bf(_randn((NB, H, W, Cin), dev, 1))
     w = _bf(_randn((Cout, Cin, 3, 3), dev, 2, 1.0 / math.sqrt(9 * Cin)))
     bias = _randn((Cout,), dev, 3)
     b = _builder(dev)
-    out = b.conv(x, _pack_conv(w), bias=bias)
+    out = b.conv(x, _pack_conv(w), bias=bias, cta_pair=cta_pair)
     _run(b)
     _check(out, _conv_ref(x, w, bias), name=f"conv3x3 {NB}x{H}x{W}x{Cin}->{Cout}")
 
 
-def test_conv_resnet_epilogue_and_shortcut(cuda_device):
+@pytest.mark.parametrize("cta_pair", [1, 2])
+def test_conv_resnet_epilogue_and_shortcut(cuda_device, cta_pair):
     """conv2 of a ResnetBlock2D fused with its 1x1 shortcut (extra K segment), temb rowvec and residual."""
     dev = cuda_device
     NB, H, W, C, Cin = 2, 32, 32, 640, 320
@@ -184,8 +191,8 @@ def test_conv_resnet_epilogue_and_shortcut(cuda_device):
     temb = _randn((NB, C), dev, 6)
     wcat = torch.cat([_pack_conv(w3), _pack_conv(w1)], dim=1).contiguous()
     b = _builder(dev)
-    out = b.conv(h, wcat, bias=bias, extra=[xin])
-    out2 = b.conv(h, _pack_conv(w3), bias=bias, rowvec=temb, residual=xin.repeat(1, 1, 1, 2).contiguous())
+    out = b.conv(h, wcat, bias=bias, extra=[xin], cta_pair=cta_pair)
+    out2 = b.conv(h, _pack_conv(w3), bias=bias, rowvec=temb, residual=xin.repeat(1, 1, 1, 2).contiguous(), cta_pair=cta_pair)
     _run(b)
     ref = _conv_ref(h, w3, bias) + _conv_ref(xin, w1, None, padding=0)
     _check(out, ref, name="conv2 + shortcut segment")

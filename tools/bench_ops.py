@@ -7,7 +7,7 @@ from stablediffusion_b200.lowering import Builder
 from stablediffusion_b200.packing import geglu_interleave, geglu_block_n
 
 ap = argparse.ArgumentParser()
-ap.add_argument("--only", default=""); ap.add_argument("--reps", type=int, default=5); ap.add_argument("--out", default="gpurun_out/bench_ops.txt")
+ap.add_argument("--only", default=""); ap.add_argument("--reps", type=int, default=5); ap.add_argument("--out", default="gpurun_out/bench_ops.txt"); ap.add_argument("--pair", type=int, default=0)
 a = ap.parse_args()
 dev = torch.device("cuda:0")
 bf = lambda *s: (torch.randn(*s, device=dev) * 0.5).to(torch.bfloat16)
@@ -18,13 +18,13 @@ def lin(name, M, N, K, res=False, geglu=False):
         bias = torch.randn(N, device=dev)
         if geglu:
             bn = geglu_block_n(N); w = geglu_interleave(w, bn).contiguous(); bias = geglu_interleave(bias, bn).contiguous()
-            b.linear(x, w, bias=bias, geglu=True, block_n=bn)
+            b.linear(x, w, bias=bias, geglu=True, block_n=bn, cta_pair=a.pair)
         else:
-            b.linear(x, w, bias=bias, residual=bf(M, N) if res else None)
+            b.linear(x, w, bias=bias, residual=bf(M, N) if res else None, cta_pair=a.pair)
     cases.append((name, mk, 2.0 * M * N * K, (M * K + N * K + M * (N // 2 if geglu else N) * (2 if res else 1)) * 2))
 def conv(name, NB, H, C, Co, res=False):
     def mk(b):
-        b.conv(bf(NB, H, H, C), bf(Co, 9 * C), bias=torch.randn(Co, device=dev), residual=bf(NB, H, H, Co) if res else None)
+        b.conv(bf(NB, H, H, C), bf(Co, 9 * C), bias=torch.randn(Co, device=dev), residual=bf(NB, H, H, Co) if res else None, cta_pair=a.pair)
     cases.append((name, mk, 2.0 * NB * H * H * Co * 9 * C, (NB * H * H * (C + Co * (2 if res else 1)) + Co * 9 * C) * 2))
 def att(name, B, h, Nq, Nk, d):
     def mk(b):
