@@ -6,7 +6,7 @@ HERE="$(cd "$(dirname "${BASH_SOURCE[0]}")" && pwd)"
 OUT="$HERE/../_lib"
 mkdir -p "$OUT"
 NVCC="${NVCC:-/usr/local/cuda/bin/nvcc}"
-FLAGS=(-gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17
+FLAGS=(${B200SD_EXTRA_NVCC_FLAGS:-} -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17
        -Xcompiler -fPIC -Xcompiler -fvisibility=hidden -Xptxas -v --expt-relaxed-constexpr)
 OBJS=()
 pids=()

@@ -28,7 +28,8 @@ namespace {
 constexpr int BM = 128;                     // rows per CTA tile (a CTA pair computes 256 x BN)
 constexpr int BK = 64;
 constexpr int A_STAGE_BYTES = BM * BK * 2;  // 16 KiB
-constexpr int GEMM_THREADS = 320;           // warp 0 TMA producer, warp 1 MMA issuer, warps 2-9 epilogue (2 per TMEM quadrant)
+constexpr int GEMM_THREADS = 384;           // warp 0 TMA producer, warp 1 MMA issuer, warps 2-9 epilogue (2 per TMEM quadrant),
+                                            // warps 10-11 epilogue TMA issue (residual loads + stores of warp group 0 / 1)
 constexpr int EPI_THREADS = 256;
 
 constexpr int RING_SLOTS = 8;              // epilogue staging ring: 8 x [128 rows x 32 bf16 columns] (SWIZZLE_64B)
@@ -75,6 +76,7 @@ struct alignas(64) GemmKParams {
   int num_m_tiles, num_n_tiles;
   int ncta;         // 1: one CTA per 128 x BN tile; 2: CTA pair (cluster of 2, tcgen05 cta_group::2) per 256 x BN tile
   int num_pm;       // ceil(num_m_tiles / ncta): M tiles of the work decomposition
+  int n_fastest;    // work order: 1 = the N tiles of one M tile are adjacent (activation read from HBM once), 0 = M fastest
   // epilogue
   void* out;
   long long ldc;
@@ -113,11 +115,23 @@ __device__ __forceinline__ TileCoord decode_tile(const GemmKParams& p, int mt, i
   }
   return t;
 }
-// work item -> tile of CTA `rank` of the pair (M fastest: CTAs running together share the weight tile in L2)
+// work item -> tile of CTA `rank` of the pair.  Work items that run together should share what does NOT fit in L2:
+// n_fastest keeps the N tiles of one M tile adjacent (large activations, small weights: the level-0 layers), the
+// other order walks M for a fixed weight tile (small activations, large weights: the low-resolution levels).
 __device__ __forceinline__ TileCoord decode_work(const GemmKParams& p, int work, int rank) {
-  const int pm = work % p.num_pm;
-  const int rest = work / p.num_pm;
-  return decode_tile(p, pm * p.ncta + rank, rest % p.num_n_tiles, rest / p.num_n_tiles);
+  int pm, nt, ks;
+  if (p.n_fastest) {
+    nt = work % p.num_n_tiles;
+    const int rest = work / p.num_n_tiles;
+    pm = rest % p.num_pm;
+    ks = rest / p.num_pm;
+  } else {
+    pm = work % p.num_pm;
+    const int rest = work / p.num_pm;
+    nt = rest % p.num_n_tiles;
+    ks = rest / p.num_n_tiles;
+  }
+  return decode_tile(p, pm * p.ncta + rank, nt, ks);
 }
 
 struct RowInfo {
@@ -301,8 +315,10 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
   uint64_t* empty_bar = full_bar + NSTAGE;
   uint64_t* tfull_bar = empty_bar + NSTAGE;
   uint64_t* tempty_bar = tfull_bar + 2;
-  uint64_t* res_bar = tempty_bar + 2;  // [RING_SLOTS] residual sub-tile landed
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(res_bar + RING_SLOTS);
+  uint64_t* res_bar = tempty_bar + 2;            // [RING_SLOTS] residual sub-tile landed in the slot
+  uint64_t* ready_bar = res_bar + RING_SLOTS;    // [RING_SLOTS] sub-tile written by its 128 epilogue threads
+  uint64_t* free_bar = ready_bar + RING_SLOTS;   // [RING_SLOTS] the slot's TMA store has finished reading it
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(free_bar + RING_SLOTS);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -319,7 +335,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
       mbar_init(&tfull_bar[i], 1);
       mbar_init(&tempty_bar[i], 8 * NCTA);  // one arrival per epilogue warp of every CTA that reads the accumulator
     }
-    for (int i = 0; i < RING_SLOTS; ++i) mbar_init(&res_bar[i], 1);
+    for (int i = 0; i < RING_SLOTS; ++i) { mbar_init(&res_bar[i], 1); mbar_init(&ready_bar[i], 128); mbar_init(&free_bar[i], 1); }
     fence_barrier_init();
   }
   if (warp == 1) {
@@ -429,6 +445,53 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
         if (acc == 0) acc_phase ^= 1;
       }
     }
+  } else if (warp >= 10) {
+    // ===================== epilogue TMA issue (one lane per warp group) =====================
+    // Issuing a 128-row TMA box costs the issuing thread several hundred cycles, so it is kept off the epilogue warps:
+    // this lane prefetches the residual sub-tiles of its group RES_AHEAD ahead into the ring slots and stores every
+    // sub-tile its 128 epilogue threads have marked ready.
+    if (p.staged && lane == 0 && unit < total_work) {
+      const int g = warp - 10;
+      const bool geglu = (p.flags & B200SD_GEMM_GEGLU) != 0;
+      const bool has_res = (p.flags & B200SD_GEMM_RESIDUAL) != 0;
+      const int bn_out = geglu ? BN / 2 : BN;
+      const int nsub = bn_out / 32;
+      const int total_q = ((total_work - unit + num_units - 1) / num_units) * nsub;
+      auto locate = [&](int qq, int& sub) {
+        const int k = qq / nsub;
+        sub = qq - k * nsub;
+        return decode_work(p, unit + k * num_units, rank);
+      };
+      auto issue_residual = [&](int qq) {
+        int sub;
+        const TileCoord tt = locate(qq, sub);
+        const int slot = qq % RING_SLOTS;
+        mbar_arrive_expect_tx(&res_bar[slot], RING_SLOT_BYTES);
+        const int col0 = tt.nt * bn_out + sub * 32;
+        if (p.spatial) tma_load_4d(ring + slot * RING_SLOT_BYTES, &p.tmR, &res_bar[slot], col0, tt.w0, tt.h0, tt.n0);
+        else tma_load_2d(ring + slot * RING_SLOT_BYTES, &p.tmR, &res_bar[slot], col0, tt.m0);
+      };
+      if (has_res) {
+        for (int qq = g; qq < RES_AHEAD && qq < total_q; qq += 2) issue_residual(qq);
+      }
+      for (int qq = g; qq < total_q; qq += 2) {
+        const int slot = qq % RING_SLOTS;
+        int sub;
+        const TileCoord tt = locate(qq, sub);
+        mbar_wait(&ready_bar[slot], (qq / RING_SLOTS) & 1);
+        if (tt.mt < p.num_m_tiles) {  // (the phantom tile of an odd pair has nothing to store)
+          const int col0 = tt.nt * bn_out + sub * 32;
+          if (p.spatial) tma_store_4d(&p.tmC, ring + slot * RING_SLOT_BYTES, col0, tt.w0, tt.h0, tt.n0);
+          else tma_store_2d(&p.tmC, ring + slot * RING_SLOT_BYTES, col0, tt.m0);
+        }
+        bulk_commit_group();
+        bulk_wait_group_read<1>();  // every store of this group but the latest has finished reading its slot
+        if (qq >= 2) mbar_arrive(&free_bar[(qq - 2) % RING_SLOTS]);
+        // slot of qq + RES_AHEAD = slot of qq - RES_AHEAD: its store was read-complete one iteration ago
+        if (has_res && qq + RES_AHEAD < total_q) issue_residual(qq + RES_AHEAD);
+      }
+      bulk_wait_group<0>();
+    }
   } else {
     // ===================== epilogue: 8 warps, two per TMEM lane quadrant (hardware rule: quadrant = warp_id % 4) ==========
     // The two warp groups (warps 2-5, warps 6-9) take alternate 32-column sub-tiles of every accumulator, so the
@@ -450,7 +513,6 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
     if (p.staged) {
       // ---- staged epilogue: sub-tiles go through an 8-slot swizzled smem ring; the residual sub-tile is prefetched by
       // TMA RES_AHEAD sub-tiles ahead into the slot it is added in, results leave by TMA store (coalesced, OOB clipped).
-      const bool elected = (warp == 2 + 4 * g && lane == 0);
       const bool geglu = (p.flags & B200SD_GEMM_GEGLU) != 0;
       const bool has_res = (p.flags & B200SD_GEMM_RESIDUAL) != 0;
       const bool has_bias = (p.flags & B200SD_GEMM_BIAS) != 0;
@@ -458,25 +520,10 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
       const int bn_out = geglu ? BN / 2 : BN;
       const int nsub = bn_out / 32;
       const int sw = (r >> 1) & 3;  // SWIZZLE_64B: 16-byte chunk index ^= (row / 2) % 4
-      auto issue_residual = [&](int qq) {
-        const int k = qq / nsub, sub = qq - k * nsub;
-        const long long w2 = static_cast<long long>(unit) + static_cast<long long>(k) * num_units;
-        if (w2 >= total_work) return;
-        const TileCoord tt = decode_work(p, static_cast<int>(w2), rank);
-        const int slot = qq % RING_SLOTS;
-        mbar_arrive_expect_tx(&res_bar[slot], RING_SLOT_BYTES);
-        const int col0 = tt.nt * bn_out + sub * 32;
-        if (p.spatial) tma_load_4d(ring + slot * RING_SLOT_BYTES, &p.tmR, &res_bar[slot], col0, tt.w0, tt.h0, tt.n0);
-        else tma_load_2d(ring + slot * RING_SLOT_BYTES, &p.tmR, &res_bar[slot], col0, tt.m0);
-      };
-      if (elected && has_res) {
-        for (int qq = g; qq < RES_AHEAD; qq += 2) issue_residual(qq);
-      }
       int qbase = 0;
       for (int work = unit; work < total_work; work += num_units, qbase += nsub) {
         const TileCoord t = decode_work(p, work, rank);
         const RowInfo ri = row_info(p, t, r);
-        const bool tile_exists = t.mt < p.num_m_tiles;
         float* bs = bias_s + acc * BN;
         if (has_bias) {  // bias row of this N tile -> smem while the MMAs of the tile are still running
           for (int i = et; i < BN; i += EPI_THREADS) {
@@ -497,10 +544,6 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
           if ((qq & 1) != g) continue;
           const int slot = qq % RING_SLOTS;
           uint8_t* srow = ring + slot * RING_SLOT_BYTES + r * 64;
-          if (elected) {
-            bulk_wait_group_read<1>();  // every store of this group but the latest has released its slot
-            if (has_res) issue_residual(qq + RES_AHEAD);
-          }
           float v[32];
           if (geglu) {
             uint32_t uh[32], ug[32];
@@ -509,11 +552,26 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
             tmem_ld_wait();
             const float* bh = bs + sub * 32;
             const float* bg = bh + BN / 2;
+            if (p.alpha != 1.0f) {
 #pragma unroll
-            for (int j = 0; j < 32; ++j) {
-              float hh = __uint_as_float(uh[j]) * p.alpha, gg = __uint_as_float(ug[j]) * p.alpha;
-              if (has_bias) { hh += bh[j]; gg += bg[j]; }
-              v[j] = hh * gelu_erf_f(gg);
+              for (int j = 0; j < 32; ++j) {
+                uh[j] = __float_as_uint(__uint_as_float(uh[j]) * p.alpha);
+                ug[j] = __float_as_uint(__uint_as_float(ug[j]) * p.alpha);
+              }
+            }
+#pragma unroll
+            for (int j4 = 0; j4 < 8; ++j4) {
+              float4 b_h = make_float4(0.f, 0.f, 0.f, 0.f), b_g = b_h;
+              if (has_bias) {
+                b_h = reinterpret_cast<const float4*>(bh)[j4];
+                b_g = reinterpret_cast<const float4*>(bg)[j4];
+              }
+              const float bhv[4] = {b_h.x, b_h.y, b_h.z, b_h.w}, bgv[4] = {b_g.x, b_g.y, b_g.z, b_g.w};
+#pragma unroll
+              for (int jj = 0; jj < 4; ++jj) {
+                const int j = 4 * j4 + jj;
+                v[j] = (__uint_as_float(uh[j]) + bhv[jj]) * gelu_erf_f(__uint_as_float(ug[j]) + bgv[jj]);
+              }
             }
           } else {
             uint32_t u[32];
@@ -538,7 +596,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
           }
           if (sub == my_last) release_acc(acc);  // accumulator fully read by this warp: hand it back to the MMA warp
           if (has_res) {
-            mbar_wait(&res_bar[slot], (qq / RING_SLOTS) & 1);
+            mbar_wait(&res_bar[slot], (qq / RING_SLOTS) & 1);  // (loaded only after the slot's previous store was read)
 #pragma unroll
             for (int c = 0; c < 4; ++c) {
               const uint4 rr = *reinterpret_cast<const uint4*>(srow + ((c ^ sw) * 16));
@@ -549,27 +607,20 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
                 v[8 * c + 2 * j] += f.x; v[8 * c + 2 * j + 1] += f.y;
               }
             }
+          } else if (qq >= RING_SLOTS) {
+            mbar_wait(&free_bar[slot], ((qq / RING_SLOTS) - 1) & 1);  // the slot's previous store has been read
           }
 #pragma unroll
           for (int c = 0; c < 4; ++c)
             *reinterpret_cast<uint4*>(srow + ((c ^ sw) * 16)) =
                 make_uint4(pack_bf16x2(v[8 * c], v[8 * c + 1]), pack_bf16x2(v[8 * c + 2], v[8 * c + 3]),
                            pack_bf16x2(v[8 * c + 4], v[8 * c + 5]), pack_bf16x2(v[8 * c + 6], v[8 * c + 7]));
-          fence_proxy_async_smem();
-          named_bar_sync(1 + g, 128);
-          if (elected) {
-            if (tile_exists) {
-              const int col0 = t.nt * bn_out + sub * 32;
-              if (p.spatial) tma_store_4d(&p.tmC, ring + slot * RING_SLOT_BYTES, col0, t.w0, t.h0, t.n0);
-              else tma_store_2d(&p.tmC, ring + slot * RING_SLOT_BYTES, col0, t.m0);
-            }
-            bulk_commit_group();
-          }
+          fence_proxy_async_smem();       // generic-proxy writes -> visible to the TMA store
+          mbar_arrive(&ready_bar[slot]);
         }
         acc ^= 1;
         if (acc == 0) acc_phase ^= 1;
       }
-      if (elected) bulk_wait_group<0>();
     } else {
       // ---- direct epilogue (split-K partials, fp32 / strided / narrow outputs): 16-column chunks alternate between groups
       for (int work = unit; work < total_work; work += num_units) {
@@ -910,6 +961,14 @@ int plan_gemm(const b200sd_gemm& g, PlannedOp* out) {
   kp.tiles_w = std::max(t.tiles_w, 1); kp.tiles_h = std::max(t.tiles_h, 1); kp.tiles_nb = std::max(t.tiles_nb, 1);
   kp.num_m_tiles = t.num_m_tiles; kp.num_n_tiles = t.num_n_tiles;
   kp.ncta = t.ncta; kp.num_pm = t.num_pm;
+  {
+    long long act_bytes = 0, w_bytes = 0;
+    for (int s = 0; s < g.nseg; ++s) {
+      act_bytes += static_cast<long long>(kp.M) * g.seg[s].channels * 2;
+      w_bytes += static_cast<long long>(g.N) * g.seg[s].channels * g.seg[s].taps * 2;
+    }
+    kp.n_fastest = act_bytes > w_bytes ? 1 : 0;
+  }
   kp.out = g.out; kp.ldc = g.ldc;
   if (g.spatial) {
     kp.OH = g.OH > 0 ? g.OH : g.H; kp.OW = g.OW > 0 ? g.OW : g.W;
