@@ -604,7 +604,9 @@ bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 
 
 int groupnorm_chunks(int NB, int HW, int C) {
   if (NB < 1 || HW < 1 || C < 8) return 1;
-  int target = (6 * 148 + NB - 1) / NB;
+  // One full wave: both kernels keep 4 CTAs of <= 256 threads resident per SM, so NB * chunks is sized to 4 * SMs
+  // (a grid of 1.2 or 1.5 waves runs as long as 2).
+  int target = std::max(1, (4 * sm_count()) / NB);
   const int R = std::max(1, 256 / (C / 8));           // pixel rows a CTA walks in parallel
   int max_chunks = std::max(1, HW / (4 * R));         // keep >= 4 loads per thread so one unrolled batch covers a chunk
   return std::max(1, std::min(target, max_chunks));
