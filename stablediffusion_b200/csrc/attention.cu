@@ -2,18 +2,18 @@
 // Replaces F.scaled_dot_product_attention behind diffusers' AttnProcessor2_0 (self- and cross-attention of
 // every BasicTransformerBlock).  No mask, no dropout, scale = d^-1/2 (given).
 //
-// One CTA = 128 query rows of one head.  Warp roles: warp 0 TMA producer, warp 1 MMA issuer, warps 2-5
-// softmax + correction + epilogue (one query row per thread: the TMEM lane IS the row, so row max / row sum
-// need no shuffles).  A KV block is 128 keys, processed as two 64-key HALVES that are pipelined against each
-// other through ONE S accumulator (128 TMEM columns):
-//   S_j[h] = Q K_j[h]^T    tcgen05.mma 128x64x16, K-major operands, into TMEM columns [64h, 64h+64)
-//   P_j[h] = exp2(S - m)   registers -> bf16 -> shared memory in the K-major SWIZZLE_128B layout the MMA expects
-//   O     += P_j[h] V_j[h] tcgen05.mma 128 x round16(d) x 16, V consumed MN-major straight from its [keys, d]
+// One CTA = 128 query rows of one head, KV blocks of 64 keys.  Warp roles: warp 0 TMA producer, warp 1 MMA issuer,
+// warps 2-5 softmax + correction + epilogue (one query row per thread: the TMEM lane IS the row, so row max / row
+// sum need no shuffles).
+//   S_j = Q K_j^T          tcgen05.mma 128x64x16, K-major operands, into 64 TMEM columns
+//   P_j = exp2(S_j - m)    registers -> bf16 -> shared memory in the K-major SWIZZLE_128B layout the MMA expects
+//   O  += P_j V_j          tcgen05.mma 128 x round16(d) x 16, V consumed MN-major straight from its [keys, d]
 //                          row layout (no transpose anywhere), O accumulates in TMEM.
-// As soon as the softmax warps have turned S_j[h] into P_j[h] the MMA warp issues PV_j[h] and S_{j+1}[h] — both
-// run while the softmax warps work on the other half, so they never wait for the tensor core in steady state.
-// The kernel is bound by the MUFU pipe (16384 ex2 per 128x128 block = 1024 SM cycles vs 384 MMA cycles at d=40),
-// hence: ONE pass over S per block (lazy running max, below) and two CTAs per SM for d <= 64.
+// The kernel is bound by the MUFU pipe (8192 ex2 per 128x64 block = 512 SM cycles vs 192 MMA cycles at d=40), so the
+// design is about keeping MUFU issue slots full: ONE pass over S per block (lazy running max, below) and a footprint
+// small enough (64 KB smem, 128 TMEM columns, <= 112 registers at d <= 64) for THREE CTAs per SM — while one CTA
+// waits for its PV_j / S_{j+1} round trip through the tensor core, the softmax warps of the other two own the SM's
+// four MUFU units.
 // Head dims that are not a multiple of 64 (SD1.5: 40, 80, 160) are handled by TMA itself: the box is 64 wide
 // but the tensor-map extent is d, so columns >= d arrive as zeros and never touch HBM.
 #include <algorithm>
@@ -27,12 +27,14 @@ namespace b200sd {
 namespace {
 
 constexpr int ATT_THREADS = 192;
-constexpr int BLK = 128;           // query rows per CTA and keys per KV block
-constexpr int HALF = 64;           // keys per pipelined half block
-constexpr int TILE16K = BLK * 128; // one [128 rows x 64 bf16] swizzled tile
+constexpr int BLK = 128;           // query rows per CTA
+constexpr int KB = 64;             // keys per KV block
+constexpr int TILE16K = BLK * 128; // [128 rows x 64 bf16] swizzled tile (Q chunk, P)
+constexpr int TILE8K = KB * 128;   // [64 rows x 64 bf16] swizzled tile (K / V chunk)
 
 struct alignas(64) AttnParams {
-  CUtensorMap tmQ, tmK, tmV;  // 4D (d, heads, rows, B), box (64, 1, 128, 1)
+  CUtensorMap tmQ;       // 4D (d, heads, rows, B), box (64, 1, 128, 1)
+  CUtensorMap tmK, tmV;  // 4D (d, heads, rows, B), box (64, 1, 64, 1)
   bf16* out;
   long long ldo;
   int B, heads, Nq, Nkv, d;
@@ -45,19 +47,17 @@ struct alignas(64) AttnParams {
 template <int DPAD>
 struct AttnCfg {
   static constexpr int DB = DPAD / 64;
-  // d <= 64 (the N = 4096 level of SD1.5, SDXL everywhere): 2 CTAs per SM so that two softmax warps share every SM
-  // sub-partition and keep its MUFU unit busy.
-  static constexpr int OCC = DPAD == 64 ? 2 : 1;
-  static constexpr int NSTK = DPAD == 128 ? 2 : 1;          // K stages (freed when S_j[1] = Q K_j[1]^T has completed:
-                                                            // a whole block before K_{j+1} is needed)
-  static constexpr int NSTV = 2;                            // V stages (freed when O += P_j[1] V_j[1] has completed)
-  static constexpr int TMEM_COLS = DPAD == 192 ? 512 : 256; // 128 columns of S, then O (<= DPAD columns)
+  static constexpr int OCC = DPAD == 64 ? 3 : (DPAD == 128 ? 2 : 1);  // CTAs per SM (see the header comment)
+  static constexpr int NSTK = 1;  // K stages: K_j is free as soon as S_j has completed, a whole softmax before K_{j+1} is needed
+  static constexpr int NSTV = 2;  // V stages: V_j is free when PV_j has completed, just before V_{j+1} is needed
+  static constexpr int TMEM_COLS = DPAD == 64 ? 128 : 256;            // 64 columns of S, then O (<= DPAD columns)
   static constexpr int Q_BYTES = DB * TILE16K;
-  static constexpr int KV_BYTES = DB * TILE16K;             // one K (or V) stage
-  static constexpr int P_BYTES = 2 * TILE16K;               // 128 rows x 128 keys bf16 = two half tiles
+  static constexpr int KV_BYTES = DB * TILE8K;                        // one K (or V) stage
+  static constexpr int P_BYTES = TILE16K;                             // 128 rows x 64 keys bf16
   static constexpr int SMEM = Q_BYTES + (NSTK + NSTV) * KV_BYTES + P_BYTES + 1024 + 256;
 };
-static_assert(AttnCfg<192>::SMEM <= 232448 && 2 * (AttnCfg<64>::SMEM + 1024) <= 233472, "shared memory budget");
+static_assert(AttnCfg<192>::SMEM <= 232448 && 3 * (AttnCfg<64>::SMEM + 1024) <= 233472 &&
+              2 * (AttnCfg<128>::SMEM + 1024) <= 233472, "shared memory budget");
 
 __device__ __forceinline__ float ex2_approx(float x) {
   float y;
@@ -79,17 +79,17 @@ __global__ void __launch_bounds__(ATT_THREADS, AttnCfg<DPAD>::OCC) attention_ker
   uint8_t* sQ = smem;
   uint8_t* sK = sQ + Cfg::Q_BYTES;                 // [NSTK][KV_BYTES]
   uint8_t* sV = sK + NSTK * Cfg::KV_BYTES;         // [NSTV][KV_BYTES]
-  uint8_t* sP = sV + NSTV * Cfg::KV_BYTES;         // [2 halves][TILE16K]
+  uint8_t* sP = sV + NSTV * Cfg::KV_BYTES;         // [TILE16K]
   uint64_t* bars = reinterpret_cast<uint64_t*>(sP + Cfg::P_BYTES);
   uint64_t* q_full = bars;             // 1
   uint64_t* k_full = bars + 1;         // NSTK
   uint64_t* k_empty = k_full + NSTK;   // NSTK
   uint64_t* v_full = k_empty + NSTK;   // NSTV
   uint64_t* v_empty = v_full + NSTV;   // NSTV
-  uint64_t* s_full = v_empty + NSTV;   // 2 (per half)
-  uint64_t* p_full = s_full + 2;       // 2 (per half)
-  uint64_t* pv_done = p_full + 2;      // 2 (per half)
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(pv_done + 2);
+  uint64_t* s_full = v_empty + NSTV;   // 1
+  uint64_t* p_full = s_full + 1;       // 1
+  uint64_t* pv_done = p_full + 1;      // 1
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(pv_done + 1);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -102,7 +102,9 @@ __global__ void __launch_bounds__(ATT_THREADS, AttnCfg<DPAD>::OCC) attention_ker
     mbar_init(q_full, 1);
     for (int i = 0; i < NSTK; ++i) { mbar_init(&k_full[i], 1); mbar_init(&k_empty[i], 1); }
     for (int i = 0; i < NSTV; ++i) { mbar_init(&v_full[i], 1); mbar_init(&v_empty[i], 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&s_full[i], 1); mbar_init(&p_full[i], 128); mbar_init(&pv_done[i], 1); }
+    mbar_init(s_full, 1);
+    mbar_init(p_full, 128);
+    mbar_init(pv_done, 1);
     fence_barrier_init();
   }
   if (warp == 1) { tmem_alloc(tmem_slot, Cfg::TMEM_COLS); tmem_relinquish(); }
@@ -111,8 +113,8 @@ __global__ void __launch_bounds__(ATT_THREADS, AttnCfg<DPAD>::OCC) attention_ker
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  const uint32_t tmem_S = tmem_base;        // 128 columns: half h at [64h, 64h + 64)
-  const uint32_t tmem_O = tmem_base + BLK;  // round16(d) columns
+  const uint32_t tmem_S = tmem_base;       // 64 columns
+  const uint32_t tmem_O = tmem_base + KB;  // round16(d) columns
 
   if (warp == 0) {
     // ===================== TMA producer =====================
@@ -124,172 +126,160 @@ __global__ void __launch_bounds__(ATT_THREADS, AttnCfg<DPAD>::OCC) attention_ker
         mbar_wait(&k_empty[sk], ((j / NSTK) & 1) ^ 1);
         mbar_arrive_expect_tx(&k_full[sk], Cfg::KV_BYTES);
         for (int db = 0; db < DB; ++db)
-          tma_load_4d(sK + sk * Cfg::KV_BYTES + db * TILE16K, &p.tmK, &k_full[sk], db * 64, head, j * BLK, batch);
+          tma_load_4d(sK + sk * Cfg::KV_BYTES + db * TILE8K, &p.tmK, &k_full[sk], db * 64, head, j * KB, batch);
         mbar_wait(&v_empty[sv], ((j / NSTV) & 1) ^ 1);
         mbar_arrive_expect_tx(&v_full[sv], Cfg::KV_BYTES);
         for (int db = 0; db < DB; ++db)
-          tma_load_4d(sV + sv * Cfg::KV_BYTES + db * TILE16K, &p.tmV, &v_full[sv], db * 64, head, j * BLK, batch);
+          tma_load_4d(sV + sv * Cfg::KV_BYTES + db * TILE8K, &p.tmV, &v_full[sv], db * 64, head, j * KB, batch);
       }
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
-    const uint32_t idesc_s = umma_idesc_bf16(BLK, HALF, 0);
+    const uint32_t idesc_s = umma_idesc_bf16(BLK, KB, 0);
     const uint32_t idesc_o = umma_idesc_bf16(BLK, p.n_pv, 1);
     const uint32_t q_addr = smem_u32(sQ);
-    // S_j[h] = Q K_j[h]^T; the K stage is released when the second half has completed
-    auto issue_S = [&](int j, int h) {
+    auto issue_S = [&](int j) {  // S_j = Q K_j^T; the K stage is released when it completes
       const int st = j % NSTK;
-      if (h == 0) {
-        mbar_wait(&k_full[st], (j / NSTK) & 1);
-        tc_fence_after();
-      }
+      mbar_wait(&k_full[st], (j / NSTK) & 1);
+      tc_fence_after();
       if (lane == 0) {
-        const uint32_t k_addr = smem_u32(sK + st * Cfg::KV_BYTES) + h * (HALF * 128);
-        const uint32_t d_tmem = tmem_S + h * HALF;
+        const uint32_t k_addr = smem_u32(sK + st * Cfg::KV_BYTES);
         for (int ks = 0; ks < p.ksteps_qk; ++ks) {
-          const uint32_t off = (ks >> 2) * TILE16K + (ks & 3) * 32;
-          umma_bf16_ss(d_tmem, umma_smem_desc_sw128(q_addr + off, 16, 1024),
-                       umma_smem_desc_sw128(k_addr + off, 16, 1024), idesc_s, ks != 0 ? 1u : 0u);
+          umma_bf16_ss(tmem_S, umma_smem_desc_sw128(q_addr + (ks >> 2) * TILE16K + (ks & 3) * 32, 16, 1024),
+                       umma_smem_desc_sw128(k_addr + (ks >> 2) * TILE8K + (ks & 3) * 32, 16, 1024), idesc_s,
+                       ks != 0 ? 1u : 0u);
         }
-        umma_commit(&s_full[h]);
-        if (h == 1) umma_commit(&k_empty[st]);
+        umma_commit(s_full);
+        umma_commit(&k_empty[st]);
       }
       __syncwarp();
     };
     mbar_wait(q_full, 0);
-    issue_S(0, 0);
-    issue_S(0, 1);
+    issue_S(0);
     for (int j = 0; j < nkv; ++j) {
-      const int sv = j % NSTV;
+      const int st = j % NSTV;
+      mbar_wait(p_full, j & 1);  // P_j written and S_j fully read
+      mbar_wait(&v_full[st], (j / NSTV) & 1);
+      tc_fence_after();
+      if (lane == 0) {
+        const uint32_t p_addr = smem_u32(sP);
+        const uint32_t v_addr = smem_u32(sV + st * Cfg::KV_BYTES);
 #pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        mbar_wait(&p_full[h], j & 1);
-        if (h == 0) mbar_wait(&v_full[sv], (j / NSTV) & 1);
-        tc_fence_after();
-        if (lane == 0) {
-          const uint32_t p_addr = smem_u32(sP) + h * TILE16K;
-          const uint32_t v_addr = smem_u32(sV + sv * Cfg::KV_BYTES) + h * (HALF / 8) * 1024;
-#pragma unroll
-          for (int ks = 0; ks < HALF / 16; ++ks) {
-            const uint64_t da = umma_smem_desc_sw128(p_addr + ks * 32, 16, 1024);
-            // V: MN-major; 16 keys = 2 groups of 8 rows (SBO 1024), 64-wide d chunks TILE16K apart (LBO)
-            const uint64_t db = umma_smem_desc_sw128(v_addr + ks * 2048, TILE16K, 1024);
-            umma_bf16_ss(tmem_O, da, db, idesc_o, (j | h | ks) != 0 ? 1u : 0u);
-          }
-          umma_commit(&pv_done[h]);
-          if (h == 1) umma_commit(&v_empty[sv]);
+        for (int ks = 0; ks < KB / 16; ++ks) {
+          const uint64_t da = umma_smem_desc_sw128(p_addr + ks * 32, 16, 1024);
+          // V: MN-major; 16 keys = 2 groups of 8 rows (SBO 1024), 64-wide d chunks TILE8K apart (LBO)
+          const uint64_t db = umma_smem_desc_sw128(v_addr + ks * 2048, TILE8K, 1024);
+          umma_bf16_ss(tmem_O, da, db, idesc_o, (j | ks) != 0 ? 1u : 0u);
         }
-        __syncwarp();
-        if (j + 1 < nkv) issue_S(j + 1, h);
+        umma_commit(pv_done);
+        umma_commit(&v_empty[st]);
       }
+      __syncwarp();
+      if (j + 1 < nkv) issue_S(j + 1);
     }
   } else {
     // ===================== softmax / correction / epilogue: thread <-> query row =====================
     const int q = warp & 3;
     const int r = q * 32 + lane;
     const uint32_t lane_base = static_cast<uint32_t>(q * 32) << 16;
+    const uint32_t s_addr = tmem_S + lane_base;
     const uint32_t o_addr = tmem_O + lane_base;
     const uint32_t prow = smem_u32(sP) + r * 128;
     const int rsw = r & 7;
     float m_run = -INFINITY;  // softmax reference point of this row, scaled log2 domain
     float l_run = 0.f;
-    // Lazy running max (single pass over S on every half but the first): probabilities are taken relative to the
-    // max of the keys BEFORE this half, and the half's own max is tracked in the same pass.  Softmax is invariant
+    // Lazy running max (single pass over S on every block but the first): probabilities are taken relative to the
+    // max of the keys BEFORE this block, and the block's own max is tracked in the same pass.  Softmax is invariant
     // to the reference point; bf16 P and the fp32 row sum keep their relative precision at any magnitude, so the
     // reference only has to move (and O be rescaled) when a row's scores outgrow it by more than 2^LAZY_TAU — then
-    // the warp redoes its half with the exact max (S is still in TMEM).
+    // the warp redoes its block with the exact max (S_j is still in TMEM).
     constexpr float LAZY_TAU = 8.0f;
     for (int j = 0; j < nkv; ++j) {
-      const int kv_valid = min(BLK, p.Nkv - j * BLK);  // keys of this block that exist
+      const int valid = min(KB, p.Nkv - j * KB);  // keys of this block that exist
+      mbar_wait(s_full, j & 1);                    // also: PV_{j-1} has consumed P (the commit covers every earlier MMA)
+      tc_fence_after();
+      // probabilities -> bf16 -> swizzled smem (K-major, 128-byte rows, 16-byte chunk ^= row % 8); returns the row sum
+      auto exp_pass = [&](auto masked_tag, const float m_ref, float& mx_out) {
+        constexpr bool MASKED = decltype(masked_tag)::value;
+        float rsum = 0.f, mx = -INFINITY;
 #pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        mbar_wait(&s_full[h], j & 1);  // also: PV_{j-1}[h] has consumed P[h] (commit covers every earlier MMA)
-        tc_fence_after();
-        const uint32_t s_addr = tmem_S + lane_base + h * HALF;
-        const int valid = min(HALF, kv_valid - h * HALF);  // may be <= 0 in the second half of a ragged block
-        // probabilities -> bf16 -> swizzled smem (K-major, 128-byte rows, 16-byte chunk ^= row % 8); returns the row sum
-        auto exp_pass = [&](auto masked_tag, const float m_ref, float& mx_out) {
-          constexpr bool MASKED = decltype(masked_tag)::value;
-          float rsum = 0.f, mx = -INFINITY;
+        for (int c = 0; c < KB / 32; ++c) {
+          uint32_t u[32];
+          tmem_ld32(s_addr + c * 32, u);
+          tmem_ld_wait();
+          uint32_t pk[16];
 #pragma unroll
-          for (int c = 0; c < HALF / 32; ++c) {
+          for (int i = 0; i < 16; ++i) {
+            const float s0 = __uint_as_float(u[2 * i]), s1 = __uint_as_float(u[2 * i + 1]);
+            float p0 = ex2_approx(fmaf(s0, p.scale_log2, -m_ref));
+            float p1 = ex2_approx(fmaf(s1, p.scale_log2, -m_ref));
+            if (MASKED) {
+              if (c * 32 + 2 * i >= valid) p0 = 0.f; else mx = fmaxf(mx, s0);
+              if (c * 32 + 2 * i + 1 >= valid) p1 = 0.f; else mx = fmaxf(mx, s1);
+            } else {
+              mx = fmaxf(mx, fmaxf(s0, s1));
+            }
+            rsum += p0 + p1;
+            pk[i] = pack_bf16x2(p0, p1);
+          }
+#pragma unroll
+          for (int i = 0; i < 4; ++i)
+            sts128(prow + (((c * 4 + i) ^ rsw) << 4), pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
+        }
+        mx_out = mx * p.scale_log2;
+        return rsum;
+      };
+      // The body is instantiated twice: the mask-free version runs on every full block (no per-element predicates).
+      auto block_body = [&](auto masked_tag) {
+        constexpr bool MASKED = decltype(masked_tag)::value;
+        if (j == 0) {  // very first block: exact max (nothing to rescale yet)
+          float mx = -INFINITY;
+#pragma unroll
+          for (int c = 0; c < KB / 32; ++c) {
             uint32_t u[32];
             tmem_ld32(s_addr + c * 32, u);
             tmem_ld_wait();
-            uint32_t pk[16];
 #pragma unroll
-            for (int i = 0; i < 16; ++i) {
-              const float s0 = __uint_as_float(u[2 * i]), s1 = __uint_as_float(u[2 * i + 1]);
-              float p0 = ex2_approx(fmaf(s0, p.scale_log2, -m_ref));
-              float p1 = ex2_approx(fmaf(s1, p.scale_log2, -m_ref));
-              if (MASKED) {
-                if (c * 32 + 2 * i >= valid) p0 = 0.f; else mx = fmaxf(mx, s0);
-                if (c * 32 + 2 * i + 1 >= valid) p1 = 0.f; else mx = fmaxf(mx, s1);
-              } else {
-                mx = fmaxf(mx, fmaxf(s0, s1));
-              }
-              rsum += p0 + p1;
-              pk[i] = pack_bf16x2(p0, p1);
-            }
-#pragma unroll
-            for (int i = 0; i < 4; ++i)
-              sts128(prow + h * TILE16K + (((c * 4 + i) ^ rsw) << 4), pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
+            for (int i = 0; i < 32; ++i)
+              if (!MASKED || c * 32 + i < valid) mx = fmaxf(mx, __uint_as_float(u[i]));
           }
-          mx_out = mx * p.scale_log2;
-          return rsum;
-        };
-        // The body is instantiated twice: the mask-free version runs on every full half (no per-element predicates).
-        auto half_body = [&](auto masked_tag) {
-          constexpr bool MASKED = decltype(masked_tag)::value;
-          if (j == 0 && h == 0) {  // very first half: exact max (nothing to rescale yet)
-            float mx = -INFINITY;
-#pragma unroll
-            for (int c = 0; c < HALF / 32; ++c) {
-              uint32_t u[32];
-              tmem_ld32(s_addr + c * 32, u);
-              tmem_ld_wait();
-#pragma unroll
-              for (int i = 0; i < 32; ++i)
-                if (!MASKED || c * 32 + i < valid) mx = fmaxf(mx, __uint_as_float(u[i]));
-            }
-            m_run = mx * p.scale_log2;
+          m_run = mx * p.scale_log2;
+        }
+        float m_blk;
+        float rsum = exp_pass(masked_tag, m_run, m_blk);
+        const bool outgrown = m_blk > m_run + LAZY_TAU;
+        if (__any_sync(0xffffffffu, outgrown)) {  // rare; warp-uniform because tcgen05.ld/st are .sync.aligned
+          float alpha = 1.0f;
+          if (outgrown) {  // this row moves its reference to the exact max; the other rows just repeat
+            alpha = ex2_approx(m_run - m_blk);
+            m_run = m_blk;
           }
-          float m_blk;
-          float rsum = exp_pass(masked_tag, m_run, m_blk);
-          const bool outgrown = m_blk > m_run + LAZY_TAU;
-          if (__any_sync(0xffffffffu, outgrown)) {  // rare; warp-uniform because tcgen05.ld/st are .sync.aligned
-            float alpha = 1.0f;
-            if (outgrown) {  // this row moves its reference to the exact max; the other rows just repeat
-              alpha = ex2_approx(m_run - m_blk);
-              m_run = m_blk;
-            }
-            rsum = exp_pass(masked_tag, m_run, m_blk);
-            l_run *= alpha;
-            // O *= alpha once every PV issued so far has landed: the latest one is PV_j[0] (h = 1) or PV_{j-1}[1]
-            mbar_wait(&pv_done[h ^ 1], (h == 1 ? j : j - 1) & 1);
-            tc_fence_after();
+          rsum = exp_pass(masked_tag, m_run, m_blk);
+          l_run *= alpha;
+          // O *= alpha once PV_{j-1} (the latest PV issued) has landed
+          mbar_wait(pv_done, (j - 1) & 1);
+          tc_fence_after();
 #pragma unroll 1
-            for (int c = 0; c < p.n_pv / 16; ++c) {
-              uint32_t u[16];
-              tmem_ld16(o_addr + c * 16, u);
-              tmem_ld_wait();
+          for (int c = 0; c < p.n_pv / 16; ++c) {
+            uint32_t u[16];
+            tmem_ld16(o_addr + c * 16, u);
+            tmem_ld_wait();
 #pragma unroll
-              for (int i = 0; i < 16; ++i) u[i] = __float_as_uint(__uint_as_float(u[i]) * alpha);
-              tmem_st16(o_addr + c * 16, u);
-            }
-            tmem_st_wait();
+            for (int i = 0; i < 16; ++i) u[i] = __float_as_uint(__uint_as_float(u[i]) * alpha);
+            tmem_st16(o_addr + c * 16, u);
           }
-          l_run += rsum;
-        };
-        if (valid == HALF) half_body(std::false_type{});
-        else half_body(std::true_type{});
-        fence_proxy_async_smem();  // P (generic-proxy stores) -> visible to the MMA's async-proxy reads
-        tc_fence_before();
-        mbar_arrive(&p_full[h]);
-      }
+          tmem_st_wait();
+        }
+        l_run += rsum;
+      };
+      if (valid == KB) block_body(std::false_type{});
+      else block_body(std::true_type{});
+      fence_proxy_async_smem();  // P (generic-proxy stores) -> visible to the MMA's async-proxy reads
+      tc_fence_before();
+      mbar_arrive(p_full);
     }
     // ---- epilogue: O / l -> bf16 -> global ----
-    mbar_wait(&pv_done[1], (nkv - 1) & 1);
+    mbar_wait(pv_done, (nkv - 1) & 1);
     tc_fence_after();
     const float inv_l = 1.0f / l_run;
     const int qrow = q0 + r;
@@ -371,20 +361,20 @@ int plan_attention(const b200sd_attention& a, PlannedOp* out) {
   if (!pl) return fail(B200SD_ERR_CUDA, "out of host memory");
   AttnParams& kp = pl->kp;
   memset(&kp, 0, sizeof(kp));
-  auto make_map = [&](CUtensorMap* m, const void* base, long long ld, int rows) {
+  auto make_map = [&](CUtensorMap* m, const void* base, long long ld, int rows, int box_rows) {
     uint64_t dims[4] = {(uint64_t)a.d, (uint64_t)a.heads, (uint64_t)rows, (uint64_t)a.B};
     uint64_t st[3] = {(uint64_t)a.d * 2, (uint64_t)ld * 2, (uint64_t)rows * ld * 2};
-    uint32_t box[4] = {64, 1, BLK, 1};
+    uint32_t box[4] = {64, 1, (uint32_t)box_rows, 1};
     return encode_tensor_map_bf16(m, base, 4, dims, st, box);
   };
-  int rc = make_map(&kp.tmQ, a.q, a.ldq, a.Nq);
-  if (!rc) rc = make_map(&kp.tmK, a.k, a.ldk, a.Nkv);
-  if (!rc) rc = make_map(&kp.tmV, a.v, a.ldv, a.Nkv);
+  int rc = make_map(&kp.tmQ, a.q, a.ldq, a.Nq, BLK);
+  if (!rc) rc = make_map(&kp.tmK, a.k, a.ldk, a.Nkv, KB);
+  if (!rc) rc = make_map(&kp.tmV, a.v, a.ldv, a.Nkv, KB);
   if (rc) { delete pl; return rc; }
   kp.out = static_cast<bf16*>(a.out);
   kp.ldo = a.ldo;
   kp.B = a.B; kp.heads = a.heads; kp.Nq = a.Nq; kp.Nkv = a.Nkv; kp.d = a.d;
-  kp.kv_blocks = (a.Nkv + BLK - 1) / BLK;
+  kp.kv_blocks = (a.Nkv + KB - 1) / KB;
   kp.n_pv = (a.d + 15) / 16 * 16;
   kp.ksteps_qk = (a.d + 15) / 16;
   kp.scale_log2 = a.scale * 1.4426950408889634f;
