@@ -25,6 +25,16 @@ for _ in range(5):
     ms = eng.run_unet_timed()
     best = ms if best is None else [min(x, y) for x, y in zip(best, ms)]
 kinds = eng.b.prog.kinds
+# whole-step time as the pipeline runs it (one CUDA-graph launch per step), to compare with the sum of per-op times
+st = eng._stream
+with torch.cuda.stream(st):
+    for _ in range(3): eng.step_once(st)
+    g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    g0.record(st)
+    for _ in range(10): eng.step_once(st)
+    g1.record(st)
+torch.cuda.synchronize()
+graph_ms = g0.elapsed_time(g1) / 10
 lines, agg = [], {}
 for i, (t, k) in enumerate(zip(best, kinds)):
     md = eng.b.meta.get(i, {})
@@ -35,7 +45,7 @@ for i, (t, k) in enumerate(zip(best, kinds)):
     e = agg.setdefault(key, [0, 0.0, 0.0, 0.0])
     e[0] += 1; e[1] += t; e[2] += md.get("flops", 0); e[3] += md.get("bytes", 0)
 tot = sum(best)
-out = [f"# {a.model} res {a.res} batch {a.batch} (UNet batch {2*a.batch}); total {tot:.3f} ms over {len(best)} ops; min of 5 event-timed runs"]
+out = [f"# {a.model} res {a.res} batch {a.batch} (UNet batch {2*a.batch}); total {tot:.3f} ms over {len(best)} ops; min of 5 event-timed runs; graph replay {graph_ms:.3f} ms/step"]
 for key, (n, t, fl, by) in sorted(agg.items(), key=lambda x: -x[1][1])[: a.top]:
     extra = f"{fl / (t * 1e-3) / 1e12:8.1f} TFLOP/s" if fl else (f"{by / (t * 1e-3) / 1e9:8.1f} GB/s" if by else "")
     out.append(f"{t:8.3f} ms {100 * t / tot:5.1f}% n={n:3d} {t / n * 1000:8.1f} us/op {extra}  {key}")
