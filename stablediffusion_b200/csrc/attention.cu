@@ -24,6 +24,20 @@
 #include "internal.h"
 
 namespace b200sd {
+#ifdef B200SD_ATT_TRACE
+// Tuning aid (not part of the ABI, compiled only with -DB200SD_ATT_TRACE): clock stamps of CTA (0,0,0)'s roles.
+__device__ unsigned long long g_att_trace[3 * 1024];
+#define ATT_TR(role, id)                                                                                      \
+  do {                                                                                                        \
+    if (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && tr_n < 1024)                                  \
+      g_att_trace[(role) * 1024 + tr_n++] = (static_cast<unsigned long long>(id) << 48) | (clock64() & 0xFFFFFFFFFFFFull); \
+  } while (0)
+extern "C" __attribute__((visibility("default"))) int b200sd_debug_att_trace(unsigned long long* dst) {
+  return static_cast<int>(cudaMemcpyFromSymbol(dst, g_att_trace, sizeof(g_att_trace)));
+}
+#else
+#define ATT_TR(role, id) do {} while (0)
+#endif
 namespace {
 
 constexpr int ATT_THREADS = 192;
@@ -47,22 +61,26 @@ struct alignas(64) AttnParams {
 template <int DPAD>
 struct AttnCfg {
   static constexpr int DB = DPAD / 64;
-  static constexpr int OCC = DPAD == 64 ? 3 : (DPAD == 128 ? 2 : 1);  // CTAs per SM (see the header comment)
+  static constexpr int OCC = DPAD == 64 ? 4 : (DPAD == 128 ? 2 : 1);  // CTAs per SM (see the header comment)
   static constexpr int NSTK = 1;  // K stages: K_j is free as soon as S_j has completed, a whole softmax before K_{j+1} is needed
-  static constexpr int NSTV = 2;  // V stages: V_j is free when PV_j has completed, just before V_{j+1} is needed
+  static constexpr int NSTV = DPAD == 64 ? 1 : 2;  // V stages: V_j is free when PV_j has completed, a softmax before V_{j+1} is needed
   static constexpr int TMEM_COLS = DPAD == 64 ? 128 : 256;            // 64 columns of S, then O (<= DPAD columns)
   static constexpr int Q_BYTES = DB * TILE16K;
   static constexpr int KV_BYTES = DB * TILE8K;                        // one K (or V) stage
   static constexpr int P_BYTES = TILE16K;                             // 128 rows x 64 keys bf16
   static constexpr int SMEM = Q_BYTES + (NSTK + NSTV) * KV_BYTES + P_BYTES + 1024 + 256;
 };
-static_assert(AttnCfg<192>::SMEM <= 232448 && 3 * (AttnCfg<64>::SMEM + 1024) <= 233472 &&
+static_assert(AttnCfg<192>::SMEM <= 232448 && 4 * (AttnCfg<64>::SMEM + 1024) <= 233472 &&
               2 * (AttnCfg<128>::SMEM + 1024) <= 233472, "shared memory budget");
 
 __device__ __forceinline__ float ex2_approx(float x) {
+#ifdef B200SD_ATT_NOEXP  // diagnostic build only: how fast is everything but the MUFU work?
+  return x * 0.001f + 0.01f;
+#else
   float y;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
+#endif
 }
 __device__ __forceinline__ void sts128(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
   asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
@@ -118,16 +136,19 @@ __global__ void __launch_bounds__(ATT_THREADS, AttnCfg<DPAD>::OCC) attention_ker
 
   if (warp == 0) {
     // ===================== TMA producer =====================
-    if (lane == 0) {
+    if (elect_one()) {
       mbar_arrive_expect_tx(q_full, Cfg::Q_BYTES);
       for (int db = 0; db < DB; ++db) tma_load_4d(sQ + db * TILE16K, &p.tmQ, q_full, db * 64, head, q0, batch);
+      int tr_n = 0; (void)tr_n;
       for (int j = 0; j < nkv; ++j) {
         const int sk = j % NSTK, sv = j % NSTV;
         mbar_wait(&k_empty[sk], ((j / NSTK) & 1) ^ 1);
+        ATT_TR(0, 9);
         mbar_arrive_expect_tx(&k_full[sk], Cfg::KV_BYTES);
         for (int db = 0; db < DB; ++db)
           tma_load_4d(sK + sk * Cfg::KV_BYTES + db * TILE8K, &p.tmK, &k_full[sk], db * 64, head, j * KB, batch);
         mbar_wait(&v_empty[sv], ((j / NSTV) & 1) ^ 1);
+        ATT_TR(0, 10);
         mbar_arrive_expect_tx(&v_full[sv], Cfg::KV_BYTES);
         for (int db = 0; db < DB; ++db)
           tma_load_4d(sV + sv * Cfg::KV_BYTES + db * TILE8K, &p.tmV, &v_full[sv], db * 64, head, j * KB, batch);
@@ -135,47 +156,61 @@ __global__ void __launch_bounds__(ATT_THREADS, AttnCfg<DPAD>::OCC) attention_ker
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
+    // This warp shares its SM sub-partition with the softmax warps of up to three CTAs, so every instruction between
+    // "P_j is ready" and "S_{j+1} is issued" sits on the critical path of the whole CTA at a fraction of the issue
+    // rate: all smem descriptors are built once, up front, and the operand barriers (V_j, K_{j+1}: both land long
+    // before P_j) are waited for BEFORE the P barrier — what remains after it is 7 tcgen05.mma and 4 commits.
+    constexpr int KS_MAX = DPAD / 16;
     const uint32_t idesc_s = umma_idesc_bf16(BLK, KB, 0);
     const uint32_t idesc_o = umma_idesc_bf16(BLK, p.n_pv, 1);
-    const uint32_t q_addr = smem_u32(sQ);
-    auto issue_S = [&](int j) {  // S_j = Q K_j^T; the K stage is released when it completes
-      const int st = j % NSTK;
-      mbar_wait(&k_full[st], (j / NSTK) & 1);
-      tc_fence_after();
-      if (lane == 0) {
-        const uint32_t k_addr = smem_u32(sK + st * Cfg::KV_BYTES);
-        for (int ks = 0; ks < p.ksteps_qk; ++ks) {
-          umma_bf16_ss(tmem_S, umma_smem_desc_sw128(q_addr + (ks >> 2) * TILE16K + (ks & 3) * 32, 16, 1024),
-                       umma_smem_desc_sw128(k_addr + (ks >> 2) * TILE8K + (ks & 3) * 32, 16, 1024), idesc_s,
-                       ks != 0 ? 1u : 0u);
-        }
-        umma_commit(s_full);
-        umma_commit(&k_empty[st]);
+    uint64_t dq[KS_MAX], dk[KS_MAX], dp[KB / 16], dv0[KB / 16], dv1[KB / 16];
+    {
+      const uint32_t q_addr = smem_u32(sQ), k_addr = smem_u32(sK), p_addr = smem_u32(sP), v_addr = smem_u32(sV);
+#pragma unroll
+      for (int ks = 0; ks < KS_MAX; ++ks) {
+        dq[ks] = umma_smem_desc_sw128(q_addr + (ks >> 2) * TILE16K + (ks & 3) * 32, 16, 1024);
+        dk[ks] = umma_smem_desc_sw128(k_addr + (ks >> 2) * TILE8K + (ks & 3) * 32, 16, 1024);
       }
-      __syncwarp();
+#pragma unroll
+      for (int ks = 0; ks < KB / 16; ++ks) {
+        dp[ks] = umma_smem_desc_sw128(p_addr + ks * 32, 16, 1024);
+        // V: MN-major; 16 keys = 2 groups of 8 rows (SBO 1024), 64-wide d chunks TILE8K apart (LBO)
+        dv0[ks] = umma_smem_desc_sw128(v_addr + ks * 2048, TILE8K, 1024);
+        dv1[ks] = umma_smem_desc_sw128(v_addr + (NSTV - 1) * Cfg::KV_BYTES + ks * 2048, TILE8K, 1024);
+      }
+    }
+    static_assert(NSTK == 1 && NSTV <= 2, "descriptor tables assume one K stage and at most two V stages");
+    int tr_n = 0; (void)tr_n;
+    auto issue_S = [&]() {  // S = Q K^T (lane 0); the K stage is released when it completes
+#pragma unroll
+      for (int ks = 0; ks < KS_MAX; ++ks)
+        if (ks < p.ksteps_qk) umma_bf16_ss(tmem_S, dq[ks], dk[ks], idesc_s, ks != 0 ? 1u : 0u);
+      umma_commit(s_full);
+      umma_commit(&k_empty[0]);
     };
     mbar_wait(q_full, 0);
-    issue_S(0);
+    mbar_wait(&k_full[0], 0);
+    tc_fence_after();
+    if (elect_one()) issue_S();
+    __syncwarp();
     for (int j = 0; j < nkv; ++j) {
       const int st = j % NSTV;
-      mbar_wait(p_full, j & 1);  // P_j written and S_j fully read
-      mbar_wait(&v_full[st], (j / NSTV) & 1);
+      mbar_wait(&v_full[st], (j / NSTV) & 1);             // V_j: loaded a block ago
+      if (j + 1 < nkv) mbar_wait(&k_full[0], (j + 1) & 1);  // K_{j+1}: loaded while the softmax of block j ran
+      mbar_wait(p_full, j & 1);                            // P_j written and S_j fully read
       tc_fence_after();
-      if (lane == 0) {
-        const uint32_t p_addr = smem_u32(sP);
-        const uint32_t v_addr = smem_u32(sV + st * Cfg::KV_BYTES);
+      if (elect_one()) {
+        ATT_TR(1, 4);
+        if (j + 1 < nkv) issue_S();  // S_{j+1} first: it is what the softmax warps are waiting for
+        ATT_TR(1, 6);
 #pragma unroll
-        for (int ks = 0; ks < KB / 16; ++ks) {
-          const uint64_t da = umma_smem_desc_sw128(p_addr + ks * 32, 16, 1024);
-          // V: MN-major; 16 keys = 2 groups of 8 rows (SBO 1024), 64-wide d chunks TILE8K apart (LBO)
-          const uint64_t db = umma_smem_desc_sw128(v_addr + ks * 2048, TILE8K, 1024);
-          umma_bf16_ss(tmem_O, da, db, idesc_o, (j | ks) != 0 ? 1u : 0u);
-        }
+        for (int ks = 0; ks < KB / 16; ++ks)
+          umma_bf16_ss(tmem_O, dp[ks], st ? dv1[ks] : dv0[ks], idesc_o, (j | ks) != 0 ? 1u : 0u);
         umma_commit(pv_done);
         umma_commit(&v_empty[st]);
+        ATT_TR(1, 8);
       }
       __syncwarp();
-      if (j + 1 < nkv) issue_S(j + 1);
     }
   } else {
     // ===================== softmax / correction / epilogue: thread <-> query row =====================
@@ -188,6 +223,7 @@ __global__ void __launch_bounds__(ATT_THREADS, AttnCfg<DPAD>::OCC) attention_ker
     const int rsw = r & 7;
     float m_run = -INFINITY;  // softmax reference point of this row, scaled log2 domain
     float l_run = 0.f;
+    int tr_n = 0; (void)tr_n;
     // Lazy running max (single pass over S on every block but the first): probabilities are taken relative to the
     // max of the keys BEFORE this block, and the block's own max is tracked in the same pass.  Softmax is invariant
     // to the reference point; bf16 P and the fp32 row sum keep their relative precision at any magnitude, so the
@@ -196,8 +232,10 @@ __global__ void __launch_bounds__(ATT_THREADS, AttnCfg<DPAD>::OCC) attention_ker
     constexpr float LAZY_TAU = 8.0f;
     for (int j = 0; j < nkv; ++j) {
       const int valid = min(KB, p.Nkv - j * KB);  // keys of this block that exist
-      mbar_wait(s_full, j & 1);                    // also: PV_{j-1} has consumed P (the commit covers every earlier MMA)
+      mbar_wait(s_full, j & 1);
       tc_fence_after();
+      bool p_busy = j > 0;  // PV_{j-1} is issued right AFTER S_j: it may still be reading P when S_j lands
+      if (warp == 2 && lane == 0) ATT_TR(2, 1);
       // probabilities -> bf16 -> swizzled smem (K-major, 128-byte rows, 16-byte chunk ^= row % 8); returns the row sum
       auto exp_pass = [&](auto masked_tag, const float m_ref, float& mx_out) {
         constexpr bool MASKED = decltype(masked_tag)::value;
@@ -222,9 +260,17 @@ __global__ void __launch_bounds__(ATT_THREADS, AttnCfg<DPAD>::OCC) attention_ker
             rsum += p0 + p1;
             pk[i] = pack_bf16x2(p0, p1);
           }
+          if (p_busy) {  // (complete long before the first chunk's exponentials are)
+            mbar_wait(pv_done, (j - 1) & 1);
+            p_busy = false;
+          }
 #pragma unroll
-          for (int i = 0; i < 4; ++i)
+          for (int i = 0; i < 4; ++i) {
+#ifdef B200SD_ATT_NOSTS  // diagnostic build only
+            if (pk[4 * i] == 0x12345678u)
+#endif
             sts128(prow + (((c * 4 + i) ^ rsw) << 4), pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
+          }
         }
         mx_out = mx * p.scale_log2;
         return rsum;
@@ -274,9 +320,11 @@ __global__ void __launch_bounds__(ATT_THREADS, AttnCfg<DPAD>::OCC) attention_ker
       };
       if (valid == KB) block_body(std::false_type{});
       else block_body(std::true_type{});
+      if (warp == 2 && lane == 0) ATT_TR(2, 2);
       fence_proxy_async_smem();  // P (generic-proxy stores) -> visible to the MMA's async-proxy reads
       tc_fence_before();
       mbar_arrive(p_full);
+      if (warp == 2 && lane == 0) ATT_TR(2, 3);
     }
     // ---- epilogue: O / l -> bf16 -> global ----
     mbar_wait(pv_done, (nkv - 1) & 1);

@@ -18,6 +18,14 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }
 __device__ __forceinline__ uint32_t lane_id() { return threadIdx.x & 31; }
+// true in exactly one lane of a converged warp.  Unlike `lane == 0` the compiler KNOWS the guarded region runs in a
+// single thread, so descriptors stay in uniform registers and a tcgen05.mma costs one issue slot instead of a chain
+// of R2UR moves.
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred P1;\n\telect.sync _|P1, 0xffffffff;\n\tselp.u32 %0, 1, 0, P1;\n\t}" : "=r"(pred));
+  return pred != 0;
+}
 
 __device__ __forceinline__ uint64_t global_timer_ns() {
   uint64_t t;

@@ -358,7 +358,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
 
   if (warp == 0) {
     // ===================== TMA producer (one lane; in a pair BOTH CTAs load: own A rows, own half of W) =====================
-    if (lane == 0) {
+    if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
       for (int work = unit; work < total_work; work += num_units) {
@@ -420,7 +420,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
         for (int i = 0; i < nkb; ++i) {
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
-          if (lane == 0) {
+          if (elect_one()) {
             const uint32_t a_addr = smem_u32(smem + stage * STAGE_BYTES);
             const uint32_t b_addr = a_addr + A_STAGE_BYTES;
 #pragma unroll
@@ -450,7 +450,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
     // Issuing a 128-row TMA box costs the issuing thread several hundred cycles, so it is kept off the epilogue warps:
     // this lane prefetches the residual sub-tiles of its group RES_AHEAD ahead into the ring slots and stores every
     // sub-tile its 128 epilogue threads have marked ready.
-    if (p.staged && lane == 0 && unit < total_work) {
+    if (p.staged && unit < total_work && elect_one()) {
       const int g = warp - 10;
       const bool geglu = (p.flags & B200SD_GEMM_GEGLU) != 0;
       const bool has_res = (p.flags & B200SD_GEMM_RESIDUAL) != 0;
