@@ -819,26 +819,8 @@ int choose_gemm_tiling(const b200sd_gemm& g, GemmTiling* t) {
     B200SD_CHECK_ARG(sg.taps >= 1 && sg.taps <= B200SD_MAX_TAPS, "gemm: segment %d taps=%d", s, sg.taps);
     kb_total += sg.taps * ((sg.channels + BK - 1) / BK);
   }
-  int bn = g.block_n;
   const bool geglu = (g.flags & B200SD_GEMM_GEGLU) != 0;
-  if (bn == 0) {
-    // Wider N tiles move fewer operand bytes per MMA cycle through the L2 -> SM fabric, which is what bounds the big
-    // convs (per k-block a CTA of a pair loads 16 KB of A + BN*64 B of W for 2*BN MMA cycles: 64 B/clk at BN=256,
-    // 83 B/clk at BN=160); 160 divides the 320/640/960/1920-wide layers that 256 does not.
-    if (g.N <= 32 && !geglu) bn = 32;
-    else if (g.N <= 64 && !geglu) bn = 64;
-    else if (g.N % 256 == 0 || (!geglu && g.N >= 960 && g.N * 10 >= ((g.N + 255) / 256) * 256 * 9)) bn = 256;  // <= 10 % tail waste
-    else if (g.N % 160 == 0 && !geglu) bn = 160;
-    else bn = 128;
-  }
-  B200SD_CHECK_ARG(bn == 32 || bn == 64 || bn == 128 || bn == 160 || bn == 256, "gemm: block_n=%d unsupported", bn);
-  if (geglu) {
-    B200SD_CHECK_ARG(bn % 64 == 0 && g.N % bn == 0, "gemm: GEGLU needs N %% block_n == 0 and block_n %% 64 == 0 (N=%d, bn=%d)",
-                     g.N, bn);
-  }
-  t->block_n = bn;
   t->kb_total = kb_total;
-  t->num_n_tiles = (g.N + bn - 1) / bn;
   if (g.spatial) {
     B200SD_CHECK_ARG(g.NB >= 1 && g.H >= 1 && g.W >= 1, "gemm: spatial dims NB=%d H=%d W=%d", g.NB, g.H, g.W);
     // choose (bw, bh, bn) powers of two with product 128 maximising the fraction of useful rows
@@ -863,32 +845,51 @@ int choose_gemm_tiling(const b200sd_gemm& g, GemmTiling* t) {
     t->tiles_w = t->tiles_h = t->tiles_nb = 0;
     t->num_m_tiles = (g.M + BM - 1) / BM;
   }
-  // CTA pair (tcgen05 cta_group::2, 256-row tiles) halves the weight bytes every SM pulls through L2; a lone or an
-  // odd trailing M tile would leave one CTA of a pair idle.
-  int ncta = g.cta_pair;
-  B200SD_CHECK_ARG(ncta >= 0 && ncta <= 2, "gemm: cta_pair=%d (0 auto, 1, 2)", ncta);
-  if (ncta == 0) ncta = (t->num_m_tiles >= 2 && (t->num_m_tiles % 2 == 0 || t->num_m_tiles >= 9) && bn >= 64) ? 2 : 1;
-  B200SD_CHECK_ARG(ncta == 1 || bn % 32 == 0, "gemm: a CTA pair needs block_n %% 32 == 0 (got %d)", bn);
-  t->ncta = ncta;
-  t->num_pm = (t->num_m_tiles + ncta - 1) / ncta;
-  // split-K: minimise  waves(work*s) * (kb per split + fixed per-tile cost)  + reduce cost
-  const int units = std::max(1, sm_count() / ncta);
-  const long long tiles = static_cast<long long>(t->num_pm) * t->num_n_tiles;
-  int splits = g.splits;
-  if (splits <= 0) {
-    double best_cost = 1e30;
-    int best_s = 1;
-    const int max_s = std::min(32, std::max(1, kb_total / 4));
-    for (int s = 1; s <= max_s; ++s) {
-      int per = (kb_total + s - 1) / s;
-      int s_eff = (kb_total + per - 1) / per;
-      if (s_eff != s) continue;
-      long long waves = (tiles * s + units - 1) / units;
-      double cost = static_cast<double>(waves) * (per + 6.0) + (s > 1 ? 10.0 + 1.5 * s : 0.0);
-      if (cost < best_cost - 1e-9) { best_cost = cost; best_s = s; }
-    }
-    splits = best_s;
+  // ---- block_n x CTA pair x split-K, chosen together by an estimate of the kernel's cycles --------------------------
+  // Measured on B200 (tools/bench_gemm_sweep.py): an SM ingests operands at ~2.6 clk per 128-byte row (~49 B/clk — the
+  // same ceiling cuBLAS sits on), so one k-block costs max(MMA cycles = 2*bn, 2.6 * (128 rows of A + bn/ncta rows of
+  // W)); wide tiles and CTA pairs (tcgen05 cta_group::2: each CTA stages half of W) buy flops per ingested row, narrow
+  // ones buy fuller waves on the small-M levels.  Per work item: ~1500 clk of pipeline fill + exposed epilogue.
+  B200SD_CHECK_ARG(g.cta_pair >= 0 && g.cta_pair <= 2, "gemm: cta_pair=%d (0 auto, 1, 2)", g.cta_pair);
+  B200SD_CHECK_ARG(g.block_n == 0 || g.block_n == 32 || g.block_n == 64 || g.block_n == 128 || g.block_n == 160 ||
+                   g.block_n == 256, "gemm: block_n=%d unsupported", g.block_n);
+  if (geglu && g.block_n) {
+    B200SD_CHECK_ARG(g.block_n % 64 == 0 && g.N % g.block_n == 0,
+                     "gemm: GEGLU needs N %% block_n == 0 and block_n %% 64 == 0 (N=%d, bn=%d)", g.N, g.block_n);
   }
+  const int bn_cand[5] = {256, 160, 128, 64, 32};
+  double best_cost = 1e300;
+  int best_bn = 0, best_ncta = 1, best_s = 1;
+  for (int bi = 0; bi < 5; ++bi) {
+    const int bn = bn_cand[bi];
+    if (g.block_n ? bn != g.block_n : ((bn == 64 && g.N > 64) || (bn == 32 && g.N > 32) || (geglu && (bn % 64 || g.N % bn))))
+      continue;  // the narrow tiles only serve narrow outputs; a GEGLU tile holds whole h|g column pairs
+    const int n_tiles = (g.N + bn - 1) / bn;
+    for (int ncta = 1; ncta <= 2; ++ncta) {
+      if (g.cta_pair && ncta != g.cta_pair) continue;
+      if (ncta == 2 && (bn % 32 != 0 || (!g.cta_pair && t->num_m_tiles < 2))) continue;
+      const int num_pm = (t->num_m_tiles + ncta - 1) / ncta;
+      const int units = std::max(1, sm_count() / ncta);
+      const double t_kb = std::max(2.0 * bn, 2.6 * (128 + bn / ncta));
+      const int max_s = g.splits > 0 ? g.splits : std::min(32, std::max(1, kb_total / 4));
+      for (int sp = g.splits > 0 ? g.splits : 1; sp <= max_s; ++sp) {
+        const int per = (kb_total + sp - 1) / sp;
+        if (g.splits <= 0 && (kb_total + per - 1) / per != sp) continue;
+        const long long waves = (static_cast<long long>(num_pm) * n_tiles * sp + units - 1) / units;
+        double cost = static_cast<double>(waves) * (per * t_kb + 1500.0);
+        if (sp > 1)  // fp32 partials written and re-read by the reduce kernel (+ its launch)
+          cost += 4000.0 + static_cast<double>(t->num_m_tiles) * BM * n_tiles * bn * 4.0 * (sp + 1) / (148.0 * 24.0);
+        if (cost < best_cost * (1.0 - 1e-9)) { best_cost = cost; best_bn = bn; best_ncta = ncta; best_s = sp; }
+      }
+    }
+  }
+  B200SD_CHECK_ARG(best_bn != 0, "gemm: no tile shape fits N=%d block_n=%d cta_pair=%d", g.N, g.block_n, g.cta_pair);
+  const int bn = best_bn;
+  t->block_n = bn;
+  t->num_n_tiles = (g.N + bn - 1) / bn;
+  t->ncta = best_ncta;
+  t->num_pm = (t->num_m_tiles + best_ncta - 1) / best_ncta;
+  int splits = best_s;
   B200SD_CHECK_ARG(splits >= 1 && splits <= kb_total, "gemm: splits=%d invalid for %d k-blocks", splits, kb_total);
   int per = (kb_total + splits - 1) / splits;
   splits = (kb_total + per - 1) / per;
