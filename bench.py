@@ -248,8 +248,15 @@ def run_b200(args, wl, rank, world, local_rank):
         n_gemm = sum(1 for k in kinds if k == N.OP_GEMM)
         gemm_flops = eng.gemm_flops
         achieved = gemm_flops / (gemm_ms * 1e-3) / 1e12
+        traffic, traffic_src = None, None   # DRAM bytes per launch of the same kernel from the committed ncu capture
+        tp = os.path.join(ROOT, "profiles", "r01_gemm_traffic.json")
+        if wl == "sd15_512_b8_ddim50_cfg" and os.path.exists(tp):
+            with open(tp) as f:
+                td = json.load(f)
+            traffic, traffic_src = td["dram_bytes_per_launch"], "profiles/r01_gemm_traffic.json (ncu, cold cache per launch)"
         roof = {"bound": "tensor", "kernel": "gemm_tc_kernel (tcgen05 implicit GEMM, all conv/linear launches of one sampler step)",
-                "achieved": achieved, "peak": pk["tf"], "unit": "TFLOP/s", "frac": achieved / pk["tf"], "traffic": None,
+                "achieved": achieved, "peak": pk["tf"], "unit": "TFLOP/s", "frac": achieved / pk["tf"], "traffic": traffic, "traffic_source": traffic_src,
+                "algorithmic_flop_per_launch": gemm_flops / n_gemm,
                 "peak_source": f"{pk['src']} bf16_tflops_sustained", "launches": n_gemm, "avg_launch_ms": gemm_ms / n_gemm,
                 "step_ms_by_kind": {N.OP_NAMES[k]: round(sum(m for m, kk in zip(ms, kinds) if kk == k), 4) for k in sorted(set(kinds))},
                 "attention_tflops": (eng.attn_flops / (att_ms * 1e-3) / 1e12) if att_ms > 0 else None}
