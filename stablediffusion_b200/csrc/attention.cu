@@ -109,6 +109,7 @@ __global__ void __launch_bounds__(ATT_THREADS, AttnCfg<DPAD>::OCC) attention_ker
   uint64_t* pv_done = p_full + 1;      // 1
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(pv_done + 1);
 
+  pdl_launch_dependents();
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const int q0 = blockIdx.x * BLK;
@@ -131,6 +132,7 @@ __global__ void __launch_bounds__(ATT_THREADS, AttnCfg<DPAD>::OCC) attention_ker
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();  // the prologue above overlapped the previous kernel's tail
   const uint32_t tmem_S = tmem_base;       // 64 columns
   const uint32_t tmem_O = tmem_base + KB;  // round16(d) columns
 
@@ -380,8 +382,7 @@ int prepare_attention(int dpad) {
 
 template <int DPAD>
 int launch_attention_t(const AttnPlan& pl, cudaStream_t s) {
-  attention_kernel<DPAD><<<pl.grid, ATT_THREADS, AttnCfg<DPAD>::SMEM, s>>>(pl.kp);
-  B200SD_CUDA(cudaGetLastError());
+  B200SD_CUDA(launch_kernel(attention_kernel<DPAD>, pl.grid, dim3(ATT_THREADS), AttnCfg<DPAD>::SMEM, s, 1, pl.kp));
   return 0;
 }
 int launch_attention(const void* plan, cudaStream_t s) {

@@ -65,6 +65,8 @@ __device__ __forceinline__ const bf16* gn_src(const GNParams& p, int n, int pix,
 }
 
 __global__ void gn_stats_kernel(const GNParams p) {
+  pdl_launch_dependents();
+  pdl_wait();
   __shared__ float gsum[64][2];
   const int chunk = blockIdx.x, n = blockIdx.y;
   const int tid = threadIdx.x;
@@ -126,6 +128,8 @@ __global__ void gn_stats_kernel(const GNParams p) {
 }
 
 __global__ void gn_apply_kernel(const GNParams p) {
+  pdl_launch_dependents();
+  pdl_wait();
   extern __shared__ float sm[];  // a[C], b[C], mean[groups], rstd[groups]
   float* sa = sm;
   float* sb = sm + p.C;
@@ -203,9 +207,9 @@ struct GNPlan { GNParams p; int threads; size_t smem; };
 int launch_groupnorm(const void* plan, cudaStream_t s) {
   const GNPlan& pl = *static_cast<const GNPlan*>(plan);
   dim3 grid(pl.p.chunks, pl.p.NB);
-  gn_stats_kernel<<<grid, pl.threads, 0, s>>>(pl.p);
+  B200SD_CUDA(launch_kernel(gn_stats_kernel, dim3(grid), dim3(pl.threads), 0, s, 1, pl.p));
   B200SD_CUDA(cudaGetLastError());
-  gn_apply_kernel<<<grid, pl.threads, pl.smem, s>>>(pl.p);
+  B200SD_CUDA(launch_kernel(gn_apply_kernel, dim3(grid), dim3(pl.threads), pl.smem, s, 1, pl.p));
   B200SD_CUDA(cudaGetLastError());
   return 0;
 }
@@ -222,6 +226,8 @@ constexpr int LN_MAXV = 8;  // up to 8 vectors (64 channels) per lane
 // and every lane has VPL independent 16-byte loads in flight.
 template <int VPL>
 __global__ void __launch_bounds__(256) layernorm_kernel(const LNParams p, int lpr) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int lane = threadIdx.x & 31;
   const int rows_per_warp = 32 / lpr;
   const int sub = lane / lpr, sl = lane % lpr;
@@ -291,14 +297,14 @@ int launch_layernorm(const void* plan, cudaStream_t s) {
   const int rows_per_cta = 8 * (32 / lpr);
   const int grid = (p.rows + rows_per_cta - 1) / rows_per_cta;
   switch (vpl) {
-    case 1: layernorm_kernel<1><<<grid, 256, 0, s>>>(p, lpr); break;
-    case 2: layernorm_kernel<2><<<grid, 256, 0, s>>>(p, lpr); break;
-    case 3: layernorm_kernel<3><<<grid, 256, 0, s>>>(p, lpr); break;
-    case 4: layernorm_kernel<4><<<grid, 256, 0, s>>>(p, lpr); break;
-    case 5: layernorm_kernel<5><<<grid, 256, 0, s>>>(p, lpr); break;
-    case 6: layernorm_kernel<6><<<grid, 256, 0, s>>>(p, lpr); break;
-    case 7: layernorm_kernel<7><<<grid, 256, 0, s>>>(p, lpr); break;
-    default: layernorm_kernel<8><<<grid, 256, 0, s>>>(p, lpr); break;
+    case 1: B200SD_CUDA(launch_kernel(layernorm_kernel<1>, dim3(grid), dim3(256), 0, s, 1, p, lpr)); break;
+    case 2: B200SD_CUDA(launch_kernel(layernorm_kernel<2>, dim3(grid), dim3(256), 0, s, 1, p, lpr)); break;
+    case 3: B200SD_CUDA(launch_kernel(layernorm_kernel<3>, dim3(grid), dim3(256), 0, s, 1, p, lpr)); break;
+    case 4: B200SD_CUDA(launch_kernel(layernorm_kernel<4>, dim3(grid), dim3(256), 0, s, 1, p, lpr)); break;
+    case 5: B200SD_CUDA(launch_kernel(layernorm_kernel<5>, dim3(grid), dim3(256), 0, s, 1, p, lpr)); break;
+    case 6: B200SD_CUDA(launch_kernel(layernorm_kernel<6>, dim3(grid), dim3(256), 0, s, 1, p, lpr)); break;
+    case 7: B200SD_CUDA(launch_kernel(layernorm_kernel<7>, dim3(grid), dim3(256), 0, s, 1, p, lpr)); break;
+    default: B200SD_CUDA(launch_kernel(layernorm_kernel<8>, dim3(grid), dim3(256), 0, s, 1, p, lpr)); break;
   }
   B200SD_CUDA(cudaGetLastError());
   return 0;
@@ -311,6 +317,8 @@ struct TEParams {
   const float* t; const float* table; const int* counter; int t_stride, rows, dim, flip; float shift, max_period; bf16* out;
 };
 __global__ void timestep_embed_kernel(const TEParams p) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int half = p.dim / 2;
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= p.rows * half) return;
@@ -329,7 +337,7 @@ __global__ void timestep_embed_kernel(const TEParams p) {
 int launch_timestep_embed(const void* plan, cudaStream_t s) {
   const TEParams& p = *static_cast<const TEParams*>(plan);
   const int n = p.rows * (p.dim / 2);
-  timestep_embed_kernel<<<(n + 127) / 128, 128, 0, s>>>(p);
+  B200SD_CUDA(launch_kernel(timestep_embed_kernel, dim3((n + 127) / 128), dim3(128), 0, s, 1, p));
   B200SD_CUDA(cudaGetLastError());
   return 0;
 }
@@ -341,6 +349,8 @@ struct PLParams {
   const void* lat; bf16* out; const float* table; const int* counter; float fixed_scale; int in_dtype, B, C, hw, Cpad, rep;
 };
 __global__ void prep_latents_kernel(const PLParams p) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= p.B * p.hw) return;
   const int b = idx / p.hw, pix = idx - b * p.hw;
@@ -358,7 +368,7 @@ __global__ void prep_latents_kernel(const PLParams p) {
 int launch_prep_latents(const void* plan, cudaStream_t s) {
   const PLParams& p = *static_cast<const PLParams*>(plan);
   const int n = p.B * p.hw;
-  prep_latents_kernel<<<(n + 127) / 128, 128, 0, s>>>(p);
+  B200SD_CUDA(launch_kernel(prep_latents_kernel, dim3((n + 127) / 128), dim3(128), 0, s, 1, p));
   B200SD_CUDA(cudaGetLastError());
   return 0;
 }
@@ -368,6 +378,8 @@ int launch_prep_latents(const void* plan, cudaStream_t s) {
 // ======================================================================================================
 struct USParams { const bf16* x; bf16* out; int NB, H, W, C; };
 __global__ void upsample2x_kernel(const USParams p) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int cv = p.C >> 3;
   const long long total = static_cast<long long>(p.NB) * p.H * p.W * cv;
   for (long long idx = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; idx < total;
@@ -388,6 +400,8 @@ __global__ void upsample2x_kernel(const USParams p) {
   }
 }
 __global__ void phase_split_kernel(const USParams p) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int cv = p.C >> 3;
   const int H2 = p.H >> 1, W2 = p.W >> 1;
   const long long total = static_cast<long long>(p.NB) * p.H * p.W * cv;
@@ -408,7 +422,7 @@ int launch_upsample2x(const void* plan, cudaStream_t s) {
   const USParams& p = *static_cast<const USParams*>(plan);
   const long long total = static_cast<long long>(p.NB) * p.H * p.W * (p.C >> 3);
   const int blocks = static_cast<int>(std::min<long long>((total + 255) / 256, 148 * 16));
-  upsample2x_kernel<<<blocks, 256, 0, s>>>(p);
+  B200SD_CUDA(launch_kernel(upsample2x_kernel, dim3(blocks), dim3(256), 0, s, 1, p));
   B200SD_CUDA(cudaGetLastError());
   return 0;
 }
@@ -416,7 +430,7 @@ int launch_phase_split(const void* plan, cudaStream_t s) {
   const USParams& p = *static_cast<const USParams*>(plan);
   const long long total = static_cast<long long>(p.NB) * p.H * p.W * (p.C >> 3);
   const int blocks = static_cast<int>(std::min<long long>((total + 255) / 256, 148 * 16));
-  phase_split_kernel<<<blocks, 256, 0, s>>>(p);
+  B200SD_CUDA(launch_kernel(phase_split_kernel, dim3(blocks), dim3(256), 0, s, 1, p));
   B200SD_CUDA(cudaGetLastError());
   return 0;
 }
@@ -426,6 +440,8 @@ int launch_phase_split(const void* plan, cudaStream_t s) {
 // ======================================================================================================
 struct SMParams { const bf16* x; bf16* out; long long ldx, ldo; int rows, cols; float scale; };
 __global__ void __launch_bounds__(256) softmax_rows_kernel(const SMParams p) {
+  pdl_launch_dependents();
+  pdl_wait();
   __shared__ float red[8];
   __shared__ float bcast;
   const int row = blockIdx.x;
@@ -475,7 +491,7 @@ __global__ void __launch_bounds__(256) softmax_rows_kernel(const SMParams p) {
 }
 int launch_softmax_rows(const void* plan, cudaStream_t s) {
   const SMParams& p = *static_cast<const SMParams*>(plan);
-  softmax_rows_kernel<<<p.rows, 256, 0, s>>>(p);
+  B200SD_CUDA(launch_kernel(softmax_rows_kernel, dim3(p.rows), dim3(256), 0, s, 1, p));
   B200SD_CUDA(cudaGetLastError());
   return 0;
 }
@@ -491,6 +507,8 @@ struct CSParams {
   const float* table; const int* counter; float gs; int cfg, x_dtype, B, C, hw, Cpad, rep, nsteps, gs_from_table;
 };
 __global__ void cfg_step_kernel(const CSParams p) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= p.B * p.hw) return;
   const int b = idx / p.hw, pix = idx - b * p.hw;
@@ -532,7 +550,7 @@ __global__ void cfg_step_kernel(const CSParams p) {
 int launch_cfg_step(const void* plan, cudaStream_t s) {
   const CSParams& p = *static_cast<const CSParams*>(plan);
   const int n = p.B * p.hw;
-  cfg_step_kernel<<<(n + 127) / 128, 128, 0, s>>>(p);
+  B200SD_CUDA(launch_kernel(cfg_step_kernel, dim3((n + 127) / 128), dim3(128), 0, s, 1, p));
   B200SD_CUDA(cudaGetLastError());
   return 0;
 }
@@ -542,6 +560,8 @@ int launch_cfg_step(const void* plan, cudaStream_t s) {
 // ======================================================================================================
 struct AXParams { const void* x; const void* y; void* out; float a, b; int xd, yd, od; long long n; };
 __global__ void axpby_kernel(const AXParams p) {
+  pdl_launch_dependents();
+  pdl_wait();
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < p.n;
        i += static_cast<long long>(gridDim.x) * blockDim.x) {
     float v = p.a * load_as_float(p.x, i, p.xd);
@@ -552,13 +572,15 @@ __global__ void axpby_kernel(const AXParams p) {
 int launch_axpby(const void* plan, cudaStream_t s) {
   const AXParams& p = *static_cast<const AXParams*>(plan);
   const int blocks = static_cast<int>(std::min<long long>((p.n + 255) / 256, 148 * 8));
-  axpby_kernel<<<blocks, 256, 0, s>>>(p);
+  B200SD_CUDA(launch_kernel(axpby_kernel, dim3(blocks), dim3(256), 0, s, 1, p));
   B200SD_CUDA(cudaGetLastError());
   return 0;
 }
 
 struct IOParams { const bf16* x; void* out; long long ldx; int B, C, HW, od; };
 __global__ void image_out_kernel(const IOParams p) {
+  pdl_launch_dependents();
+  pdl_wait();
   const long long total = static_cast<long long>(p.B) * p.HW;
   for (long long idx = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; idx < total;
        idx += static_cast<long long>(gridDim.x) * blockDim.x) {
@@ -573,15 +595,19 @@ int launch_image_out(const void* plan, cudaStream_t s) {
   const IOParams& p = *static_cast<const IOParams*>(plan);
   const long long total = static_cast<long long>(p.B) * p.HW;
   const int blocks = static_cast<int>(std::min<long long>((total + 255) / 256, 148 * 8));
-  image_out_kernel<<<blocks, 256, 0, s>>>(p);
+  B200SD_CUDA(launch_kernel(image_out_kernel, dim3(blocks), dim3(256), 0, s, 1, p));
   B200SD_CUDA(cudaGetLastError());
   return 0;
 }
 
-__global__ void step_advance_kernel(int* counter) { *counter += 1; }
+__global__ void step_advance_kernel(int* counter) {
+  pdl_launch_dependents();
+  pdl_wait();
+  *counter += 1;
+}
 struct SAParams { int* counter; };
 int launch_step_advance(const void* plan, cudaStream_t s) {
-  step_advance_kernel<<<1, 1, 0, s>>>(static_cast<const SAParams*>(plan)->counter);
+  B200SD_CUDA(launch_kernel(step_advance_kernel, dim3(1), dim3(1), 0, s, 1, static_cast<const SAParams*>(plan)->counter));
   B200SD_CUDA(cudaGetLastError());
   return 0;
 }

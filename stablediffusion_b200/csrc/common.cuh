@@ -27,6 +27,20 @@ __device__ __forceinline__ bool elect_one() {
   return pred != 0;
 }
 
+// Programmatic dependent launch: every kernel of the library is launched with programmatic stream serialization and
+// executes pdl_wait() before its first global access (it blocks until the PREVIOUS kernel of the stream has completed and
+// its writes are visible; a kernel that skipped it would race with its predecessor).  Measured on B200 (SD1.5 step, one
+// CUDA graph of 440 kernels): programmatic edges alone 19.15 -> 18.49 ms at UNet batch 16 and 5.40 -> 5.29 ms at batch 2;
+// an EARLY trigger (griddepcontrol.launch_dependents at kernel entry, so that the next kernel's CTAs become resident
+// while this one drains) made it WORSE (18.90 / 6.38 ms: the waiting CTAs take SM slots from the running kernel), so the
+// trigger is left implicit at kernel exit unless B200SD_PDL_EARLY_TRIGGER is defined.
+__device__ __forceinline__ void pdl_launch_dependents() {
+#ifdef B200SD_PDL_EARLY_TRIGGER
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+#endif
+}
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 __device__ __forceinline__ uint64_t global_timer_ns() {
   uint64_t t;
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));

@@ -320,6 +320,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
   uint64_t* free_bar = ready_bar + RING_SLOTS;   // [RING_SLOTS] the slot's TMA store has finished reading it
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(free_bar + RING_SLOTS);
 
+  pdl_launch_dependents();  // the next kernel may start its prologue as SMs free up
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const int rank = NCTA == 2 ? static_cast<int>(cluster_ctarank()) : 0;  // rank 0 = leader of the pair (issues the MMAs)
@@ -353,6 +354,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
   if (NCTA == 2) cluster_sync_all(); else __syncthreads();  // barriers initialised cluster-wide before any remote arrive
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();  // everything above overlapped the previous kernel's tail; its results are visible from here on
 
   const int total_work = p.num_pm * p.num_n_tiles * p.splits;
 
@@ -690,6 +692,8 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
 // Split-K reduction + epilogue.  grid = (tiles, BN/16 or BN/32 for GEGLU), block = 128 (thread = tile row).
 template <int BN>
 __global__ void __launch_bounds__(128) gemm_splitk_reduce_kernel(const __grid_constant__ GemmKParams p) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int tile = blockIdx.x;  // nt * num_m_tiles + mt
   const int c = blockIdx.y;
   const int r = threadIdx.x;
@@ -762,22 +766,9 @@ int prepare_gemm(int bn, int ncta) { return ncta == 2 ? prepare_gemm_n<2>(bn) : 
 
 template <int BN, int NCTA>
 int launch_gemm_bn(const GemmPlan& pl, cudaStream_t s) {
-  cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(pl.grid);
-  cfg.blockDim = dim3(GEMM_THREADS);
-  cfg.dynamicSmemBytes = gemm_smem_bytes(BN, NCTA);
-  cfg.stream = s;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = NCTA;
-  attr[0].val.clusterDim.y = 1;
-  attr[0].val.clusterDim.z = 1;
-  cfg.attrs = attr;
-  cfg.numAttrs = 1;
-  B200SD_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<BN, NCTA>, pl.kp));
+  B200SD_CUDA(launch_kernel(gemm_tc_kernel<BN, NCTA>, dim3(pl.grid), dim3(GEMM_THREADS), gemm_smem_bytes(BN, NCTA), s, NCTA, pl.kp));
   if (pl.kp.splits > 1) {
-    gemm_splitk_reduce_kernel<BN><<<dim3(pl.reduce_grid_x, pl.reduce_grid_y), 128, 0, s>>>(pl.kp);
-    B200SD_CUDA(cudaGetLastError());
+    B200SD_CUDA(launch_kernel(gemm_splitk_reduce_kernel<BN>, dim3(pl.reduce_grid_x, pl.reduce_grid_y), dim3(128), 0, s, 1, pl.kp));
   }
   return 0;
 }

@@ -7,6 +7,7 @@
 #include <stdio.h>
 
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "../../include/b200sd.h"
@@ -70,6 +71,36 @@ struct GemmTiling {
 int choose_gemm_tiling(const b200sd_gemm& g, GemmTiling* t);
 int groupnorm_chunks(int NB, int HW, int C);
 int sm_count();  // of the current device; 148 when no device is visible (planning arithmetic only)
+
+// Every kernel launch of the library: programmatic stream serialization (see pdl_wait() in common.cuh; B200SD_PDL=0 in
+// the environment turns it off) and, for the CTA-pair GEMM, a cluster dimension.  Works under stream capture.
+bool pdl_enabled();
+template <class... KArgs, class... Args>
+cudaError_t launch_kernel(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, int cluster_x,
+                          Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[2];
+  int n = 0;
+  if (cluster_x > 1) {
+    attr[n].id = cudaLaunchAttributeClusterDimension;
+    attr[n].val.clusterDim.x = cluster_x;
+    attr[n].val.clusterDim.y = 1;
+    attr[n].val.clusterDim.z = 1;
+    ++n;
+  }
+  if (pdl_enabled()) {
+    attr[n].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[n].val.programmaticStreamSerializationAllowed = 1;
+    ++n;
+  }
+  cfg.attrs = attr;
+  cfg.numAttrs = n;
+  return cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
+}
 
 template <class T>
 void destroy_plan(void* p) {

@@ -2,6 +2,8 @@
 #include <mutex>
 #include <new>
 
+#include <stdlib.h>
+
 #include "internal.h"
 
 namespace b200sd {
@@ -19,6 +21,14 @@ int fail(int status, const char* fmt, ...) {
   va_end(ap);
   last_error_ref() = buf;
   return status;
+}
+
+bool pdl_enabled() {
+  static const bool on = [] {
+    const char* e = getenv("B200SD_PDL");
+    return !(e && e[0] == '0');
+  }();
+  return on;
 }
 
 int sm_count() {
