@@ -2,21 +2,25 @@
 // Replaces F.scaled_dot_product_attention behind diffusers' AttnProcessor2_0 (self- and cross-attention of
 // every BasicTransformerBlock).  No mask, no dropout, scale = d^-1/2 (given).
 //
-// One CTA = 128 query rows of one head, KV blocks of 64 keys.  Warp roles: warp 0 TMA producer, warp 1 MMA issuer,
-// warps 2-5 softmax + correction + epilogue (one query row per thread: the TMEM lane IS the row, so row max / row
-// sum need no shuffles).
-//   S_j = Q K_j^T          tcgen05.mma 128x64x16, K-major operands, into 64 TMEM columns
+// One CTA = NQ query tiles of 128 rows of one head (NQ = 4 at d <= 64, 2 above), KV blocks of 64 keys, one CTA per
+// SM.  Warp roles: warp 0 TMA producer, warp 1 MMA issuer, then one softmax warpgroup per query tile (softmax +
+// correction + epilogue, one query row per thread: the TMEM lane IS the row, so row max / row sum need no shuffles).
+//   S_j = Q K_j^T          tcgen05.mma 128x64x16, K-major operands, into the tile's 64 TMEM columns
 //   P_j = exp2(S_j - m)    registers -> bf16 -> shared memory in the K-major SWIZZLE_128B layout the MMA expects
 //   O  += P_j V_j          tcgen05.mma 128 x round16(d) x 16, V consumed MN-major straight from its [keys, d]
 //                          row layout (no transpose anywhere), O accumulates in TMEM.
-// The kernel is bound by the MUFU pipe (8192 ex2 per 128x64 block = 512 SM cycles vs 192 MMA cycles at d=40), so the
-// design is about keeping MUFU issue slots full: ONE pass over S per block (lazy running max, below) and a footprint
-// small enough (64 KB smem, 128 TMEM columns, <= 112 registers at d <= 64) for THREE CTAs per SM — while one CTA
-// waits for its PV_j / S_{j+1} round trip through the tensor core, the softmax warps of the other two own the SM's
-// four MUFU units.
+// Measured on B200 (diagnostic builds, N = 4096, d = 40): with one 128-row tile per CTA and four CTAs per SM the
+// kernel sat on TWO equal ceilings — the softmax chain (710 us with the K/V loads removed) and the L2 -> SM traffic
+// of the K/V blocks (750 us with the softmax removed; 374 us with both removed): every 128 query rows re-read all of
+// K and V, 4.3 GB per launch.  Sharing each K/V block between the NQ query tiles of a CTA divides that traffic by NQ
+// and frees the shared memory for a 3-deep K and V ring.  The query tiles run as independent pipelines through the
+// one MMA warp (it polls their barriers round-robin), so while one tile waits for its PV_j / S_{j+1} round trip
+// through the tensor core the softmax warpgroups of the others own the SM's four MUFU units.  ONE pass over S per
+// block (lazy running max, below) keeps the MUFU work at its minimum of 8192 ex2 per 128x64 block.
 // Head dims that are not a multiple of 64 (SD1.5: 40, 80, 160) are handled by TMA itself: the box is 64 wide
 // but the tensor-map extent is d, so columns >= d arrive as zeros and never touch HBM.
 #include <algorithm>
+#include <cstdlib>
 #include <new>
 #include <type_traits>
 
@@ -25,11 +29,14 @@
 
 namespace b200sd {
 #ifdef B200SD_ATT_TRACE
-// Tuning aid (not part of the ABI, compiled only with -DB200SD_ATT_TRACE): clock stamps of CTA (0,0,0)'s roles.
-__device__ unsigned long long g_att_trace[3 * 1024];
+// Tuning aid (not part of the ABI, compiled only with -DB200SD_ATT_TRACE): clock stamps of one CTA's roles (0 TMA, 1 MMA, 2.. softmax of tile 0..).
+#ifndef B200SD_ATT_TRACE_Z
+#define B200SD_ATT_TRACE_Z 0
+#endif
+__device__ unsigned long long g_att_trace[6 * 1024];
 #define ATT_TR(role, id)                                                                                      \
   do {                                                                                                        \
-    if (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && tr_n < 1024)                                  \
+    if (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == B200SD_ATT_TRACE_Z && tr_n < 1024)                                  \
       g_att_trace[(role) * 1024 + tr_n++] = (static_cast<unsigned long long>(id) << 48) | (clock64() & 0xFFFFFFFFFFFFull); \
   } while (0)
 extern "C" __attribute__((visibility("default"))) int b200sd_debug_att_trace(unsigned long long* dst) {
@@ -40,8 +47,7 @@ extern "C" __attribute__((visibility("default"))) int b200sd_debug_att_trace(uns
 #endif
 namespace {
 
-constexpr int ATT_THREADS = 192;
-constexpr int BLK = 128;           // query rows per CTA
+constexpr int BLK = 128;           // rows of a query tile
 constexpr int KB = 64;             // keys per KV block
 constexpr int TILE16K = BLK * 128; // [128 rows x 64 bf16] swizzled tile (Q chunk, P)
 constexpr int TILE8K = KB * 128;   // [64 rows x 64 bf16] swizzled tile (K / V chunk)
@@ -58,20 +64,26 @@ struct alignas(64) AttnParams {
   float scale_log2;
 };
 
-template <int DPAD>
+// NQ = query tiles (softmax warpgroups) per CTA.  The wide configurations (4 tiles at d <= 64, 2 above) own an SM;
+// the single-tile ones keep the small footprint (4 / 2 / 1 CTAs per SM) for grids the wide CTAs would quantize badly.
+template <int DPAD, int NQ>
 struct AttnCfg {
   static constexpr int DB = DPAD / 64;
-  static constexpr int OCC = DPAD == 64 ? 4 : (DPAD == 128 ? 2 : 1);  // CTAs per SM (see the header comment)
-  static constexpr int NSTK = 1;  // K stages: K_j is free as soon as S_j has completed, a whole softmax before K_{j+1} is needed
-  static constexpr int NSTV = DPAD == 64 ? 1 : 2;  // V stages: V_j is free when PV_j has completed, a softmax before V_{j+1} is needed
-  static constexpr int TMEM_COLS = DPAD == 64 ? 128 : 256;            // 64 columns of S, then O (<= DPAD columns)
-  static constexpr int Q_BYTES = DB * TILE16K;
-  static constexpr int KV_BYTES = DB * TILE8K;                        // one K (or V) stage
-  static constexpr int P_BYTES = TILE16K;                             // 128 rows x 64 keys bf16
-  static constexpr int SMEM = Q_BYTES + (NSTK + NSTV) * KV_BYTES + P_BYTES + 1024 + 256;
+  static constexpr int NMMA = NQ >= 4 ? 2 : 1;              // MMA warps; each serves NQ / NMMA tiles
+  static constexpr int THREADS = 64 + 128 * NQ + (NMMA - 1) * 32;  // warp 0 TMA, warp 1 MMA, NQ softmax warpgroups, [last warp MMA]
+  static_assert(NQ % NMMA == 0, "tiles per MMA warp");
+  static constexpr int OCC = NQ > 1 ? 1 : (DPAD == 64 ? 4 : (DPAD == 128 ? 2 : 1));  // CTAs per SM
+  static constexpr int TILE_COLS = KB + DPAD;               // TMEM columns of a tile: 64 of S, then O
+  static constexpr int TMEM_COLS = NQ * TILE_COLS <= 128 ? 128 : (NQ * TILE_COLS <= 256 ? 256 : 512);
+  // ring depths: K_j is free once S_j has completed (a whole softmax before K_{j+1} is needed), V_j once PV_j has
+  static constexpr int NSTK = NQ > 1 ? (DPAD == 192 ? 2 : 3) : 1;
+  static constexpr int NSTV = NQ > 1 ? (DPAD == 192 ? 2 : 3) : (DPAD == 64 ? 1 : 2);
+  static constexpr int QT_BYTES = DB * TILE16K;             // one query tile
+  static constexpr int KV_BYTES = DB * TILE8K;              // one K (or V) stage
+  static constexpr int SMEM = NQ * (QT_BYTES + TILE16K) + (NSTK + NSTV) * KV_BYTES + 1024 + 256;
+  static_assert(OCC * (SMEM + 1024) <= 233472, "shared memory budget");
+  static_assert(OCC * TMEM_COLS <= 512 && NQ * TILE_COLS <= TMEM_COLS, "TMEM budget");
 };
-static_assert(AttnCfg<192>::SMEM <= 232448 && 4 * (AttnCfg<64>::SMEM + 1024) <= 233472 &&
-              2 * (AttnCfg<128>::SMEM + 1024) <= 233472, "shared memory budget");
 
 __device__ __forceinline__ float ex2_approx(float x) {
 #ifdef B200SD_ATT_NOEXP  // diagnostic build only: how fast is everything but the MUFU work?
@@ -85,45 +97,47 @@ __device__ __forceinline__ float ex2_approx(float x) {
 __device__ __forceinline__ void sts128(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
   asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
+// A shared-memory matrix descriptor `bytes` further on (the start address is the low 14 bits, in 16-byte units; shared
+// memory is < 256 KB, so the sum never carries out of the field).
+__device__ __forceinline__ uint64_t desc_advance(uint64_t desc, uint32_t bytes) { return desc + (bytes >> 4); }
 
-template <int DPAD>
-__global__ void __launch_bounds__(ATT_THREADS, AttnCfg<DPAD>::OCC) attention_kernel(const __grid_constant__ AttnParams p) {
-  using Cfg = AttnCfg<DPAD>;
-  constexpr int DB = Cfg::DB;
-  constexpr int NSTK = Cfg::NSTK, NSTV = Cfg::NSTV;
+template <int DPAD, int NQ>
+__global__ void __launch_bounds__(AttnCfg<DPAD, NQ>::THREADS, AttnCfg<DPAD, NQ>::OCC)
+attention_kernel(const __grid_constant__ AttnParams p) {
+  using Cfg = AttnCfg<DPAD, NQ>;
+  constexpr int DB = Cfg::DB, NSTK = Cfg::NSTK, NSTV = Cfg::NSTV;
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* sQ = smem;
-  uint8_t* sK = sQ + Cfg::Q_BYTES;                 // [NSTK][KV_BYTES]
+  uint8_t* sQ = smem;                              // [NQ][QT_BYTES]
+  uint8_t* sP = sQ + NQ * Cfg::QT_BYTES;           // [NQ][TILE16K]
+  uint8_t* sK = sP + NQ * TILE16K;                 // [NSTK][KV_BYTES]
   uint8_t* sV = sK + NSTK * Cfg::KV_BYTES;         // [NSTV][KV_BYTES]
-  uint8_t* sP = sV + NSTV * Cfg::KV_BYTES;         // [TILE16K]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sP + Cfg::P_BYTES);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sV + NSTV * Cfg::KV_BYTES);
   uint64_t* q_full = bars;             // 1
   uint64_t* k_full = bars + 1;         // NSTK
-  uint64_t* k_empty = k_full + NSTK;   // NSTK
+  uint64_t* k_empty = k_full + NSTK;   // NSTK  (one arrival per live tile: its S_j has completed)
   uint64_t* v_full = k_empty + NSTK;   // NSTV
-  uint64_t* v_empty = v_full + NSTV;   // NSTV
-  uint64_t* s_full = v_empty + NSTV;   // 1
-  uint64_t* p_full = s_full + 1;       // 1
-  uint64_t* pv_done = p_full + 1;      // 1
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(pv_done + 1);
+  uint64_t* v_empty = v_full + NSTV;   // NSTV  (one arrival per live tile: its PV_j has completed)
+  uint64_t* s_full = v_empty + NSTV;   // NQ
+  uint64_t* p_full = s_full + NQ;      // NQ    (128 arrivals: the tile's softmax threads)
+  uint64_t* pv_done = p_full + NQ;     // NQ
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(pv_done + NQ);
 
   pdl_launch_dependents();
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const int q0 = blockIdx.x * BLK;
+  const int q0 = blockIdx.x * (BLK * NQ);
   const int head = blockIdx.y;
   const int batch = blockIdx.z;
   const int nkv = p.kv_blocks;
+  const int live = min(NQ, (p.Nq - q0 + BLK - 1) / BLK);  // query tiles of this CTA that exist (>= 1)
 
   if (threadIdx.x == 0) {
     mbar_init(q_full, 1);
-    for (int i = 0; i < NSTK; ++i) { mbar_init(&k_full[i], 1); mbar_init(&k_empty[i], 1); }
-    for (int i = 0; i < NSTV; ++i) { mbar_init(&v_full[i], 1); mbar_init(&v_empty[i], 1); }
-    mbar_init(s_full, 1);
-    mbar_init(p_full, 128);
-    mbar_init(pv_done, 1);
+    for (int i = 0; i < NSTK; ++i) { mbar_init(&k_full[i], 1); mbar_init(&k_empty[i], live); }
+    for (int i = 0; i < NSTV; ++i) { mbar_init(&v_full[i], 1); mbar_init(&v_empty[i], live); }
+    for (int t = 0; t < NQ; ++t) { mbar_init(&s_full[t], 1); mbar_init(&p_full[t], 128); mbar_init(&pv_done[t], 1); }
     fence_barrier_init();
   }
   if (warp == 1) { tmem_alloc(tmem_slot, Cfg::TMEM_COLS); tmem_relinquish(); }
@@ -133,39 +147,57 @@ __global__ void __launch_bounds__(ATT_THREADS, AttnCfg<DPAD>::OCC) attention_ker
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   pdl_wait();  // the prologue above overlapped the previous kernel's tail
-  const uint32_t tmem_S = tmem_base;       // 64 columns
-  const uint32_t tmem_O = tmem_base + KB;  // round16(d) columns
 
   if (warp == 0) {
     // ===================== TMA producer =====================
     if (elect_one()) {
-      mbar_arrive_expect_tx(q_full, Cfg::Q_BYTES);
-      for (int db = 0; db < DB; ++db) tma_load_4d(sQ + db * TILE16K, &p.tmQ, q_full, db * 64, head, q0, batch);
+      mbar_arrive_expect_tx(q_full, live * Cfg::QT_BYTES);
+      for (int t = 0; t < live; ++t)
+        for (int db = 0; db < DB; ++db)
+          tma_load_4d(sQ + t * Cfg::QT_BYTES + db * TILE16K, &p.tmQ, q_full, db * 64, head, q0 + t * BLK, batch);
       int tr_n = 0; (void)tr_n;
       for (int j = 0; j < nkv; ++j) {
         const int sk = j % NSTK, sv = j % NSTV;
         mbar_wait(&k_empty[sk], ((j / NSTK) & 1) ^ 1);
         ATT_TR(0, 9);
-        mbar_arrive_expect_tx(&k_full[sk], Cfg::KV_BYTES);
-        for (int db = 0; db < DB; ++db)
-          tma_load_4d(sK + sk * Cfg::KV_BYTES + db * TILE8K, &p.tmK, &k_full[sk], db * 64, head, j * KB, batch);
+#ifdef B200SD_ATT_NOKV  // diagnostic build only: K/V blocks after the first ring fill are not loaded
+        if (j >= NSTK) { mbar_arrive(&k_full[sk]); } else
+#endif
+        {
+          mbar_arrive_expect_tx(&k_full[sk], Cfg::KV_BYTES);
+          for (int db = 0; db < DB; ++db)
+            tma_load_4d(sK + sk * Cfg::KV_BYTES + db * TILE8K, &p.tmK, &k_full[sk], db * 64, head, j * KB, batch);
+        }
         mbar_wait(&v_empty[sv], ((j / NSTV) & 1) ^ 1);
         ATT_TR(0, 10);
-        mbar_arrive_expect_tx(&v_full[sv], Cfg::KV_BYTES);
-        for (int db = 0; db < DB; ++db)
-          tma_load_4d(sV + sv * Cfg::KV_BYTES + db * TILE8K, &p.tmV, &v_full[sv], db * 64, head, j * KB, batch);
+#ifdef B200SD_ATT_NOKV
+        if (j >= NSTV) { mbar_arrive(&v_full[sv]); } else
+#endif
+        {
+          mbar_arrive_expect_tx(&v_full[sv], Cfg::KV_BYTES);
+          for (int db = 0; db < DB; ++db)
+            tma_load_4d(sV + sv * Cfg::KV_BYTES + db * TILE8K, &p.tmV, &v_full[sv], db * 64, head, j * KB, batch);
+        }
       }
     }
-  } else if (warp == 1) {
-    // ===================== MMA issuer =====================
-    // This warp shares its SM sub-partition with the softmax warps of up to three CTAs, so every instruction between
-    // "P_j is ready" and "S_{j+1} is issued" sits on the critical path of the whole CTA at a fraction of the issue
-    // rate: all smem descriptors are built once, up front, and the operand barriers (V_j, K_{j+1}: both land long
-    // before P_j) are waited for BEFORE the P barrier — what remains after it is 7 tcgen05.mma and 4 commits.
+  } else if (warp == 1 || warp == 2 + 4 * NQ) {
+    // ===================== MMA issuers =====================
+    // Per tile and block j the hand-off is: the tile's softmax warpgroup has written P_j (and finished reading S_j) ->
+    // issue S_{j+1} (what that warpgroup waits for next), then PV_j.  A service costs ~500 cycles of the issuing warp
+    // (it shares its SM sub-partition with softmax warps), so four tiles get two issuer warps; each serves its tiles
+    // in a FIXED round-robin order with blocking waits.  The tiles settle into a staggered steady state (a tile's
+    // softmax runs while the next one is served).  Measured alternatives at N = 4096, d = 40: one warp for all four
+    // tiles 809 us, one warp polling the barriers of four tiles 1022 us (a probe is a serialized shared-memory round
+    // trip), one warp per tile 700 us, this 670 us.  In-order service is deadlock-free: block j of every tile of a warp
+    // is issued before block j+1 of any, and the two warps depend on each other only through the K/V ring, which the
+    // producer refills as soon as the LAST tile's MMA has released a slot.  All shared-memory descriptors are built
+    // once, up front; a tile or ring slot is a constant added to the start-address field.
+    constexpr int TPW = NQ / Cfg::NMMA;            // tiles per MMA warp
+    const int t_first = warp == 1 ? 0 : TPW;       // this warp's tiles: [t_first, t_first + TPW)
     constexpr int KS_MAX = DPAD / 16;
     const uint32_t idesc_s = umma_idesc_bf16(BLK, KB, 0);
     const uint32_t idesc_o = umma_idesc_bf16(BLK, p.n_pv, 1);
-    uint64_t dq[KS_MAX], dk[KS_MAX], dp[KB / 16], dv0[KB / 16], dv1[KB / 16];
+    uint64_t dq[KS_MAX], dk[KS_MAX], dp[KB / 16], dv[KB / 16];
     {
       const uint32_t q_addr = smem_u32(sQ), k_addr = smem_u32(sK), p_addr = smem_u32(sP), v_addr = smem_u32(sV);
 #pragma unroll
@@ -177,51 +209,68 @@ __global__ void __launch_bounds__(ATT_THREADS, AttnCfg<DPAD>::OCC) attention_ker
       for (int ks = 0; ks < KB / 16; ++ks) {
         dp[ks] = umma_smem_desc_sw128(p_addr + ks * 32, 16, 1024);
         // V: MN-major; 16 keys = 2 groups of 8 rows (SBO 1024), 64-wide d chunks TILE8K apart (LBO)
-        dv0[ks] = umma_smem_desc_sw128(v_addr + ks * 2048, TILE8K, 1024);
-        dv1[ks] = umma_smem_desc_sw128(v_addr + (NSTV - 1) * Cfg::KV_BYTES + ks * 2048, TILE8K, 1024);
+        dv[ks] = umma_smem_desc_sw128(v_addr + ks * 2048, TILE8K, 1024);
       }
     }
-    static_assert(NSTK == 1 && NSTV <= 2, "descriptor tables assume one K stage and at most two V stages");
     int tr_n = 0; (void)tr_n;
-    auto issue_S = [&]() {  // S = Q K^T (lane 0); the K stage is released when it completes
+    // S_t(jn) = Q_t K_jn^T (one elected lane); the K slot gets this tile's release when the product completes
+    auto issue_S = [&](int t, int jn) {
+      const uint32_t q_off = t * Cfg::QT_BYTES, k_off = (jn % NSTK) * Cfg::KV_BYTES;
+      const uint32_t tmem_S = tmem_base + t * Cfg::TILE_COLS;
 #pragma unroll
       for (int ks = 0; ks < KS_MAX; ++ks)
-        if (ks < p.ksteps_qk) umma_bf16_ss(tmem_S, dq[ks], dk[ks], idesc_s, ks != 0 ? 1u : 0u);
-      umma_commit(s_full);
-      umma_commit(&k_empty[0]);
+        if (ks < p.ksteps_qk)
+          umma_bf16_ss(tmem_S, desc_advance(dq[ks], q_off), desc_advance(dk[ks], k_off), idesc_s, ks != 0 ? 1u : 0u);
+      umma_commit(&s_full[t]);
+      umma_commit(&k_empty[jn % NSTK]);
     };
     mbar_wait(q_full, 0);
     mbar_wait(&k_full[0], 0);
     tc_fence_after();
-    if (elect_one()) issue_S();
+    if (elect_one()) {
+      for (int t = t_first; t < min(live, t_first + TPW); ++t) issue_S(t, 0);
+    }
     __syncwarp();
     for (int j = 0; j < nkv; ++j) {
       const int st = j % NSTV;
-      mbar_wait(&v_full[st], (j / NSTV) & 1);             // V_j: loaded a block ago
-      if (j + 1 < nkv) mbar_wait(&k_full[0], (j + 1) & 1);  // K_{j+1}: loaded while the softmax of block j ran
-      mbar_wait(p_full, j & 1);                            // P_j written and S_j fully read
-      tc_fence_after();
-      if (elect_one()) {
-        ATT_TR(1, 4);
-        if (j + 1 < nkv) issue_S();  // S_{j+1} first: it is what the softmax warps are waiting for
-        ATT_TR(1, 6);
+      mbar_wait(&v_full[st], (j / NSTV) & 1);                                    // V_j: loaded a block or more ago
+      if (j + 1 < nkv) mbar_wait(&k_full[(j + 1) % NSTK], ((j + 1) / NSTK) & 1);  // K_{j+1}: likewise
 #pragma unroll
-        for (int ks = 0; ks < KB / 16; ++ks)
-          umma_bf16_ss(tmem_O, dp[ks], st ? dv1[ks] : dv0[ks], idesc_o, (j | ks) != 0 ? 1u : 0u);
-        umma_commit(pv_done);
-        umma_commit(&v_empty[st]);
-        ATT_TR(1, 8);
+      for (int tt = 0; tt < TPW; ++tt) {
+        const int t = t_first + tt;
+        if (t < live) {
+          mbar_wait(&p_full[t], j & 1);  // P_j of tile t written and its S_j fully read
+          tc_fence_after();
+          if (elect_one()) {
+            if (t == 0) ATT_TR(1, 4);
+            if (j + 1 < nkv) issue_S(t, j + 1);  // S_{j+1} first: it is what the softmax warpgroup is waiting for
+            if (t == 0) ATT_TR(1, 6);
+            const uint32_t p_off = t * TILE16K, v_off = st * Cfg::KV_BYTES;
+            const uint32_t tmem_O = tmem_base + t * Cfg::TILE_COLS + KB;
+#pragma unroll
+            for (int ks = 0; ks < KB / 16; ++ks)
+              umma_bf16_ss(tmem_O, desc_advance(dp[ks], p_off), desc_advance(dv[ks], v_off), idesc_o, (j | ks) != 0 ? 1u : 0u);
+            umma_commit(&pv_done[t]);
+            umma_commit(&v_empty[st]);
+            if (t == 0) ATT_TR(1, 8);
+          }
+          __syncwarp();
+        }
       }
-      __syncwarp();
     }
   } else {
     // ===================== softmax / correction / epilogue: thread <-> query row =====================
-    const int q = warp & 3;
+    const int t = (warp - 2) >> 2;  // query tile of this warpgroup
+    const int q = warp & 3;         // TMEM lane quarter this warp may touch
     const int r = q * 32 + lane;
     const uint32_t lane_base = static_cast<uint32_t>(q * 32) << 16;
-    const uint32_t s_addr = tmem_S + lane_base;
-    const uint32_t o_addr = tmem_O + lane_base;
-    const uint32_t prow = smem_u32(sP) + r * 128;
+    const uint32_t s_addr = tmem_base + t * Cfg::TILE_COLS + lane_base;
+    const uint32_t o_addr = s_addr + KB;
+    const uint32_t prow = smem_u32(sP) + t * TILE16K + r * 128;
+    uint64_t* const my_s_full = &s_full[t];
+    uint64_t* const my_p_full = &p_full[t];
+    uint64_t* const my_pv_done = &pv_done[t];
+    const int nblk = t < live ? nkv : 0;  // a warpgroup whose tile lies beyond Nq has nothing to do
     const int rsw = r & 7;
     float m_run = -INFINITY;  // softmax reference point of this row, scaled log2 domain
     float l_run = 0.f;
@@ -232,12 +281,12 @@ __global__ void __launch_bounds__(ATT_THREADS, AttnCfg<DPAD>::OCC) attention_ker
     // reference only has to move (and O be rescaled) when a row's scores outgrow it by more than 2^LAZY_TAU — then
     // the warp redoes its block with the exact max (S_j is still in TMEM).
     constexpr float LAZY_TAU = 8.0f;
-    for (int j = 0; j < nkv; ++j) {
+    for (int j = 0; j < nblk; ++j) {
       const int valid = min(KB, p.Nkv - j * KB);  // keys of this block that exist
-      mbar_wait(s_full, j & 1);
+      mbar_wait(my_s_full, j & 1);
       tc_fence_after();
       bool p_busy = j > 0;  // PV_{j-1} is issued right AFTER S_j: it may still be reading P when S_j lands
-      if (warp == 2 && lane == 0) ATT_TR(2, 1);
+      if (q == 2 && lane == 0) ATT_TR(2 + t, 1);
       // probabilities -> bf16 -> swizzled smem (K-major, 128-byte rows, 16-byte chunk ^= row % 8); returns the row sum
       auto exp_pass = [&](auto masked_tag, const float m_ref, float& mx_out) {
         constexpr bool MASKED = decltype(masked_tag)::value;
@@ -263,14 +312,11 @@ __global__ void __launch_bounds__(ATT_THREADS, AttnCfg<DPAD>::OCC) attention_ker
             pk[i] = pack_bf16x2(p0, p1);
           }
           if (p_busy) {  // (complete long before the first chunk's exponentials are)
-            mbar_wait(pv_done, (j - 1) & 1);
+            mbar_wait(my_pv_done, (j - 1) & 1);
             p_busy = false;
           }
 #pragma unroll
           for (int i = 0; i < 4; ++i) {
-#ifdef B200SD_ATT_NOSTS  // diagnostic build only
-            if (pk[4 * i] == 0x12345678u)
-#endif
             sts128(prow + (((c * 4 + i) ^ rsw) << 4), pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
           }
         }
@@ -305,7 +351,7 @@ __global__ void __launch_bounds__(ATT_THREADS, AttnCfg<DPAD>::OCC) attention_ker
           rsum = exp_pass(masked_tag, m_run, m_blk);
           l_run *= alpha;
           // O *= alpha once PV_{j-1} (the latest PV issued) has landed
-          mbar_wait(pv_done, (j - 1) & 1);
+          mbar_wait(my_pv_done, (j - 1) & 1);
           tc_fence_after();
 #pragma unroll 1
           for (int c = 0; c < p.n_pv / 16; ++c) {
@@ -320,19 +366,22 @@ __global__ void __launch_bounds__(ATT_THREADS, AttnCfg<DPAD>::OCC) attention_ker
         }
         l_run += rsum;
       };
+#ifdef B200SD_ATT_NOSOFTMAX  // diagnostic build only
+      if (j > 0) l_run = 1.f; else
+#endif
       if (valid == KB) block_body(std::false_type{});
       else block_body(std::true_type{});
-      if (warp == 2 && lane == 0) ATT_TR(2, 2);
+      if (q == 2 && lane == 0) ATT_TR(2 + t, 2);
       fence_proxy_async_smem();  // P (generic-proxy stores) -> visible to the MMA's async-proxy reads
       tc_fence_before();
-      mbar_arrive(p_full);
-      if (warp == 2 && lane == 0) ATT_TR(2, 3);
+      mbar_arrive(my_p_full);
+      if (q == 2 && lane == 0) ATT_TR(2 + t, 3);
     }
     // ---- epilogue: O / l -> bf16 -> global ----
-    mbar_wait(pv_done, (nkv - 1) & 1);
+    if (nblk > 0) mbar_wait(my_pv_done, (nkv - 1) & 1);
     tc_fence_after();
     const float inv_l = 1.0f / l_run;
-    const int qrow = q0 + r;
+    const int qrow = nblk > 0 ? q0 + t * BLK + r : p.Nq;
     bf16* orow = p.out + (static_cast<long long>(batch) * p.Nq + qrow) * p.ldo + head * p.d;
 #pragma unroll 1
     for (int c = 0; c < p.n_pv / 16; ++c) {
@@ -358,41 +407,66 @@ __global__ void __launch_bounds__(ATT_THREADS, AttnCfg<DPAD>::OCC) attention_ker
 
 struct AttnPlan {
   AttnParams kp;
-  int dpad;
+  int dpad, nq;
   dim3 grid;
 };
 
-template <int DPAD>
+template <int DPAD, int NQ>
 int prepare_attention_t() {  // plan time, outside any stream capture
   static bool attr_set = false;
   if (!attr_set) {
-    B200SD_CUDA(cudaFuncSetAttribute(attention_kernel<DPAD>, cudaFuncAttributeMaxDynamicSharedMemorySize, AttnCfg<DPAD>::SMEM));
+    B200SD_CUDA(cudaFuncSetAttribute(attention_kernel<DPAD, NQ>, cudaFuncAttributeMaxDynamicSharedMemorySize, AttnCfg<DPAD, NQ>::SMEM));
     attr_set = true;
   }
   return 0;
 }
-int prepare_attention(int dpad) {
-  switch (dpad) {
-    case 64: return prepare_attention_t<64>();
-    case 128: return prepare_attention_t<128>();
-    case 192: return prepare_attention_t<192>();
-  }
-  return fail(B200SD_ERR_UNSUPPORTED, "attention: padded head dim %d unsupported", dpad);
-}
-
-template <int DPAD>
+template <int DPAD, int NQ>
 int launch_attention_t(const AttnPlan& pl, cudaStream_t s) {
-  B200SD_CUDA(launch_kernel(attention_kernel<DPAD>, pl.grid, dim3(ATT_THREADS), AttnCfg<DPAD>::SMEM, s, 1, pl.kp));
+  using Cfg = AttnCfg<DPAD, NQ>;
+  B200SD_CUDA(launch_kernel(attention_kernel<DPAD, NQ>, pl.grid, dim3(Cfg::THREADS), Cfg::SMEM, s, 1, pl.kp));
   return 0;
+}
+// One switch for both uses: LAUNCH = false sets the kernel attribute, true launches.
+template <bool LAUNCH>
+int dispatch_attention(int dpad, int nq, const AttnPlan* pl, cudaStream_t s) {
+#define B200SD_ATT_CASE(D, Q) \
+  if (dpad == D && nq == Q) { if constexpr (LAUNCH) return launch_attention_t<D, Q>(*pl, s); else return prepare_attention_t<D, Q>(); }
+  B200SD_ATT_CASE(64, 4)
+  B200SD_ATT_CASE(64, 1)
+  B200SD_ATT_CASE(128, 2)
+  B200SD_ATT_CASE(128, 1)
+  B200SD_ATT_CASE(192, 2)
+  B200SD_ATT_CASE(192, 1)
+#undef B200SD_ATT_CASE
+  return fail(B200SD_ERR_UNSUPPORTED, "attention: padded head dim %d with %d query tiles per CTA unsupported", dpad, nq);
 }
 int launch_attention(const void* plan, cudaStream_t s) {
   const AttnPlan& pl = *static_cast<const AttnPlan*>(plan);
-  switch (pl.dpad) {
-    case 64: return launch_attention_t<64>(pl, s);
-    case 128: return launch_attention_t<128>(pl, s);
-    case 192: return launch_attention_t<192>(pl, s);
+  return dispatch_attention<true>(pl.dpad, pl.nq, &pl, s);
+}
+int wide_tiles(int dpad) { return dpad == 64 ? 4 : 2; }
+int occupancy(int dpad, int nq) { return nq > 1 ? 1 : (dpad == 64 ? 4 : (dpad == 128 ? 2 : 1)); }
+
+// Query tiles per CTA for a problem: the wide CTA (K/V blocks shared by its tiles, deep rings) unless its grid
+// quantizes worse on the 148 SMs than the single-tile one (B200SD_ATT_NQ overrides, for tuning).
+int choose_tiles(int dpad, int B, int heads, int Nq, int kv_blocks) {
+  if (const char* e = std::getenv("B200SD_ATT_NQ")) {
+    const int v = std::atoi(e);
+    if (v == 1 || v == wide_tiles(dpad)) return v;
   }
-  return fail(B200SD_ERR_UNSUPPORTED, "attention: padded head dim %d unsupported", pl.dpad);
+  if (kv_blocks <= 2) return 1;  // cross-attention (77 keys): the run is all prologue, which the small CTA keeps short
+  const int sms = sm_count();
+  const long long tiles = static_cast<long long>((Nq + BLK - 1) / BLK);
+  auto cost = [&](int nq) {
+    const long long ctas = ((tiles + nq - 1) / nq) * heads * B;
+    const double per_sm = static_cast<double>((ctas + sms - 1) / sms);  // CTAs the busiest SM works through
+    // per-CTA time in units of one tile running alone on an SM share: a single-tile CTA runs `occ` to an SM; a wide one
+    // owns the SM for its nq tiles, each ~12% cheaper for sharing K/V (measured 0.77-0.93 across the SD shapes)
+    const double per_cta = (nq == 1 ? 1.0 : 0.88 * nq) / static_cast<double>(occupancy(dpad, 1));
+    return per_sm * per_cta;
+  };
+  const int wide = wide_tiles(dpad);
+  return cost(wide) < cost(1) ? wide : 1;
 }
 
 }  // namespace
@@ -428,8 +502,10 @@ int plan_attention(const b200sd_attention& a, PlannedOp* out) {
   kp.ksteps_qk = (a.d + 15) / 16;
   kp.scale_log2 = a.scale * 1.4426950408889634f;
   pl->dpad = (a.d + 63) / 64 * 64;
-  pl->grid = dim3((a.Nq + BLK - 1) / BLK, a.heads, a.B);
-  rc = prepare_attention(pl->dpad);
+  pl->nq = choose_tiles(pl->dpad, a.B, a.heads, a.Nq, kp.kv_blocks);
+  const int rows_per_cta = BLK * pl->nq;
+  pl->grid = dim3((a.Nq + rows_per_cta - 1) / rows_per_cta, a.heads, a.B);
+  rc = dispatch_attention<false>(pl->dpad, pl->nq, nullptr, nullptr);
   if (rc) { delete pl; return rc; }
   out->kind = B200SD_OP_ATTENTION;
   out->plan = pl;

@@ -12,15 +12,15 @@ b.attention(bf(B, Nq, h * d), bf(B, Nk, h * d), bf(B, Nk, h * d), h, d, d ** -0.
 s = torch.cuda.current_stream().cuda_stream
 b.prog.run(s); torch.cuda.synchronize()
 b.prog.run(s); torch.cuda.synchronize()
-buf = (C.c_ulonglong * 3072)()
+buf = (C.c_ulonglong * 6144)()
 N.lib().b200sd_debug_att_trace(buf)
-names = {0: "tma", 1: "mma", 2: "softmax"}
+names = {0: "tma", 1: "mma", 2: "sm0", 3: "sm1", 4: "sm2", 5: "sm3"}
 ev = []
-for role in range(3):
+for role in range(6):
     for i in range(1024):
         v = buf[role * 1024 + i]
         if v: ev.append((v & 0xFFFFFFFFFFFF, role, v >> 48))
 ev.sort(); t0 = ev[0][0]
-lo, hi = int(os.environ.get("TRACE_LO", "0")), int(os.environ.get("TRACE_HI", "300"))
+lo, hi = int(os.environ.get("TRACE_LO", "0")), int(os.environ.get("TRACE_HI", "100000"))
 for t, role, idn in ev[lo:hi]:
-    print(f"{t - t0:8d} {'            ' * role}{names[role]}:{idn}")
+    print(f"{t - t0:8d} {'         ' * role}{names[role]}:{idn}")

@@ -54,6 +54,13 @@ conv("conv_16x8x8_1280_1280", 16, 8, 1280, 1280)
 att("attn_self_4096_d40", 16, 8, 4096, 4096, 40)
 att("attn_self_1024_d80", 16, 8, 1024, 1024, 80)
 att("attn_cross_4096_d40", 16, 8, 4096, 77, 40)
+att("attn_cross_1024_d80", 16, 8, 1024, 77, 80)
+att("attn_self_256_d160", 16, 8, 256, 256, 160)
+att("attn_self_64_d160", 16, 8, 64, 64, 160)
+att("attn_self_4096_d40_b2", 2, 8, 4096, 4096, 40)
+att("attn_self_1024_d80_b2", 2, 8, 1024, 1024, 80)
+att("attn_xl_4096_d64", 4, 10, 4096, 4096, 64)
+att("attn_xl_1024_d64", 4, 20, 1024, 1024, 64)
 gn("gn_16x4096x320", 16, 4096, 320)
 ln("ln_65536x320", 65536, 320)
 
