@@ -122,7 +122,8 @@ attention_kernel(const __grid_constant__ AttnParams p) {
   uint64_t* s_full = v_empty + NSTV;   // NQ
   uint64_t* p_full = s_full + NQ;      // NQ    (128 arrivals: the tile's softmax threads)
   uint64_t* pv_done = p_full + NQ;     // NQ
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(pv_done + NQ);
+  uint64_t* s_free = pv_done + NQ;     // NQ    (128 arrivals: S_j has been read out)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(s_free + NQ);
 
   pdl_launch_dependents();
   const int warp = threadIdx.x >> 5;
@@ -137,7 +138,9 @@ attention_kernel(const __grid_constant__ AttnParams p) {
     mbar_init(q_full, 1);
     for (int i = 0; i < NSTK; ++i) { mbar_init(&k_full[i], 1); mbar_init(&k_empty[i], live); }
     for (int i = 0; i < NSTV; ++i) { mbar_init(&v_full[i], 1); mbar_init(&v_empty[i], live); }
-    for (int t = 0; t < NQ; ++t) { mbar_init(&s_full[t], 1); mbar_init(&p_full[t], 128); mbar_init(&pv_done[t], 1); }
+    for (int t = 0; t < NQ; ++t) {
+      mbar_init(&s_full[t], 1); mbar_init(&p_full[t], 128); mbar_init(&pv_done[t], 1); mbar_init(&s_free[t], 128);
+    }
     fence_barrier_init();
   }
   if (warp == 1) { tmem_alloc(tmem_slot, Cfg::TMEM_COLS); tmem_relinquish(); }
@@ -182,8 +185,8 @@ attention_kernel(const __grid_constant__ AttnParams p) {
     }
   } else if (warp == 1 || warp == 2 + 4 * NQ) {
     // ===================== MMA issuers =====================
-    // Per tile and block j the hand-off is: the tile's softmax warpgroup has written P_j (and finished reading S_j) ->
-    // issue S_{j+1} (what that warpgroup waits for next), then PV_j.  A service costs ~500 cycles of the issuing warp
+    // Per tile and block j there are two hand-offs: the tile's softmax warpgroup has read S_j out -> issue S_{j+1};
+    // it has written P_j -> issue PV_j.  Such a pair of services costs ~500 cycles of the issuing warp
     // (it shares its SM sub-partition with softmax warps), so four tiles get two issuer warps; each serves its tiles
     // in a FIXED round-robin order with blocking waits.  The tiles settle into a staggered steady state (a tile's
     // softmax runs while the next one is served).  Measured alternatives at N = 4096, d = 40: one warp for all four
@@ -232,19 +235,33 @@ attention_kernel(const __grid_constant__ AttnParams p) {
     }
     __syncwarp();
     for (int j = 0; j < nkv; ++j) {
+      if (j + 1 < nkv) {
+        mbar_wait(&k_full[(j + 1) % NSTK], ((j + 1) / NSTK) & 1);  // K_{j+1}: loaded a block or more ago
+#pragma unroll
+        for (int tt = 0; tt < TPW; ++tt) {
+          const int t = t_first + tt;
+          if (t < live) {
+            mbar_wait(&s_free[t], j & 1);  // S_j of tile t read out (half a block before P_j is complete)
+            tc_fence_after();
+            if (elect_one()) {
+              if (t == 0) ATT_TR(1, 4);
+              issue_S(t, j + 1);
+              if (t == 0) ATT_TR(1, 6);
+            }
+            __syncwarp();
+          }
+        }
+      }
       const int st = j % NSTV;
-      mbar_wait(&v_full[st], (j / NSTV) & 1);                                    // V_j: loaded a block or more ago
-      if (j + 1 < nkv) mbar_wait(&k_full[(j + 1) % NSTK], ((j + 1) / NSTK) & 1);  // K_{j+1}: likewise
+      mbar_wait(&v_full[st], (j / NSTV) & 1);  // V_j: likewise
 #pragma unroll
       for (int tt = 0; tt < TPW; ++tt) {
         const int t = t_first + tt;
         if (t < live) {
-          mbar_wait(&p_full[t], j & 1);  // P_j of tile t written and its S_j fully read
+          mbar_wait(&p_full[t], j & 1);  // P_j of tile t written
           tc_fence_after();
           if (elect_one()) {
-            if (t == 0) ATT_TR(1, 4);
-            if (j + 1 < nkv) issue_S(t, j + 1);  // S_{j+1} first: it is what the softmax warpgroup is waiting for
-            if (t == 0) ATT_TR(1, 6);
+            if (t == 0) ATT_TR(1, 7);
             const uint32_t p_off = t * TILE16K, v_off = st * Cfg::KV_BYTES;
             const uint32_t tmem_O = tmem_base + t * Cfg::TILE_COLS + KB;
 #pragma unroll
@@ -270,6 +287,7 @@ attention_kernel(const __grid_constant__ AttnParams p) {
     uint64_t* const my_s_full = &s_full[t];
     uint64_t* const my_p_full = &p_full[t];
     uint64_t* const my_pv_done = &pv_done[t];
+    uint64_t* const my_s_free = &s_free[t];
     const int nblk = t < live ? nkv : 0;  // a warpgroup whose tile lies beyond Nq has nothing to do
     const int rsw = r & 7;
     float m_run = -INFINITY;  // softmax reference point of this row, scaled log2 domain
@@ -279,96 +297,107 @@ attention_kernel(const __grid_constant__ AttnParams p) {
     // max of the keys BEFORE this block, and the block's own max is tracked in the same pass.  Softmax is invariant
     // to the reference point; bf16 P and the fp32 row sum keep their relative precision at any magnitude, so the
     // reference only has to move (and O be rescaled) when a row's scores outgrow it by more than 2^LAZY_TAU — then
-    // the warp redoes its block with the exact max (S_j is still in TMEM).
+    // the warp redoes its block with the exact max (S_j is still in TMEM: the warp has not released it yet).
+    // S_j is released to the MMA warp as soon as its second half sits in registers (and its max is known to be
+    // harmless), i.e. half a block BEFORE P_j is complete: S_{j+1} is computed under the second half's exponentials,
+    // so the warpgroup goes from block to block without waiting for the tensor core.
     constexpr float LAZY_TAU = 8.0f;
     for (int j = 0; j < nblk; ++j) {
       const int valid = min(KB, p.Nkv - j * KB);  // keys of this block that exist
       mbar_wait(my_s_full, j & 1);
       tc_fence_after();
-      bool p_busy = j > 0;  // PV_{j-1} is issued right AFTER S_j: it may still be reading P when S_j lands
+      bool p_busy = j > 0;  // PV_{j-1} may still be reading P when S_j lands
       if (q == 2 && lane == 0) ATT_TR(2 + t, 1);
-      // probabilities -> bf16 -> swizzled smem (K-major, 128-byte rows, 16-byte chunk ^= row % 8); returns the row sum
-      auto exp_pass = [&](auto masked_tag, const float m_ref, float& mx_out) {
+      // max of the valid raw scores of 32-key chunk c
+      auto raw_max = [&](auto masked_tag, int c, const uint32_t (&u)[32]) {
         constexpr bool MASKED = decltype(masked_tag)::value;
-        float rsum = 0.f, mx = -INFINITY;
+        float mx = -INFINITY;
 #pragma unroll
-        for (int c = 0; c < KB / 32; ++c) {
-          uint32_t u[32];
-          tmem_ld32(s_addr + c * 32, u);
-          tmem_ld_wait();
-          uint32_t pk[16];
+        for (int i = 0; i < 32; ++i)
+          if (!MASKED || c * 32 + i < valid) mx = fmaxf(mx, __uint_as_float(u[i]));
+        return mx;
+      };
+      // chunk c: probabilities relative to m_ref -> bf16 -> swizzled smem (K-major, 128-byte rows, 16-byte piece ^=
+      // row % 8); returns the chunk's row sum
+      auto exp_store = [&](auto masked_tag, int c, const uint32_t (&u)[32], const float m_ref) {
+        constexpr bool MASKED = decltype(masked_tag)::value;
+        float rsum = 0.f;
+        uint32_t pk[16];
 #pragma unroll
-          for (int i = 0; i < 16; ++i) {
-            const float s0 = __uint_as_float(u[2 * i]), s1 = __uint_as_float(u[2 * i + 1]);
-            float p0 = ex2_approx(fmaf(s0, p.scale_log2, -m_ref));
-            float p1 = ex2_approx(fmaf(s1, p.scale_log2, -m_ref));
-            if (MASKED) {
-              if (c * 32 + 2 * i >= valid) p0 = 0.f; else mx = fmaxf(mx, s0);
-              if (c * 32 + 2 * i + 1 >= valid) p1 = 0.f; else mx = fmaxf(mx, s1);
-            } else {
-              mx = fmaxf(mx, fmaxf(s0, s1));
-            }
-            rsum += p0 + p1;
-            pk[i] = pack_bf16x2(p0, p1);
+        for (int i = 0; i < 16; ++i) {
+          float p0 = ex2_approx(fmaf(__uint_as_float(u[2 * i]), p.scale_log2, -m_ref));
+          float p1 = ex2_approx(fmaf(__uint_as_float(u[2 * i + 1]), p.scale_log2, -m_ref));
+          if (MASKED) {
+            if (c * 32 + 2 * i >= valid) p0 = 0.f;
+            if (c * 32 + 2 * i + 1 >= valid) p1 = 0.f;
           }
-          if (p_busy) {  // (complete long before the first chunk's exponentials are)
-            mbar_wait(my_pv_done, (j - 1) & 1);
-            p_busy = false;
-          }
-#pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            sts128(prow + (((c * 4 + i) ^ rsw) << 4), pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
-          }
+          rsum += p0 + p1;
+          pk[i] = pack_bf16x2(p0, p1);
         }
-        mx_out = mx * p.scale_log2;
+        if (p_busy) {  // (complete long before the first chunk's exponentials are)
+          mbar_wait(my_pv_done, (j - 1) & 1);
+          p_busy = false;
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+          sts128(prow + (((c * 4 + i) ^ rsw) << 4), pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
         return rsum;
       };
       // The body is instantiated twice: the mask-free version runs on every full block (no per-element predicates).
       auto block_body = [&](auto masked_tag) {
-        constexpr bool MASKED = decltype(masked_tag)::value;
+        uint32_t u[32];
         if (j == 0) {  // very first block: exact max (nothing to rescale yet)
           float mx = -INFINITY;
 #pragma unroll
           for (int c = 0; c < KB / 32; ++c) {
-            uint32_t u[32];
             tmem_ld32(s_addr + c * 32, u);
             tmem_ld_wait();
-#pragma unroll
-            for (int i = 0; i < 32; ++i)
-              if (!MASKED || c * 32 + i < valid) mx = fmaxf(mx, __uint_as_float(u[i]));
+            mx = fmaxf(mx, raw_max(masked_tag, c, u));
           }
           m_run = mx * p.scale_log2;
         }
-        float m_blk;
-        float rsum = exp_pass(masked_tag, m_run, m_blk);
+        tmem_ld32(s_addr, u);
+        tmem_ld_wait();
+        float mx = raw_max(masked_tag, 0, u);
+        float rsum = exp_store(masked_tag, 0, u, m_run);
+        tmem_ld32(s_addr + 32, u);
+        tmem_ld_wait();
+        mx = fmaxf(mx, raw_max(masked_tag, 1, u));
+        const float m_blk = mx * p.scale_log2;
         const bool outgrown = m_blk > m_run + LAZY_TAU;
-        if (__any_sync(0xffffffffu, outgrown)) {  // rare; warp-uniform because tcgen05.ld/st are .sync.aligned
+        if (!__any_sync(0xffffffffu, outgrown)) {
+          tc_fence_before();
+          mbar_arrive(my_s_free);  // S_j is in registers: S_{j+1} may overwrite it
+          rsum += exp_store(masked_tag, 1, u, m_run);
+        } else {  // rare; warp-uniform because tcgen05.ld/st are .sync.aligned
           float alpha = 1.0f;
           if (outgrown) {  // this row moves its reference to the exact max; the other rows just repeat
             alpha = ex2_approx(m_run - m_blk);
             m_run = m_blk;
           }
-          rsum = exp_pass(masked_tag, m_run, m_blk);
+          rsum = exp_store(masked_tag, 1, u, m_run);
+          tmem_ld32(s_addr, u);  // first half again, against the new reference
+          tmem_ld_wait();
+          tc_fence_before();
+          mbar_arrive(my_s_free);
+          rsum += exp_store(masked_tag, 0, u, m_run);
           l_run *= alpha;
           // O *= alpha once PV_{j-1} (the latest PV issued) has landed
-          mbar_wait(my_pv_done, (j - 1) & 1);
+          if (j > 0) mbar_wait(my_pv_done, (j - 1) & 1);
           tc_fence_after();
 #pragma unroll 1
           for (int c = 0; c < p.n_pv / 16; ++c) {
-            uint32_t u[16];
-            tmem_ld16(o_addr + c * 16, u);
+            uint32_t o[16];
+            tmem_ld16(o_addr + c * 16, o);
             tmem_ld_wait();
 #pragma unroll
-            for (int i = 0; i < 16; ++i) u[i] = __float_as_uint(__uint_as_float(u[i]) * alpha);
-            tmem_st16(o_addr + c * 16, u);
+            for (int i = 0; i < 16; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+            tmem_st16(o_addr + c * 16, o);
           }
           tmem_st_wait();
         }
         l_run += rsum;
       };
-#ifdef B200SD_ATT_NOSOFTMAX  // diagnostic build only
-      if (j > 0) l_run = 1.f; else
-#endif
       if (valid == KB) block_body(std::false_type{});
       else block_body(std::true_type{});
       if (q == 2 && lane == 0) ATT_TR(2 + t, 2);
