@@ -39,7 +39,7 @@ extern "C" {
 #define B200SD_API
 #endif
 
-#define B200SD_ABI_VERSION 1
+#define B200SD_ABI_VERSION 2
 #define B200SD_MAX_SEG 3
 #define B200SD_MAX_TAPS 9
 
@@ -64,7 +64,9 @@ typedef enum b200sd_op_kind {
   B200SD_OP_CFG_STEP = 10,     /* eps = u + s(c-u); scheduler update (Euler / DDIM / DPM++2M) (:484-489)   */
   B200SD_OP_AXPBY = 11,        /* out = a*x + b*y  (add_noise, scale_model_input, latent un-scale)         */
   B200SD_OP_IMAGE_OUT = 12,    /* NHWC bf16 -> NCHW image tensor                                          */
-  B200SD_OP_STEP_ADVANCE = 13  /* ++(*step_counter)                                                       */
+  B200SD_OP_STEP_ADVANCE = 13, /* ++(*step_counter)                                                       */
+  B200SD_OP_IMAGE_U8 = 14,     /* NCHW image in [-1,1] -> uint8 HWC (runpod-worker/handler_logic.py:21-29) */
+  B200SD_OP_EMBED = 15         /* token + position embedding lookup of the CLIP text encoders             */
 } b200sd_op_kind;
 
 /* element types of host-visible tensors (latents, images) */
@@ -78,7 +80,9 @@ enum {
   B200SD_GEMM_RESIDUAL = 1 << 3,  /* += residual[m][n] (bf16)                                             */
   B200SD_GEMM_SILU = 1 << 4,      /* v = silu(v) after bias                                               */
   B200SD_GEMM_GEGLU = 1 << 5,     /* out[m][j] = h*gelu(g); weight rows pre-interleaved per N tile        */
-  B200SD_GEMM_OUT_F32 = 1 << 6    /* store fp32 instead of bf16                                           */
+  B200SD_GEMM_OUT_F32 = 1 << 6,   /* store fp32 instead of bf16                                           */
+  B200SD_GEMM_QUICK_GELU = 1 << 7, /* v = v * sigmoid(1.702 v) after bias (CLIP-L MLP)                     */
+  B200SD_GEMM_GELU = 1 << 8       /* v = gelu(v) (erf form) after bias (OpenCLIP bigG MLP)                 */
 };
 
 /* One K segment of an implicit GEMM.  The A operand of the whole GEMM is the K-concatenation of the
@@ -159,6 +163,8 @@ typedef struct b200sd_attention {
   int64_t ldq, ldk, ldv, ldo;
   int32_t B, heads, Nq, Nkv, d;
   float scale;   /* softmax(scale * q k^T)                                                                */
+  int32_t causal; /* 1: key j is visible to query i only when j <= i (CLIP text encoders)                  */
+  int32_t pad_;
 } b200sd_attention;
 
 /* ---- small bandwidth ops --------------------------------------------------------------------------- */
@@ -250,6 +256,26 @@ typedef struct b200sd_image_out {
   int32_t B, C, HW, out_dtype;
 } b200sd_image_out;
 
+/* The serving output stage, `convert_pt_to_numpy` (runpod-worker/handler_logic.py:21-29), as one kernel:
+ *   out[b, pix, c] = uint8( clamp(x[b, c, pix] / 2 + 0.5, 0, 1) * 255 )      (truncation, like Tensor.to(torch.uint8))
+ * Every intermediate is rounded to the element type of x, as torch's eager elementwise ops do, so the bytes are the
+ * reference's bytes for the same image tensor. */
+typedef struct b200sd_image_u8 {
+  const void* x; /* [B, C, HW] dtype x_dtype */
+  uint8_t* out;  /* [B, HW, C] */
+  int32_t B, C, HW, x_dtype;
+} b200sd_image_u8;
+
+/* CLIPTextEmbeddings: out[r] = token_embedding[ids[r]] + position_embedding[r % L]  (pipeline :587-589 calls the
+ * encoder; the module is transformers' CLIPTextEmbeddings). */
+typedef struct b200sd_embed {
+  const int32_t* ids; /* [rows] token ids, 0 <= id < vocab (checked on the device: an id out of range traps)   */
+  const void* tok;    /* bf16 [vocab, D]                                                                      */
+  const void* pos;    /* bf16 [L, D]                                                                          */
+  void* out;          /* bf16 [rows, D]                                                                       */
+  int32_t rows, L, D, vocab;
+} b200sd_embed;
+
 typedef struct b200sd_step_advance {
   int32_t* step_counter;
 } b200sd_step_advance;
@@ -271,6 +297,8 @@ typedef struct b200sd_op {
     b200sd_axpby axpby;
     b200sd_image_out image_out;
     b200sd_step_advance step_advance;
+    b200sd_image_u8 image_u8;
+    b200sd_embed embed;
   } u;
 } b200sd_op;
 

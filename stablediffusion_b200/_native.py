@@ -22,15 +22,18 @@ STEP_ROW = 16
 # enum b200sd_op_kind
 OP_GEMM, OP_GROUPNORM, OP_LAYERNORM, OP_ATTENTION, OP_TIMESTEP_EMBED, OP_PREP_LATENTS = 1, 2, 3, 4, 5, 6
 OP_UPSAMPLE2X, OP_PHASE_SPLIT, OP_SOFTMAX_ROWS, OP_CFG_STEP, OP_AXPBY, OP_IMAGE_OUT, OP_STEP_ADVANCE = 7, 8, 9, 10, 11, 12, 13
+OP_IMAGE_U8, OP_EMBED = 14, 15
+ABI_VERSION = 2  # include/b200sd.h B200SD_ABI_VERSION
 OP_NAMES = {
     1: "gemm", 2: "groupnorm", 3: "layernorm", 4: "attention", 5: "timestep_embed", 6: "prep_latents",
     7: "upsample2x", 8: "phase_split", 9: "softmax_rows", 10: "cfg_step", 11: "axpby", 12: "image_out",
-    13: "step_advance",
+    13: "step_advance", 14: "image_u8", 15: "embed",
 }
 # enum b200sd_dtype
 BF16, F32, F16 = 0, 1, 2
 # gemm flags
 GEMM_BIAS, GEMM_BIAS_ROW, GEMM_ROWVEC, GEMM_RESIDUAL, GEMM_SILU, GEMM_GEGLU, GEMM_OUT_F32 = 1, 2, 4, 8, 16, 32, 64
+GEMM_QUICK_GELU, GEMM_GELU = 128, 256
 # step-table columns
 ST_TIMESTEP, ST_IN_SCALE, ST_K1, ST_K2, ST_CX, ST_CE, ST_C0, ST_C1, ST_GUIDANCE = range(9)
 
@@ -81,7 +84,7 @@ class Attention(C.Structure):
         ("q", C.c_void_p), ("k", C.c_void_p), ("v", C.c_void_p), ("out", C.c_void_p),
         ("ldq", C.c_int64), ("ldk", C.c_int64), ("ldv", C.c_int64), ("ldo", C.c_int64),
         ("B", C.c_int32), ("heads", C.c_int32), ("Nq", C.c_int32), ("Nkv", C.c_int32), ("d", C.c_int32),
-        ("scale", C.c_float),
+        ("scale", C.c_float), ("causal", C.c_int32), ("pad_", C.c_int32),
     ]
 
 
@@ -143,12 +146,21 @@ class StepAdvance(C.Structure):
     _fields_ = [("step_counter", C.c_void_p)]
 
 
+class ImageU8(C.Structure):
+    _fields_ = [("x", C.c_void_p), ("out", C.c_void_p), ("B", C.c_int32), ("C", C.c_int32), ("HW", C.c_int32), ("x_dtype", C.c_int32)]
+
+
+class Embed(C.Structure):
+    _fields_ = [("ids", C.c_void_p), ("tok", C.c_void_p), ("pos", C.c_void_p), ("out", C.c_void_p),
+                ("rows", C.c_int32), ("L", C.c_int32), ("D", C.c_int32), ("vocab", C.c_int32)]
+
+
 class _OpUnion(C.Union):
     _fields_ = [
         ("gemm", Gemm), ("groupnorm", GroupNorm), ("layernorm", LayerNorm), ("attention", Attention),
         ("timestep_embed", TimestepEmbed), ("prep_latents", PrepLatents), ("upsample2x", Upsample2x),
         ("phase_split", PhaseSplit), ("softmax_rows", SoftmaxRows), ("cfg_step", CfgStep), ("axpby", Axpby),
-        ("image_out", ImageOut), ("step_advance", StepAdvance),
+        ("image_out", ImageOut), ("step_advance", StepAdvance), ("image_u8", ImageU8), ("embed", Embed),
     ]
 
 
@@ -160,13 +172,13 @@ STRUCT_OF_KIND = {
     OP_GEMM: Gemm, OP_GROUPNORM: GroupNorm, OP_LAYERNORM: LayerNorm, OP_ATTENTION: Attention,
     OP_TIMESTEP_EMBED: TimestepEmbed, OP_PREP_LATENTS: PrepLatents, OP_UPSAMPLE2X: Upsample2x,
     OP_PHASE_SPLIT: PhaseSplit, OP_SOFTMAX_ROWS: SoftmaxRows, OP_CFG_STEP: CfgStep, OP_AXPBY: Axpby,
-    OP_IMAGE_OUT: ImageOut, OP_STEP_ADVANCE: StepAdvance, 100: GemmSeg,
+    OP_IMAGE_OUT: ImageOut, OP_STEP_ADVANCE: StepAdvance, OP_IMAGE_U8: ImageU8, OP_EMBED: Embed, 100: GemmSeg,
 }
 FIELD_OF_KIND = {
     OP_GEMM: "gemm", OP_GROUPNORM: "groupnorm", OP_LAYERNORM: "layernorm", OP_ATTENTION: "attention",
     OP_TIMESTEP_EMBED: "timestep_embed", OP_PREP_LATENTS: "prep_latents", OP_UPSAMPLE2X: "upsample2x",
     OP_PHASE_SPLIT: "phase_split", OP_SOFTMAX_ROWS: "softmax_rows", OP_CFG_STEP: "cfg_step", OP_AXPBY: "axpby",
-    OP_IMAGE_OUT: "image_out", OP_STEP_ADVANCE: "step_advance",
+    OP_IMAGE_OUT: "image_out", OP_STEP_ADVANCE: "step_advance", OP_IMAGE_U8: "image_u8", OP_EMBED: "embed",
 }
 
 ENTRY_POINTS = {
@@ -224,7 +236,7 @@ def lib() -> C.CDLL:
                 fn = getattr(l, name)
                 fn.restype = res
                 fn.argtypes = args
-            if l.b200sd_abi_version() != 1:
+            if l.b200sd_abi_version() != ABI_VERSION:
                 raise RuntimeError("libb200sd ABI version mismatch")
             if l.b200sd_sizeof_op() != C.sizeof(Op):
                 raise RuntimeError(f"b200sd_op layout mismatch: C {l.b200sd_sizeof_op()} vs ctypes {C.sizeof(Op)}")

@@ -62,6 +62,7 @@ struct alignas(64) AttnParams {
   int n_pv;        // round16(d): UMMA N of the PV product
   int ksteps_qk;   // ceil(d/16)
   float scale_log2;
+  int causal;      // key j visible to query i only when j <= i
 };
 
 // NQ = query tiles (softmax warpgroups) per CTA.  The wide configurations (4 tiles at d <= 64, 2 above) own an SM;
@@ -304,6 +305,8 @@ attention_kernel(const __grid_constant__ AttnParams p) {
     constexpr float LAZY_TAU = 8.0f;
     for (int j = 0; j < nblk; ++j) {
       const int valid = min(KB, p.Nkv - j * KB);  // keys of this block that exist
+      // keys of this block this row may see (causal: those up to its own position; <= 0 when the block is all future)
+      const int lim = p.causal ? min(valid, q0 + t * BLK + r + 1 - j * KB) : valid;
       mbar_wait(my_s_full, j & 1);
       tc_fence_after();
       bool p_busy = j > 0;  // PV_{j-1} may still be reading P when S_j lands
@@ -314,7 +317,7 @@ attention_kernel(const __grid_constant__ AttnParams p) {
         float mx = -INFINITY;
 #pragma unroll
         for (int i = 0; i < 32; ++i)
-          if (!MASKED || c * 32 + i < valid) mx = fmaxf(mx, __uint_as_float(u[i]));
+          if (!MASKED || c * 32 + i < lim) mx = fmaxf(mx, __uint_as_float(u[i]));
         return mx;
       };
       // chunk c: probabilities relative to m_ref -> bf16 -> swizzled smem (K-major, 128-byte rows, 16-byte piece ^=
@@ -328,8 +331,8 @@ attention_kernel(const __grid_constant__ AttnParams p) {
           float p0 = ex2_approx(fmaf(__uint_as_float(u[2 * i]), p.scale_log2, -m_ref));
           float p1 = ex2_approx(fmaf(__uint_as_float(u[2 * i + 1]), p.scale_log2, -m_ref));
           if (MASKED) {
-            if (c * 32 + 2 * i >= valid) p0 = 0.f;
-            if (c * 32 + 2 * i + 1 >= valid) p1 = 0.f;
+            if (c * 32 + 2 * i >= lim) p0 = 0.f;
+            if (c * 32 + 2 * i + 1 >= lim) p1 = 0.f;
           }
           rsum += p0 + p1;
           pk[i] = pack_bf16x2(p0, p1);
@@ -398,7 +401,7 @@ attention_kernel(const __grid_constant__ AttnParams p) {
         }
         l_run += rsum;
       };
-      if (valid == KB) block_body(std::false_type{});
+      if (valid == KB && !p.causal) block_body(std::false_type{});
       else block_body(std::true_type{});
       if (q == 2 && lane == 0) ATT_TR(2 + t, 2);
       fence_proxy_async_smem();  // P (generic-proxy stores) -> visible to the MMA's async-proxy reads
@@ -503,6 +506,7 @@ int choose_tiles(int dpad, int B, int heads, int Nq, int kv_blocks) {
 int plan_attention(const b200sd_attention& a, PlannedOp* out) {
   B200SD_CHECK_ARG(a.q && a.k && a.v && a.out, "attention: NULL pointer");
   B200SD_CHECK_ARG(a.B >= 1 && a.heads >= 1 && a.Nq >= 1 && a.Nkv >= 1, "attention: bad shape");
+  B200SD_CHECK_ARG(!a.causal || a.Nq == a.Nkv, "attention: the causal mask needs Nq == Nkv");
   B200SD_CHECK_ARG(a.d >= 8 && a.d % 8 == 0 && a.d <= 192, "attention: head dim %d unsupported (multiple of 8, <= 192)", a.d);
   B200SD_CHECK_ARG(a.ldq % 8 == 0 && a.ldk % 8 == 0 && a.ldv % 8 == 0 && a.ldo % 8 == 0, "attention: pitches must be multiples of 8");
   B200SD_CHECK_ARG(a.ldq >= a.heads * a.d && a.ldk >= a.heads * a.d && a.ldv >= a.heads * a.d && a.ldo >= a.heads * a.d,
@@ -530,6 +534,7 @@ int plan_attention(const b200sd_attention& a, PlannedOp* out) {
   kp.n_pv = (a.d + 15) / 16 * 16;
   kp.ksteps_qk = (a.d + 15) / 16;
   kp.scale_log2 = a.scale * 1.4426950408889634f;
+  kp.causal = a.causal ? 1 : 0;
   pl->dpad = (a.d + 63) / 64 * 64;
   pl->nq = choose_tiles(pl->dpad, a.B, a.heads, a.Nq, kp.kv_blocks);
   const int rows_per_cta = BLK * pl->nq;

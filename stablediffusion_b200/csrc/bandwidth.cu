@@ -600,6 +600,85 @@ int launch_image_out(const void* plan, cudaStream_t s) {
   return 0;
 }
 
+// ======================================================================================================
+// Output stage: image tensor in [-1, 1] (NCHW) -> uint8 HWC, `convert_pt_to_numpy` of the serving handler
+// (runpod-worker/handler_logic.py:21-29): (img / 2 + 0.5).clamp(0, 1), permute, * 255, .to(torch.uint8).
+// Each intermediate is rounded to the tensor's element type, as torch's eager ops do, so the bytes are identical.
+// Algorithmic bytes per pixel: C elements read + C bytes written.
+// ======================================================================================================
+struct U8Params { const void* x; uint8_t* out; int B, C, HW, xd; };
+template <int XD>
+__device__ __forceinline__ float round_like(float v) {
+  if (XD == B200SD_BF16) return __bfloat162float(__float2bfloat16_rn(v));
+  if (XD == B200SD_F16) return __half2float(__float2half_rn(v));
+  return v;
+}
+template <int XD>
+__global__ void image_u8_kernel(const U8Params p) {
+  pdl_launch_dependents();
+  pdl_wait();
+  const long long total = static_cast<long long>(p.B) * p.HW;
+  for (long long idx = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; idx < total;
+       idx += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const long long b = idx / p.HW, pix = idx - b * p.HW;
+    for (int c = 0; c < p.C; ++c) {  // consecutive threads read consecutive pixels of one plane: coalesced
+      float v = load_as_float(p.x, (b * p.C + c) * p.HW + pix, XD);
+      v = round_like<XD>(v * 0.5f);        // img / 2
+      v = round_like<XD>(v + 0.5f);        // + 0.5
+      v = fminf(fmaxf(v, 0.f), 1.f);       // clamp(0, 1)   (NaN -> 0 on both sides is not needed: VAE output is finite)
+      v = round_like<XD>(v * 255.f);       // * 255
+      p.out[idx * p.C + c] = static_cast<uint8_t>(static_cast<int>(v));  // truncation
+    }
+  }
+}
+int launch_image_u8(const void* plan, cudaStream_t s) {
+  const U8Params& p = *static_cast<const U8Params*>(plan);
+  const long long total = static_cast<long long>(p.B) * p.HW;
+  const int blocks = static_cast<int>(std::min<long long>((total + 255) / 256, 148 * 8));
+  switch (p.xd) {
+    case B200SD_BF16: B200SD_CUDA(launch_kernel(image_u8_kernel<B200SD_BF16>, dim3(blocks), dim3(256), 0, s, 1, p)); break;
+    case B200SD_F16: B200SD_CUDA(launch_kernel(image_u8_kernel<B200SD_F16>, dim3(blocks), dim3(256), 0, s, 1, p)); break;
+    default: B200SD_CUDA(launch_kernel(image_u8_kernel<B200SD_F32>, dim3(blocks), dim3(256), 0, s, 1, p)); break;
+  }
+  B200SD_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// ======================================================================================================
+// CLIP text embeddings: token row + position row (transformers CLIPTextEmbeddings), 8 channels per thread.
+// ======================================================================================================
+struct EmbParams { const int* ids; const bf16* tok; const bf16* pos; bf16* out; int rows, L, D, vocab; };
+__global__ void embed_kernel(const EmbParams p) {
+  pdl_launch_dependents();
+  pdl_wait();
+  const int vecs = p.D >> 3;
+  const long long total = static_cast<long long>(p.rows) * vecs;
+  for (long long idx = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; idx < total;
+       idx += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int row = static_cast<int>(idx / vecs), v = static_cast<int>(idx - static_cast<long long>(row) * vecs);
+    const int id = __ldg(p.ids + row);
+    if (id < 0 || id >= p.vocab) __trap();  // a bad token id must not read outside the table
+    const uint4 a = __ldg(reinterpret_cast<const uint4*>(p.tok + static_cast<long long>(id) * p.D) + v);
+    const uint4 b = __ldg(reinterpret_cast<const uint4*>(p.pos + static_cast<long long>(row % p.L) * p.D) + v);
+    const uint32_t aw[4] = {a.x, a.y, a.z, a.w}, bw[4] = {b.x, b.y, b.z, b.w};
+    uint32_t o[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float2 fa = unpack_bf16x2(aw[j]), fb = unpack_bf16x2(bw[j]);
+      o[j] = pack_bf16x2(fa.x + fb.x, fa.y + fb.y);
+    }
+    *(reinterpret_cast<uint4*>(p.out + static_cast<long long>(row) * p.D) + v) = make_uint4(o[0], o[1], o[2], o[3]);
+  }
+}
+int launch_embed(const void* plan, cudaStream_t s) {
+  const EmbParams& p = *static_cast<const EmbParams*>(plan);
+  const long long total = static_cast<long long>(p.rows) * (p.D >> 3);
+  const int blocks = static_cast<int>(std::min<long long>((total + 255) / 256, 148 * 8));
+  B200SD_CUDA(launch_kernel(embed_kernel, dim3(blocks), dim3(256), 0, s, 1, p));
+  B200SD_CUDA(cudaGetLastError());
+  return 0;
+}
+
 __global__ void step_advance_kernel(int* counter) {
   pdl_launch_dependents();
   pdl_wait();
@@ -734,6 +813,21 @@ int plan_image_out(const b200sd_image_out& g, PlannedOp* out) {
   B200SD_CHECK_ARG(g.x && g.out && g.B >= 1 && g.C >= 1 && g.HW >= 1 && g.ldx >= g.C && dtype_ok(g.out_dtype), "image_out: bad arguments");
   IOParams p{static_cast<const bf16*>(g.x), g.out, g.ldx, g.B, g.C, g.HW, g.out_dtype};
   return finish_plan(out, B200SD_OP_IMAGE_OUT, p, launch_image_out);
+}
+
+int plan_image_u8(const b200sd_image_u8& g, PlannedOp* out) {
+  B200SD_CHECK_ARG(g.x && g.out, "image_u8: NULL pointer");
+  B200SD_CHECK_ARG(g.B >= 1 && g.C >= 1 && g.HW >= 1 && dtype_ok(g.x_dtype), "image_u8: bad shape or dtype");
+  U8Params p{g.x, g.out, g.B, g.C, g.HW, g.x_dtype};
+  return finish_plan(out, B200SD_OP_IMAGE_U8, p, launch_image_u8);
+}
+
+int plan_embed(const b200sd_embed& g, PlannedOp* out) {
+  B200SD_CHECK_ARG(g.ids && g.tok && g.pos && g.out, "embed: NULL pointer");
+  B200SD_CHECK_ARG(g.rows >= 1 && g.L >= 1 && g.vocab >= 1 && g.D >= 8 && g.D % 8 == 0, "embed: bad shape (D must be a multiple of 8)");
+  B200SD_CHECK_ARG(aligned16(g.tok) && aligned16(g.pos) && aligned16(g.out), "embed: tables and output must be 16-byte aligned");
+  EmbParams p{g.ids, static_cast<const bf16*>(g.tok), static_cast<const bf16*>(g.pos), static_cast<bf16*>(g.out), g.rows, g.L, g.D, g.vocab};
+  return finish_plan(out, B200SD_OP_EMBED, p, launch_embed);
 }
 
 int plan_step_advance(const b200sd_step_advance& g, PlannedOp* out) {

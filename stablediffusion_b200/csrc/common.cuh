@@ -53,6 +53,8 @@ __device__ __forceinline__ float silu_f(float x) { return __fdividef(x, 1.0f + _
 //   Phi(-|x|) = 0.5 * erfc(|x|/sqrt2) = 0.5 * t*(a1 + t*(a2 + t*(a3 + t*(a4 + t*a5)))) * exp(-x^2/2),  t = 1/(1 + p|x|/sqrt2)
 // (Abramowitz & Stegun 7.1.26, |erf error| <= 1.5e-7): 2 MUFU + ~14 FMA-pipe instructions instead of libdevice erff's ~35.
 // Measured against float64: max |error| 4.2e-7 over [-12, 12], i.e. far below one bf16 ulp of any output that matters.
+// CLIP's "quick_gelu": x * sigmoid(1.702 x)
+__device__ __forceinline__ float quick_gelu_f(float x) { return __fdividef(x, 1.0f + __expf(-1.702f * x)); }
 __device__ __forceinline__ float gelu_erf_f(float x) {
   const float ax = fabsf(x);
   float t;

@@ -205,6 +205,14 @@ __device__ __forceinline__ void epilogue_store16(const GemmKParams& p, const Row
 #pragma unroll
     for (int j = 0; j < 16; ++j) v[j] = silu_f(v[j]);
   }
+  if (flags & B200SD_GEMM_QUICK_GELU) {
+#pragma unroll
+    for (int j = 0; j < 16; ++j) v[j] = quick_gelu_f(v[j]);
+  }
+  if (flags & B200SD_GEMM_GELU) {
+#pragma unroll
+    for (int j = 0; j < 16; ++j) v[j] = gelu_erf_f(v[j]);
+  }
   const bool vec_ok = full && ((p.ldc & 7) == 0);
   if (flags & B200SD_GEMM_RESIDUAL) {
     const bf16* rp = p.residual + ri.res_off + n;
@@ -270,6 +278,14 @@ __device__ __forceinline__ void epilogue_extra32(const GemmKParams& p, const Row
   if (flags & B200SD_GEMM_SILU) {
 #pragma unroll
     for (int j = 0; j < 32; ++j) v[j] = silu_f(v[j]);
+  }
+  if (flags & B200SD_GEMM_QUICK_GELU) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) v[j] = quick_gelu_f(v[j]);
+  }
+  if (flags & B200SD_GEMM_GELU) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) v[j] = gelu_erf_f(v[j]);
   }
 }
 
@@ -518,7 +534,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
       const bool geglu = (p.flags & B200SD_GEMM_GEGLU) != 0;
       const bool has_res = (p.flags & B200SD_GEMM_RESIDUAL) != 0;
       const bool has_bias = (p.flags & B200SD_GEMM_BIAS) != 0;
-      const bool extra = (p.flags & (B200SD_GEMM_BIAS_ROW | B200SD_GEMM_ROWVEC | B200SD_GEMM_SILU)) != 0;
+      const bool extra = (p.flags & (B200SD_GEMM_BIAS_ROW | B200SD_GEMM_ROWVEC | B200SD_GEMM_SILU | B200SD_GEMM_QUICK_GELU | B200SD_GEMM_GELU)) != 0;
       const int bn_out = geglu ? BN / 2 : BN;
       const int nsub = bn_out / 32;
       const int sw = (r >> 1) & 3;  // SWIZZLE_64B: 16-byte chunk index ^= (row / 2) % 4
@@ -974,7 +990,7 @@ int plan_gemm(const b200sd_gemm& g, PlannedOp* out) {
   if ((g.flags & (B200SD_GEMM_BIAS | B200SD_GEMM_BIAS_ROW)) && !g.bias) { delete pl; return fail(B200SD_ERR_INVALID, "gemm: bias flag without bias pointer"); }
   if ((g.flags & B200SD_GEMM_ROWVEC) && !g.rowvec) { delete pl; return fail(B200SD_ERR_INVALID, "gemm: rowvec flag without pointer"); }
   if ((g.flags & B200SD_GEMM_RESIDUAL) && !g.residual) { delete pl; return fail(B200SD_ERR_INVALID, "gemm: residual flag without pointer"); }
-  if ((g.flags & B200SD_GEMM_GEGLU) && (g.flags & (B200SD_GEMM_RESIDUAL | B200SD_GEMM_ROWVEC | B200SD_GEMM_SILU | B200SD_GEMM_OUT_F32 | B200SD_GEMM_BIAS_ROW))) {
+  if ((g.flags & B200SD_GEMM_GEGLU) && (g.flags & (B200SD_GEMM_RESIDUAL | B200SD_GEMM_ROWVEC | B200SD_GEMM_SILU | B200SD_GEMM_QUICK_GELU | B200SD_GEMM_GELU | B200SD_GEMM_OUT_F32 | B200SD_GEMM_BIAS_ROW))) {
     delete pl; return fail(B200SD_ERR_INVALID, "gemm: GEGLU epilogue only combines with BIAS");
   }
   if ((g.flags & B200SD_GEMM_GEGLU) && (g.ldc % 8 != 0)) { delete pl; return fail(B200SD_ERR_INVALID, "gemm: GEGLU needs ldc %% 8 == 0"); }

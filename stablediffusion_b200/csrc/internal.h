@@ -60,6 +60,8 @@ int plan_cfg_step(const b200sd_cfg_step& g, PlannedOp* out);
 int plan_axpby(const b200sd_axpby& g, PlannedOp* out);
 int plan_image_out(const b200sd_image_out& g, PlannedOp* out);
 int plan_step_advance(const b200sd_step_advance& g, PlannedOp* out);
+int plan_image_u8(const b200sd_image_u8& g, PlannedOp* out);
+int plan_embed(const b200sd_embed& g, PlannedOp* out);
 
 // host-only helpers used by sizing entry points
 struct GemmTiling {

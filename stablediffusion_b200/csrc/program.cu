@@ -139,6 +139,8 @@ size_t b200sd_sizeof_struct(int32_t kind) {
     case B200SD_OP_AXPBY: return sizeof(b200sd_axpby);
     case B200SD_OP_IMAGE_OUT: return sizeof(b200sd_image_out);
     case B200SD_OP_STEP_ADVANCE: return sizeof(b200sd_step_advance);
+    case B200SD_OP_IMAGE_U8: return sizeof(b200sd_image_u8);
+    case B200SD_OP_EMBED: return sizeof(b200sd_embed);
     case 100: return sizeof(b200sd_gemm_seg);
   }
   return 0;
@@ -201,6 +203,8 @@ int b200sd_program_add(b200sd_program* p, const b200sd_op* op) {
     case B200SD_OP_AXPBY: rc = plan_axpby(op->u.axpby, &po); break;
     case B200SD_OP_IMAGE_OUT: rc = plan_image_out(op->u.image_out, &po); break;
     case B200SD_OP_STEP_ADVANCE: rc = plan_step_advance(op->u.step_advance, &po); break;
+    case B200SD_OP_IMAGE_U8: rc = plan_image_u8(op->u.image_u8, &po); break;
+    case B200SD_OP_EMBED: rc = plan_embed(op->u.embed, &po); break;
     default: return fail(B200SD_ERR_INVALID, "unknown op kind %d", op->kind);
   }
   if (rc) return rc;

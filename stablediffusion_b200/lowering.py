@@ -92,7 +92,7 @@ class Builder:
         self.meta[idx] = self._pending_meta
 
     @staticmethod
-    def _epilogue(g: N.Gemm, bias, rowvec, residual, ldr, silu, geglu, out_f32, bias_row, alpha, rows_per_group):
+    def _epilogue(g: N.Gemm, bias, rowvec, residual, ldr, silu, geglu, out_f32, bias_row, alpha, rows_per_group, act=None):
         flags = 0
         if bias is not None:
             if bias.dtype != torch.float32:
@@ -116,11 +116,15 @@ class Builder:
             flags |= N.GEMM_GEGLU
         if out_f32:
             flags |= N.GEMM_OUT_F32
+        if act is not None:
+            if act not in ("quick_gelu", "gelu"):
+                raise ValueError(f"unknown activation '{act}'")
+            flags |= N.GEMM_QUICK_GELU if act == "quick_gelu" else N.GEMM_GELU
         g.flags = flags
         g.alpha = alpha
 
     def linear(self, a, w, out=None, bias=None, residual=None, rowvec=None, rows_per_group=0, silu=False, geglu=False,
-               out_f32=False, bias_row=False, alpha=1.0, a2=None, splits=0, block_n=0, cta_pair=0):
+               out_f32=False, bias_row=False, alpha=1.0, a2=None, splits=0, block_n=0, cta_pair=0, act=None):
         """out[M,N] = a[M,K] @ w[N,K]^T (+ epilogue).  `a2` appends a second K segment ([M,K2], weights w[:, K:])."""
         ap, M, K, lda = _rows_view(a)
         wp, Nn, Kw, ldw = _rows_view(w)
@@ -151,7 +155,7 @@ class Builder:
             _, rm, rn, ldr = _rows_view(residual)
             if rm != M or rn != n_out:
                 raise ValueError("linear: residual shape mismatch")
-        self._epilogue(g, bias, rowvec, residual, ldr, silu, geglu, out_f32, bias_row, alpha, rows_per_group)
+        self._epilogue(g, bias, rowvec, residual, ldr, silu, geglu, out_f32, bias_row, alpha, rows_per_group, act)
         self._pending_meta = dict(op='linear', M=M, N=Nn, K=K + K2, flops=2 * M * Nn * (K + K2), geglu=geglu)
         self._finish_gemm(g, (a, w, out, bias, residual, rowvec, a2))
         self.gemm_flops += 2 * M * Nn * (K + K2)
@@ -249,7 +253,7 @@ class Builder:
         return out
 
     # ---- attention ----------------------------------------------------------------------------------
-    def attention(self, q, k, v, heads, d, scale, out=None):
+    def attention(self, q, k, v, heads, d, scale, out=None, causal=False):
         """q [B,Nq,*], k/v [B,Nkv,*]: 3-D views, last dim contiguous, batch stride = rows*pitch."""
         B, Nq, _ = q.shape
         Nkv = k.shape[1]
@@ -262,6 +266,7 @@ class Builder:
         p.q, p.k, p.v, p.out = q.data_ptr(), k.data_ptr(), v.data_ptr(), out.data_ptr()
         p.ldq, p.ldk, p.ldv, p.ldo = q.stride(1), k.stride(1), v.stride(1), out.stride(1)
         p.B, p.heads, p.Nq, p.Nkv, p.d, p.scale = B, heads, Nq, Nkv, d, float(scale)
+        p.causal = 1 if causal else 0
         idx = self.prog.add(N.OP_ATTENTION, p, self.tag, (q, k, v, out))
         self.meta[idx] = dict(op='attention', B=B, heads=heads, Nq=Nq, Nkv=Nkv, d=d, flops=4 * B * heads * Nq * Nkv * d)
         self.attn_flops += 4 * B * heads * Nq * Nkv * d
@@ -348,6 +353,27 @@ class Builder:
         p = N.ImageOut()
         p.x, p.out, p.ldx, p.B, p.C, p.HW, p.out_dtype = x.data_ptr(), out.data_ptr(), ldx, B, C_valid, HW, dtype_code(out)
         self.prog.add(N.OP_IMAGE_OUT, p, self.tag, (x, out))
+        return out
+
+    def image_u8(self, x, out):
+        """x: [B, C, H*W] image in [-1, 1] (bf16 / fp16 / fp32) -> out: uint8 [B, H*W, C] (handler_logic.py:21-29)."""
+        B, Cc, HW = x.shape
+        p = N.ImageU8()
+        p.x, p.out, p.B, p.C, p.HW, p.x_dtype = x.data_ptr(), out.data_ptr(), B, Cc, HW, dtype_code(x)
+        self.prog.add(N.OP_IMAGE_U8, p, self.tag, (x, out))
+        return out
+
+    def embed(self, ids, tok, pos, out=None):
+        """ids: int32 [rows]; tok: bf16 [vocab, D]; pos: bf16 [L, D] -> bf16 [rows, D] = tok[ids] + pos[row % L]."""
+        if ids.dtype != torch.int32 or tok.dtype != torch.bfloat16 or pos.dtype != torch.bfloat16:
+            raise ValueError("embed: ids must be int32, tables bf16")
+        rows, (vocab, D), Lp = ids.numel(), tok.shape, pos.shape[0]
+        if out is None:
+            out = self.empty([rows, D])
+        p = N.Embed()
+        p.ids, p.tok, p.pos, p.out = ids.data_ptr(), tok.data_ptr(), pos.data_ptr(), out.data_ptr()
+        p.rows, p.L, p.D, p.vocab = rows, Lp, D, vocab
+        self.prog.add(N.OP_EMBED, p, self.tag, (ids, tok, pos, out))
         return out
 
     def step_advance(self, step_counter):

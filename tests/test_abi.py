@@ -38,7 +38,7 @@ def test_library_has_no_libcuda_link_dependency():
 
 def test_struct_layouts_match_header():
     lib = N.lib()
-    assert lib.b200sd_abi_version() == 1
+    assert lib.b200sd_abi_version() == N.ABI_VERSION == 2
     assert lib.b200sd_sizeof_op() == C.sizeof(N.Op)
     for kind, st in N.STRUCT_OF_KIND.items():
         assert lib.b200sd_sizeof_struct(kind) == C.sizeof(st), st.__name__
