@@ -6,7 +6,8 @@ Loading (reference :106-156 `load_hf_checkpoint`): an HF-layout folder — `unet
 (`diffusion_pytorch_model.fp16.safetensors`), i.e. exactly what scripts/convert_from_A1111.py:1381-1386 writes.
 Weights are converted to bf16 and re-laid-out for the kernels at load.  There is no network in this build:
 hub ids (`OnMoon/...`, `runwayml/...`) must already be local folders, otherwise loading raises.
-Text encoders / tokenizers stay torch + transformers objects: they are outside the hot path.
+Tokenizers stay transformers objects; the text encoders are read with transformers and become native
+`B200CLIPTextModel`s when the wrapper moves to the device.
 """
 from __future__ import annotations
 
@@ -17,6 +18,7 @@ import torch
 
 from ..config import UNET_DEFAULTS, VAE_DEFAULTS, Config, load_json_config, scheduler_config, unet_config, vae_config
 from ..lora import parse_lora_state_dict
+from ..clip import B200CLIPTextModel
 from ..random_init import random_state_dict
 from ..schedulers import B200EulerDiscreteScheduler, make_scheduler
 from ..unet import B200UNet, unet_param_shapes
@@ -64,6 +66,10 @@ class _ImageProcessor:
             arrs.append(np.asarray(im, dtype=np.float32) / 255.0)
         x = torch.from_numpy(np.stack(arrs)).permute(0, 3, 1, 2)
         return 2.0 * x - 1.0 if self.do_normalize else x
+
+
+def _is_hf_clip(enc) -> bool:
+    return type(enc).__name__ in ("CLIPTextModel", "CLIPTextModelWithProjection") and hasattr(enc, "state_dict")
 
 
 class SDModelWrapper:
@@ -140,10 +146,16 @@ class SDModelWrapper:
     def to(self, device):
         self.vae.to(device)
         self.base.to(device)
-        if self.text_encoder is not None:
-            self.text_encoder.to(device)
-        if getattr(self, "text_encoder_2", None) is not None:
-            self.text_encoder_2.to(device)
+        # text encoders: transformers modules become native B200 encoders the first time they reach the device
+        # (SURVEY §8(f) rank 2); the torch module stays on the host as the master copy LoRA is merged into
+        for name in ("text_encoder", "text_encoder_2"):
+            enc = getattr(self, name, None)
+            if enc is None:
+                continue
+            if torch.device(device).type == "cuda" and not isinstance(enc, B200CLIPTextModel) and _is_hf_clip(enc):
+                setattr(self, name, B200CLIPTextModel.from_transformers(enc, device=device))
+            else:
+                enc.to(device)
         self.device = torch.device(device)
 
     def set_scheduler(self, scheduler_name):
@@ -217,6 +229,8 @@ class SDModelWrapper:
                 for m, delta in st["layers"]:
                     m.weight.data += ((new_w - st["weight"]) * delta).to(m.weight.device, m.weight.dtype)
                 st["weight"] = new_w
+                if isinstance(enc, B200CLIPTextModel):
+                    enc.refresh_weights()
 
     def set_adapters(self, adapter_names: Union[List[str], str], adapter_weights: Optional[List[float]] = None):
         names = [adapter_names] if isinstance(adapter_names, str) else list(adapter_names)

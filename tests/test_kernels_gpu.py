@@ -445,3 +445,48 @@ def test_bad_arguments_raise_value_error(cuda_device):
     w = _bf(_randn((128, 100), dev, 2))
     with pytest.raises(ValueError):
         b.linear(a, w)
+
+
+# ---- CLIP text-encoder pieces -------------------------------------------------------
+
+@pytest.mark.parametrize("B,heads,Nn,d", [(3, 12, 77, 64), (2, 2, 77, 32), (2, 4, 300, 64), (1, 20, 77, 64), (1, 2, 640, 40)])
+def test_attention_causal(cuda_device, B, heads, Nn, d):
+    """Key j is visible to query i only when j <= i (transformers' causal mask of the CLIP text towers)."""
+    dev = cuda_device
+    C = heads * d
+    qkv = _bf(_randn((B, Nn, 3 * C), dev, 21))
+    b = _builder(dev)
+    out = b.attention(qkv[:, :, :C], qkv[:, :, C:2 * C], qkv[:, :, 2 * C:], heads, d, d ** -0.5, causal=True)
+    _run(b)
+    q, k, v = [t.float().reshape(B, Nn, heads, d).transpose(1, 2) for t in qkv.split(C, dim=-1)]
+    ref = F.scaled_dot_product_attention(q, k, v, is_causal=True).transpose(1, 2).reshape(B, Nn, C)
+    _check(out, ref, rtol=2 ** -6, name="causal attention")
+
+
+@pytest.mark.parametrize("act", ["quick_gelu", "gelu"])
+@pytest.mark.parametrize("M,N,K", [(231, 3072, 768), (308, 5120, 1280), (77, 128, 64)])
+def test_gemm_clip_activations(cuda_device, act, M, N, K):
+    dev = cuda_device
+    a = _bf(_randn((M, K), dev, 1))
+    w = _bf(_randn((N, K), dev, 2, 1.0 / math.sqrt(K)))
+    bias = _randn((N,), dev, 3)
+    b = _builder(dev)
+    out = b.linear(a, w, bias=bias, act=act)
+    _run(b)
+    z = a.float() @ w.float().t() + bias
+    ref = z * torch.sigmoid(1.702 * z) if act == "quick_gelu" else F.gelu(z)
+    _check(out, ref, name=f"gemm+{act}")
+
+
+def test_embed_bit_exact(cuda_device):
+    dev = cuda_device
+    g = torch.Generator().manual_seed(3)
+    vocab, Lseq, D, B = 1000, 77, 768, 5
+    tok = _bf(_randn((vocab, D), dev, 1))
+    pos = _bf(_randn((Lseq, D), dev, 2))
+    ids = torch.randint(0, vocab, (B * Lseq,), generator=g).to(torch.int32).to(dev)
+    b = _builder(dev)
+    out = b.embed(ids, tok, pos)
+    _run(b)
+    ref = (tok[ids.long()].float() + pos.float().repeat(B, 1)).to(torch.bfloat16)
+    assert torch.equal(out, ref)
