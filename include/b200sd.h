@@ -180,7 +180,17 @@ enum { /* columns of one step-table row */
   B200SD_ST_CE = 5,
   B200SD_ST_C0 = 6,
   B200SD_ST_C1 = 7,
-  B200SD_ST_GUIDANCE = 8     /* guidance scale (read when cfg_step.gs_from_table != 0)                     */
+  B200SD_ST_GUIDANCE = 8,    /* guidance scale (read when cfg_step.gs_from_table != 0)                     */
+  B200SD_ST_CN = 9,          /* x' += CN * noise[step]            (ancestral / SDE samplers)                      */
+  B200SD_ST_H1 = 10,         /* x' += H1*e[-1] + H2*e[-2] + H3*e[-3]   (linear multistep on eps: PNDM / PLMS)     */
+  B200SD_ST_H2 = 11,
+  B200SD_ST_H3 = 12,
+  B200SD_ST_FLAGS = 13       /* float image of B200SD_STF_* bits                                               */
+};
+enum {
+  B200SD_STF_PUSH_EPS = 1,   /* after the update: e[-3] <- e[-2] <- e[-1] <- eps                                */
+  B200SD_STF_SAVE_X = 2,     /* remember the sample the step started from (PNDM `cur_sample`)                   */
+  B200SD_STF_USE_SAVED_X = 4 /* update the remembered sample instead of the current one (PNDM counter == 1)     */
 };
 
 typedef struct b200sd_timestep_embed {
@@ -237,6 +247,9 @@ typedef struct b200sd_cfg_step {
   int32_t x_dtype, B, C, hw, Cpad, rep;
   int32_t nsteps;   /* rows in the table (next_in uses row step+1 if it exists)                            */
   int32_t gs_from_table; /* 1: take the guidance scale from the step table (column B200SD_ST_GUIDANCE)      */
+  const float* noise;    /* fp32 [nsteps_of_noise, B, C, hw]: row `step` is this step's standard-normal draw (NULL: CN ignored) */
+  float* eps_hist;       /* fp32 [3, B, C, hw] eps history for the H1..H3 terms (NULL if unused)            */
+  float* x_saved;        /* fp32 [B, C, hw] for B200SD_STF_SAVE_X / USE_SAVED_X (NULL if unused)             */
 } b200sd_cfg_step;
 
 typedef struct b200sd_axpby {

@@ -15,9 +15,11 @@ def cfg_combine(noise_pred: torch.Tensor, guidance_scale: float) -> torch.Tensor
 
 @torch.no_grad()
 def denoise(unet, scheduler, latents, prompt_embeds, timesteps, guidance_scale, do_cfg=True, added_cond_kwargs=None,
-            return_eps=False):
+            return_eps=False, step_noise=None):
+    """`step_noise[i]`: the standard-normal draw of step i for the ancestral / SDE samplers (the reference draws it
+    inside scheduler.step from the global RNG, pipeline :489; tests pass the draws the device used)."""
     eps_trace = []
-    for t in timesteps:
+    for i, t in enumerate(timesteps):
         x_in = torch.cat([latents] * 2) if do_cfg else latents
         x_in = scheduler.scale_model_input(x_in, t)
         noise_pred = unet(x_in, t, prompt_embeds, added_cond_kwargs=added_cond_kwargs)
@@ -25,7 +27,10 @@ def denoise(unet, scheduler, latents, prompt_embeds, timesteps, guidance_scale, 
             eps_trace.append(noise_pred.clone())
         if do_cfg:
             noise_pred = cfg_combine(noise_pred, guidance_scale)
-        latents = scheduler.step(noise_pred, t, latents)
+        if step_noise is not None:
+            latents = scheduler.step(noise_pred, t, latents, step_noise[i])
+        else:
+            latents = scheduler.step(noise_pred, t, latents)
     return (latents, eps_trace) if return_eps else latents
 
 

@@ -234,8 +234,137 @@ class DPMSolverMultistepOracle(_Base):
         return a * x0 + s * noise
 
 
+class EulerAncestralOracle(EulerDiscreteOracle):
+    """EulerAncestralDiscreteScheduler (`euler_a`, models/stable_diffusion.py:209-210).  The reference calls
+    `scheduler.step(noise_pred, t, latents)` without a generator (pipeline :489), i.e. the noise comes from the global
+    device RNG; the oracle takes the draw as an argument so that both sides can be fed the same one."""
+
+    def step(self, eps, t, x, noise):
+        self._init_step_index(t)
+        x = x.to(torch.float32)
+        sigma = self.sigmas[self.step_index]
+        x0 = x - sigma * eps
+        sigma_from, sigma_to = self.sigmas[self.step_index], self.sigmas[self.step_index + 1]
+        sigma_up = (sigma_to ** 2 * (sigma_from ** 2 - sigma_to ** 2) / sigma_from ** 2) ** 0.5
+        sigma_down = (sigma_to ** 2 - sigma_up ** 2) ** 0.5
+        d = (x - x0) / sigma
+        dt = sigma_down - sigma
+        self.step_index += 1
+        return x + d * dt + noise * sigma_up
+
+
+class DPMSolverSDEOracle(DPMSolverMultistepOracle):
+    """DPMSolverMultistepScheduler with algorithm_type="sde-dpmsolver++" (`DPM++ 2M SDE Karras`,
+    models/stable_diffusion.py:215-218 — the reference spells the Karras switch `se_karras_sigmas`, which
+    `from_config` drops, so the sigmas are NOT Karras-spaced; reproduced as is)."""
+
+    def step(self, eps, t, x, noise):
+        self._init_step_index(t)
+        i = self.step_index
+        n = len(self.timesteps)
+        lower_final = i == n - 1
+        a_s, s_s = self._alpha_sigma(self.sigmas[i])
+        x0 = (x - s_s * eps) / a_s
+        self.m = [self.m[1], x0]
+        x = x.to(torch.float32)
+        a_t, s_t = self._alpha_sigma(self.sigmas[i + 1])
+        lam_t = torch.log(a_t) - torch.log(s_t)
+        lam_s = torch.log(a_s) - torch.log(s_s)
+        h = lam_t - lam_s
+        if self.lower_order_nums < 1 or lower_final:
+            out = (s_t / s_s * torch.exp(-h)) * x + (a_t * (1 - torch.exp(-2.0 * h))) * x0 \
+                + s_t * torch.sqrt(1.0 - torch.exp(-2.0 * h)) * noise
+        else:
+            a_s1, s_s1 = self._alpha_sigma(self.sigmas[i - 1])
+            lam_s1 = torch.log(a_s1) - torch.log(s_s1)
+            r0 = (lam_s - lam_s1) / h
+            D0, D1 = self.m[1], (1.0 / r0) * (self.m[1] - self.m[0])
+            out = (s_t / s_s * torch.exp(-h)) * x + (a_t * (1 - torch.exp(-2.0 * h))) * D0 \
+                + 0.5 * (a_t * (1 - torch.exp(-2.0 * h))) * D1 + s_t * torch.sqrt(1.0 - torch.exp(-2.0 * h)) * noise
+        if self.lower_order_nums < 2:
+            self.lower_order_nums += 1
+        self.step_index += 1
+        return out
+
+
+class PNDMOracle(_Base):
+    """PNDMScheduler (`PNDM`, models/stable_diffusion.py:219-220) with skip_prk_steps=True (every SD checkpoint:
+    scripts/convert_from_A1111.py:947-982) — i.e. PLMS: N + 1 UNet evaluations, the second timestep visited twice."""
+    init_noise_sigma = 1.0
+
+    def __init__(self, **config):
+        super().__init__(**config)
+        if not self.config.get("skip_prk_steps", False):
+            raise ValueError("PNDM with Runge-Kutta warm-up steps is not used by SD checkpoints")
+        self.final_alpha_cumprod = torch.tensor(1.0) if self.config.get("set_alpha_to_one", False) else self.alphas_cumprod[0]
+        self.spacing = self.config.get("timestep_spacing", "leading")
+
+    def set_timesteps(self, n, device=None):
+        N = self.config["num_train_timesteps"]
+        self.num_inference_steps = n
+        if self.spacing == "linspace":
+            ts = np.linspace(0, N - 1, n).round().astype(np.int64)
+        elif self.spacing == "leading":
+            ts = (np.arange(0, n) * (N // n)).round()
+            ts += self.config.get("steps_offset", 0)
+        else:
+            ts = np.round(np.arange(N, 0, -N / n))[::-1].astype(np.int64)
+            ts -= 1
+        plms = np.concatenate([ts[:-1], ts[-2:-1], ts[-1:]])[::-1].copy()
+        self.timesteps = torch.from_numpy(plms.astype(np.int64))
+        self.ets, self.counter, self.cur_sample = [], 0, None
+
+    def scale_model_input(self, x, t):
+        return x
+
+    def _prev(self, x, t, prev_t, mo):
+        a_t = self.alphas_cumprod[t]
+        a_p = self.alphas_cumprod[prev_t] if prev_t >= 0 else self.final_alpha_cumprod
+        b_t, b_p = 1 - a_t, 1 - a_p
+        sample_coeff = (a_p / a_t) ** 0.5
+        denom = a_t * b_p ** 0.5 + (a_t * b_t * a_p) ** 0.5
+        return sample_coeff * x - (a_p - a_t) * mo / denom
+
+    def step(self, eps, t, x):
+        t = int(t)
+        ratio = self.config["num_train_timesteps"] // self.num_inference_steps
+        prev_t = t - ratio
+        x = x.to(torch.float32)
+        if self.counter != 1:
+            self.ets = self.ets[-3:]
+            self.ets.append(eps)
+        else:
+            prev_t = t
+            t = t + ratio
+        if len(self.ets) == 1 and self.counter == 0:
+            mo = eps
+            self.cur_sample = x
+        elif len(self.ets) == 1 and self.counter == 1:
+            mo = (eps + self.ets[-1]) / 2
+            x = self.cur_sample
+            self.cur_sample = None
+        elif len(self.ets) == 2:
+            mo = (3 * self.ets[-1] - self.ets[-2]) / 2
+        elif len(self.ets) == 3:
+            mo = (23 * self.ets[-1] - 16 * self.ets[-2] + 5 * self.ets[-3]) / 12
+        else:
+            mo = (1 / 24) * (55 * self.ets[-1] - 59 * self.ets[-2] + 37 * self.ets[-3] - 9 * self.ets[-4])
+        out = self._prev(x, t, prev_t, mo)
+        self.counter += 1
+        return out
+
+    def add_noise(self, x0, noise, timesteps):
+        a = self.alphas_cumprod[timesteps.long()].flatten().to(x0.dtype)
+        while a.dim() < x0.dim():
+            a = a.unsqueeze(-1)
+        return a ** 0.5 * x0 + (1 - a) ** 0.5 * noise
+
+
+STOCHASTIC = ("euler_a", "DPM++ 2M SDE Karras")
+
+
 def make_scheduler(name: str, config: dict):
-    """Name table of models/stable_diffusion.py:205-222 (hot-path subset)."""
+    """Name table of models/stable_diffusion.py:205-222 (all but uni_pc)."""
     if name == "euler":
         return EulerDiscreteOracle(**config)
     if name == "DDIM":
@@ -244,4 +373,10 @@ def make_scheduler(name: str, config: dict):
         return DPMSolverMultistepOracle(**config)
     if name == "DPM++ 2M Karras":
         return DPMSolverMultistepOracle(use_karras_sigmas=True, **config)
+    if name == "euler_a":
+        return EulerAncestralOracle(**config)
+    if name == "DPM++ 2M SDE Karras":
+        return DPMSolverSDEOracle(**config)
+    if name == "PNDM":
+        return PNDMOracle(**config)
     raise ValueError(f"Unknown scheduler name: {name}")

@@ -505,6 +505,7 @@ int launch_softmax_rows(const void* plan, cudaStream_t s) {
 struct CSParams {
   const bf16* eps; long long ld_eps; const void* x; void* x_out; float* x0_prev; bf16* next_in;
   const float* table; const int* counter; float gs; int cfg, x_dtype, B, C, hw, Cpad, rep, nsteps, gs_from_table;
+  const float* noise; float* eps_hist; float* x_saved;
 };
 __global__ void cfg_step_kernel(const CSParams p) {
   pdl_launch_dependents();
@@ -517,6 +518,10 @@ __global__ void cfg_step_kernel(const CSParams p) {
   const float K1 = row[B200SD_ST_K1], K2 = row[B200SD_ST_K2], CX = row[B200SD_ST_CX], CE = row[B200SD_ST_CE],
               C0 = row[B200SD_ST_C0], C1 = row[B200SD_ST_C1];
   const float gs = p.gs_from_table ? row[B200SD_ST_GUIDANCE] : p.gs;
+  const float CN = p.noise ? row[B200SD_ST_CN] : 0.f;
+  const float H1 = row[B200SD_ST_H1], H2 = row[B200SD_ST_H2], H3 = row[B200SD_ST_H3];
+  const int flags = static_cast<int>(row[B200SD_ST_FLAGS]);
+  const long long plane = static_cast<long long>(p.B) * p.C * p.hw;
   float next_scale = 1.0f;
   if (p.next_in && step + 1 < p.nsteps) next_scale = p.table[static_cast<long long>(step + 1) * B200SD_STEP_ROW + B200SD_ST_IN_SCALE];
   const bf16* eu = p.eps + (static_cast<long long>(b) * p.hw + pix) * p.ld_eps;
@@ -526,13 +531,25 @@ __global__ void cfg_step_kernel(const CSParams p) {
     float e = u;
     if (p.cfg) e = gs * (__bfloat162float(ec[c]) - u) + u;
     const long long xi = (static_cast<long long>(b) * p.C + c) * p.hw + pix;
-    const float x = load_as_float(p.x, xi, p.x_dtype);
+    const float x_now = load_as_float(p.x, xi, p.x_dtype);
+    const float x = (p.x_saved && (flags & B200SD_STF_USE_SAVED_X)) ? p.x_saved[xi] : x_now;
     const float x0 = (x - K1 * e) * K2;
     float xn = CX * x + CE * e + C0 * x0;
     if (p.x0_prev) {
       if (C1 != 0.f) xn += C1 * (x0 - p.x0_prev[xi]);
       p.x0_prev[xi] = x0;
     }
+    if (CN != 0.f) xn += CN * p.noise[static_cast<long long>(step) * plane + xi];
+    if (p.eps_hist) {
+      const float h1 = p.eps_hist[xi], h2 = p.eps_hist[plane + xi], h3 = p.eps_hist[2 * plane + xi];
+      xn += H1 * h1 + H2 * h2 + H3 * h3;
+      if (flags & B200SD_STF_PUSH_EPS) {
+        p.eps_hist[2 * plane + xi] = h2;
+        p.eps_hist[plane + xi] = h1;
+        p.eps_hist[xi] = e;
+      }
+    }
+    if (p.x_saved && (flags & B200SD_STF_SAVE_X)) p.x_saved[xi] = x_now;
     store_from_float(p.x_out, xi, p.x_dtype, xn);
     if (p.next_in) {
       // the UNet consumes the value the pipeline would hand it: latents in their storage dtype, scaled
@@ -799,7 +816,8 @@ int plan_cfg_step(const b200sd_cfg_step& g, PlannedOp* out) {
   B200SD_CHECK_ARG(g.B >= 1 && g.C >= 1 && g.hw >= 1 && g.ld_eps >= g.C && g.nsteps >= 1, "cfg_step: bad shape");
   B200SD_CHECK_ARG(!g.next_in || (g.Cpad >= g.C && g.rep >= 1), "cfg_step: next_in needs Cpad/rep");
   CSParams p{static_cast<const bf16*>(g.eps), g.ld_eps, g.x, g.x_out, g.x0_prev, static_cast<bf16*>(g.next_in),
-             g.step_table, g.step_counter, g.guidance_scale, g.cfg, g.x_dtype, g.B, g.C, g.hw, g.Cpad, g.rep, g.nsteps, g.gs_from_table};
+             g.step_table, g.step_counter, g.guidance_scale, g.cfg, g.x_dtype, g.B, g.C, g.hw, g.Cpad, g.rep, g.nsteps, g.gs_from_table,
+             g.noise, g.eps_hist, g.x_saved};
   return finish_plan(out, B200SD_OP_CFG_STEP, p, launch_cfg_step);
 }
 

@@ -31,7 +31,8 @@ MAX_STEPS = 1000
 
 class DenoiseEngine:
     def __init__(self, unet: B200UNet, B: int, h: int, w: int, do_cfg: bool, ctx_dim: int, uses_history: bool,
-                 pair_group=None, pair_rank: int = 0, use_graph: bool = True):
+                 pair_group=None, pair_rank: int = 0, use_graph: bool = True, eps_history: bool = False,
+                 noise_steps: int = 0):
         if unet.packed is None:
             raise RuntimeError("UNet has no weights on a CUDA device")
         self.unet, self.B, self.h, self.w, self.do_cfg = unet, B, h, w, do_cfg
@@ -56,6 +57,11 @@ class DenoiseEngine:
         self.counter = pre.zeros([1], torch.int32)
         self.unet_in_full = pre.empty([rep_total * B, h * w, pk.cin_pad])  # both CFG halves (identical rows)
         self.hist = pre.zeros([B, C, h * w], torch.float32) if uses_history else None
+        # PNDM / PLMS: three earlier eps + the remembered sample; ancestral / SDE samplers: one standard-normal draw per
+        # step, generated for the whole trajectory before the loop (the captured graph indexes it by the step counter)
+        self.eps_hist = pre.zeros([3, B, C, h * w], torch.float32) if eps_history else None
+        self.x_saved = pre.zeros([B, C, h * w], torch.float32) if eps_history else None
+        self.noise = pre.zeros([noise_steps, B, C, h * w], torch.float32) if noise_steps > 0 else None
         pre.prep_latents(self.latents, self.unet_in_full, rep=rep_total, step_table=self.table, step_counter=self.counter)
         self.prep = pre
 
@@ -88,7 +94,8 @@ class DenoiseEngine:
 
     def _emit_tail(self, b: L.Builder, eps):
         b.cfg_step(eps, self.latents, self.latents, self.table, self.counter, 1.0, self.do_cfg, MAX_STEPS,
-                   x0_prev=self.hist, next_in=self.unet_in_full, rep=2 if self.do_cfg else 1, gs_from_table=True)
+                   x0_prev=self.hist, next_in=self.unet_in_full, rep=2 if self.do_cfg else 1, gs_from_table=True,
+                   noise=self.noise, eps_hist=self.eps_hist, x_saved=self.x_saved)
         b.step_advance(self.counter)
 
     @property
@@ -96,11 +103,23 @@ class DenoiseEngine:
         return self.b.prog.num_launches + (self.tail.prog.num_launches if self.tail else 0)
 
     # ---- one trajectory ---------------------------------------------------------------------------------
-    def load(self, latents, prompt_embeds, step_rows: torch.Tensor, guidance_scale: float, text_embeds=None, time_ids=None):
-        """Stage one request: latents (any float dtype, NCHW), context embeddings, the scheduler's table rows."""
+    def load(self, latents, prompt_embeds, step_rows: torch.Tensor, guidance_scale: float, text_embeds=None, time_ids=None,
+             generator=None):
+        """Stage one request: latents (any float dtype, NCHW), context embeddings, the scheduler's table rows.
+        `generator`: device RNG the per-step noise of a stochastic sampler is drawn from (None: the global one, which
+        is what the reference's `scheduler.step(noise_pred, t, latents)` uses, pipeline :489)."""
         n = step_rows.shape[0]
         if n > MAX_STEPS:
             raise ValueError(f"at most {MAX_STEPS} sampler steps")
+        if self.noise is not None:
+            if n > self.noise.shape[0]:
+                raise ValueError(f"engine built for {self.noise.shape[0]} noisy steps, {n} requested")
+            self.noise[:n].copy_(torch.randn((n,) + tuple(self.noise.shape[1:]), generator=generator, device=self.device,
+                                             dtype=torch.float32))
+        elif bool((step_rows[:, N.ST_CN] != 0).any()):
+            raise ValueError("this sampler needs per-step noise: build the engine with noise_steps > 0")
+        if self.eps_hist is not None:
+            self.eps_hist.zero_()
         rows = step_rows.clone()
         rows[:, N.ST_GUIDANCE] = float(guidance_scale)
         rows[0, N.ST_C1] = 0.0  # a multistep solver has no history on the first executed step (img2img starts mid-table)

@@ -325,7 +325,7 @@ class Builder:
         return out
 
     def cfg_step(self, eps, x, x_out, step_table, step_counter, guidance_scale, cfg, nsteps, x0_prev=None, next_in=None, rep=2,
-                 gs_from_table=False):
+                 gs_from_table=False, noise=None, eps_hist=None, x_saved=None):
         B, Cc, h, w = x.shape
         p = N.CfgStep()
         p.eps, p.ld_eps = eps.data_ptr(), eps.shape[-1]
@@ -335,7 +335,11 @@ class Builder:
         p.B, p.C, p.hw = B, Cc, h * w
         p.Cpad = next_in.shape[-1] if next_in is not None else 0
         p.rep, p.nsteps, p.gs_from_table = rep, nsteps, int(bool(gs_from_table))
-        self.prog.add(N.OP_CFG_STEP, p, self.tag, (eps, x, x_out, step_table, step_counter, x0_prev, next_in))
+        for t in (noise, eps_hist, x_saved):
+            if t is not None and (t.dtype != torch.float32 or not t.is_contiguous()):
+                raise ValueError("cfg_step: noise / eps_hist / x_saved must be contiguous fp32")
+        p.noise, p.eps_hist, p.x_saved = ptr(noise), ptr(eps_hist), ptr(x_saved)
+        self.prog.add(N.OP_CFG_STEP, p, self.tag, (eps, x, x_out, step_table, step_counter, x0_prev, next_in, noise, eps_hist, x_saved))
         return x_out
 
     def axpby(self, x, a, y=None, b=0.0, out=None):

@@ -49,18 +49,25 @@ class StableDiffusionUnifiedPipeline:
         self.use_graph = use_graph
         self.verbose = verbose
         self._engines: Dict[tuple, DenoiseEngine] = {}
+        # ancestral / SDE samplers: the reference calls scheduler.step without a generator (:489), i.e. the noise comes
+        # from the device's global RNG; tests set a seeded device generator here to feed the oracle the same draws
+        self._step_generator = None
 
     def _log(self, *a):
         if self.verbose:
             print(*a)
 
-    def _engine(self, B, h, w, ctx_dim) -> DenoiseEngine:
+    def _engine(self, B, h, w, ctx_dim, n_steps: int = 0) -> DenoiseEngine:
         m = self.model
-        key = (id(m.base), id(m.base.packed), B, h, w, ctx_dim, self.do_classifier_free_guidance, m.scheduler._uses_history)
+        sch = m.scheduler
+        noise_steps = (n_steps + 63) // 64 * 64 if sch._stochastic else 0  # capacity of the pre-drawn noise, in steps
+        key = (id(m.base), id(m.base.packed), B, h, w, ctx_dim, self.do_classifier_free_guidance, sch._uses_history,
+               sch._uses_eps_history, noise_steps)
         eng = self._engines.get(key)
         if eng is None:
-            eng = DenoiseEngine(m.base, B, h, w, self.do_classifier_free_guidance, ctx_dim, m.scheduler._uses_history,
-                                pair_group=self.pair_group, pair_rank=self.pair_rank, use_graph=self.use_graph)
+            eng = DenoiseEngine(m.base, B, h, w, self.do_classifier_free_guidance, ctx_dim, sch._uses_history,
+                                pair_group=self.pair_group, pair_rank=self.pair_rank, use_graph=self.use_graph,
+                                eps_history=sch._uses_eps_history, noise_steps=noise_steps)
             self._engines = {k: v for k, v in self._engines.items() if k[1] == id(m.base.packed)}  # drop stale weights
             self._engines[key] = eng
         return eng
@@ -162,10 +169,10 @@ class StableDiffusionUnifiedPipeline:
         prompt_embeds = prompt_embeds.to(self.device)
 
         B, _, h, w = latents.shape
-        eng = self._engine(B, h, w, prompt_embeds.shape[-1])
         n = len(timesteps)
-        rows = m.scheduler._table[start_index:start_index + n]
-        eng.load(latents, prompt_embeds, rows, guidance_scale, text_embeds, time_ids)
+        eng = self._engine(B, h, w, prompt_embeds.shape[-1], n)
+        rows = m.scheduler.rows_for(start_index, n)
+        eng.load(latents, prompt_embeds, rows, guidance_scale, text_embeds, time_ids, generator=self._step_generator)
         out = eng.run(n)
         self.last_engine = eng
 

@@ -117,8 +117,9 @@ class _SchedulerBase:
     def scale_model_input(self, sample, timestep=None):
         return sample
 
-    def step(self, model_output, timestep, sample, return_dict=False, **unused):
-        """x_{t-1} from (already CFG-combined) eps — the un-fused call at pipeline :489."""
+    def step(self, model_output, timestep, sample, return_dict=False, generator=None, **unused):
+        """x_{t-1} from (already CFG-combined) eps — the un-fused call at pipeline :489.  Stochastic samplers draw
+        their noise here, like diffusers, from `generator` (the reference passes none: the device's global RNG)."""
         self._init_step_index(timestep)
         dev = sample.device
         if dev.type != "cuda":
@@ -135,12 +136,18 @@ class _SchedulerBase:
             st["x"] = b.empty([B, C, h, w], torch.float32)
             st["counter"] = b.zeros([1], torch.int32)
             st["hist"] = b.zeros([B, C, h * w], torch.float32) if self._uses_history else None
-            b.cfg_step(st["eps"], st["x"], st["x"], self.step_table(dev), st["counter"], 1.0, False,
-                       len(self._table), x0_prev=st["hist"])
+            st["eps_hist"] = b.zeros([3, B, C, h * w], torch.float32) if self._uses_eps_history else None
+            st["x_saved"] = b.zeros([B, C, h * w], torch.float32) if self._uses_eps_history else None
+            st["noise"] = b.zeros([len(self._table), B, C, h * w], torch.float32) if self._stochastic else None
+            b.cfg_step(st["eps"], st["x"], st["x"], self._unfused_table(dev), st["counter"], 1.0, False,
+                       len(self._table), x0_prev=st["hist"], noise=st["noise"], eps_hist=st["eps_hist"], x_saved=st["x_saved"])
             self._programs[key] = st
+        cidx = self._unfused_counter()
         st["eps_nchw"].copy_(model_output)
         st["x"].copy_(sample)
-        st["counter"].fill_(self._step_index)
+        st["counter"].fill_(cidx)
+        if self._stochastic:
+            st["noise"][cidx].copy_(torch.randn((B, C, h, w), generator=generator, device=dev, dtype=torch.float32).view(B, C, h * w))
         st["b"].prog.run(torch.cuda.current_stream(dev).cuda_stream)
         self._step_index += 1
         # diffusers casts the result to the model-output dtype; we return the sample's dtype when
@@ -149,6 +156,18 @@ class _SchedulerBase:
         prev = st["x"].to(out_dtype)
         return (prev,)
 
+    def _unfused_table(self, dev):
+        return self.step_table(dev)
+
+    def _unfused_counter(self) -> int:
+        return self._step_index
+
+    def rows_for(self, start_index: int, n: int) -> torch.Tensor:
+        """Host table rows of the n steps executed from `start_index` (img2img starts mid-schedule)."""
+        return self._table[start_index:start_index + n]
+
+    _uses_eps_history = False   # PNDM / PLMS: eps history + remembered sample
+    _stochastic = False         # the update has a noise term (ancestral / SDE samplers)
     _uses_history = False
 
 
@@ -357,14 +376,186 @@ class B200DPMSolverMultistepScheduler(_SchedulerBase):
         return self._elementwise(original_samples, float(a), noise, float(s))
 
 
+class B200EulerAncestralDiscreteScheduler(B200EulerDiscreteScheduler):
+    """EulerAncestralDiscreteScheduler (name `euler_a`, models/stable_diffusion.py:209-210): Euler to sigma_down,
+    then fresh noise of scale sigma_up.  Same timestep / sigma tables as `euler`."""
+    _stochastic = True
+
+    def _build_table(self):
+        tab = super()._build_table()
+        for i in range(self.num_inference_steps):
+            s_from, s_to = self.sigmas[i], self.sigmas[i + 1]
+            s_up = (s_to ** 2 * (s_from ** 2 - s_to ** 2) / s_from ** 2) ** 0.5
+            s_down = (s_to ** 2 - s_up ** 2) ** 0.5
+            tab[i, N.ST_CE] = s_down - s_from
+            tab[i, N.ST_CN] = s_up
+        return tab
+
+
+class B200DPMSolverSDEScheduler(B200DPMSolverMultistepScheduler):
+    """`DPM++ 2M SDE Karras` as the reference builds it (models/stable_diffusion.py:215-218):
+    algorithm_type="sde-dpmsolver++"; the Karras switch is spelt `se_karras_sigmas` there, which `from_config` drops,
+    so the sigma spacing is the plain one — reproduced as is."""
+    _stochastic = True
+    _class_defaults = dict(B200DPMSolverMultistepScheduler._class_defaults, algorithm_type="sde-dpmsolver++")
+
+    def __init__(self, se_karras_sigmas=None, **config):
+        config.setdefault("algorithm_type", "sde-dpmsolver++")
+        _SchedulerBase.__init__(self, **config)
+        c = self.config
+        if c["algorithm_type"] != "sde-dpmsolver++" or c["solver_order"] != 2 or c["solver_type"] != "midpoint":
+            raise ValueError("only sde-dpmsolver++ / order 2 / midpoint is supported")
+        if c["timestep_spacing"] != "linspace" or c["final_sigmas_type"] != "zero":
+            raise ValueError("DPM++ 2M SDE: only linspace spacing with final sigma zero is supported")
+
+    def _build_table(self):
+        n = self.num_inference_steps
+        tab = torch.zeros(n, N.STEP_ROW, dtype=torch.float32)
+        for i in range(n):
+            a_s, s_s = self._alpha_sigma(self.sigmas[i])
+            a_t, s_t = self._alpha_sigma(self.sigmas[i + 1])
+            lam_t = torch.log(a_t) - torch.log(s_t)
+            lam_s = torch.log(a_s) - torch.log(s_s)
+            h = lam_t - lam_s
+            gain = a_t * (1 - torch.exp(-2.0 * h))
+            tab[i, N.ST_TIMESTEP] = float(self._timesteps_host[i])
+            tab[i, N.ST_IN_SCALE] = 1.0
+            tab[i, N.ST_K1], tab[i, N.ST_K2] = s_s, 1.0 / a_s
+            tab[i, N.ST_CX] = s_t / s_s * torch.exp(-h)
+            tab[i, N.ST_C0] = gain
+            tab[i, N.ST_CN] = s_t * torch.sqrt(1.0 - torch.exp(-2.0 * h))
+            if not ((i == 0) or (i == n - 1)):
+                a_s1, s_s1 = self._alpha_sigma(self.sigmas[i - 1])
+                lam_s1 = torch.log(a_s1) - torch.log(s_s1)
+                r0 = (lam_s - lam_s1) / h
+                tab[i, N.ST_C1] = 0.5 * gain * (1.0 / r0)
+        return tab
+
+
+class B200PNDMScheduler(_SchedulerBase):
+    """PNDMScheduler (name `PNDM`, models/stable_diffusion.py:219-220) with skip_prk_steps (all SD checkpoints): PLMS —
+    linear multistep on eps (up to 4 terms), N + 1 UNet evaluations, the second timestep visited twice, the second
+    evaluation redoing the first step from the remembered sample with the averaged eps."""
+    _class_defaults = dict(timestep_spacing="leading", skip_prk_steps=True, set_alpha_to_one=False, steps_offset=0)
+    init_noise_sigma = 1.0
+    _uses_eps_history = True
+
+    def __init__(self, **config):
+        super().__init__(**config)
+        if not self.config["skip_prk_steps"]:
+            raise ValueError("PNDM with Runge-Kutta warm-up steps is not on the SD path (SD configs set skip_prk_steps)")
+        self.final_alpha_cumprod = torch.tensor(1.0) if self.config["set_alpha_to_one"] else self.alphas_cumprod[0]
+        self._start = 0
+
+    def set_timesteps(self, num_inference_steps, device=None):
+        c = self.config
+        ntrain = c["num_train_timesteps"]
+        n = self.num_inference_steps = int(num_inference_steps)
+        sp = c["timestep_spacing"]
+        if sp == "linspace":
+            ts = np.linspace(0, ntrain - 1, n).round().astype(np.int64)
+        elif sp == "leading":
+            ts = (np.arange(0, n) * (ntrain // n)).round()
+            ts += c["steps_offset"]
+        elif sp == "trailing":
+            ts = np.round(np.arange(ntrain, 0, -ntrain / n))[::-1].astype(np.int64)
+            ts -= 1
+        else:
+            raise ValueError(f"{sp} is not supported")
+        plms = np.concatenate([ts[:-1], ts[-2:-1], ts[-1:]])[::-1].copy()
+        self._timesteps_host = plms.astype(np.int64)
+        self._start = 0
+        self._finish_set_timesteps(device)
+        self.timesteps = torch.from_numpy(self._timesteps_host).to(self.device)
+
+    def index_for_timestep(self, timestep) -> int:
+        idx = np.nonzero(self._timesteps_host == int(timestep))[0]
+        if len(idx) == 0:
+            raise ValueError(f"timestep {timestep} is not in the schedule")
+        return int(idx[0])
+
+    def _build_table(self):
+        return self._build_table_from(0)
+
+    def _build_table_from(self, start: int):
+        """Rows for the sequence executed from schedule position `start`: PNDM's special cases follow ITS call counter
+        (0 on the first call), not the position in the schedule — exactly what diffusers does when img2img starts late."""
+        ts = self._timesteps_host[start:]
+        ratio = self.config["num_train_timesteps"] // self.num_inference_steps
+        tab = torch.zeros(len(ts), N.STEP_ROW, dtype=torch.float32)
+        n_ets = 0
+        for counter, t in enumerate(int(v) for v in ts):
+            prev_t = t - ratio
+            if counter != 1:
+                n_ets = min(n_ets, 3) + 1
+            else:
+                prev_t, t_used = t, t + ratio
+            t_eff = t if counter != 1 else t_used
+            a_t = self.alphas_cumprod[t_eff]
+            a_p = self.alphas_cumprod[prev_t] if prev_t >= 0 else self.final_alpha_cumprod
+            b_t, b_p = 1 - a_t, 1 - a_p
+            sample_coeff = (a_p / a_t) ** 0.5
+            g = -(a_p - a_t) / (a_t * b_p ** 0.5 + (a_t * b_t * a_p) ** 0.5)
+            if n_ets == 1 and counter == 0:
+                w, flags = (1.0, 0.0, 0.0, 0.0), N.STF_PUSH_EPS | N.STF_SAVE_X
+            elif n_ets == 1 and counter == 1:
+                w, flags = (0.5, 0.5, 0.0, 0.0), N.STF_USE_SAVED_X
+            elif n_ets == 2:
+                w, flags = (1.5, -0.5, 0.0, 0.0), N.STF_PUSH_EPS
+            elif n_ets == 3:
+                w, flags = (23 / 12, -16 / 12, 5 / 12, 0.0), N.STF_PUSH_EPS
+            else:
+                w, flags = (55 / 24, -59 / 24, 37 / 24, -9 / 24), N.STF_PUSH_EPS
+            tab[counter, N.ST_TIMESTEP] = float(t)
+            tab[counter, N.ST_IN_SCALE] = 1.0
+            tab[counter, N.ST_K2] = 1.0
+            tab[counter, N.ST_CX] = sample_coeff
+            tab[counter, N.ST_CE], tab[counter, N.ST_H1] = g * w[0], g * w[1]
+            tab[counter, N.ST_H2], tab[counter, N.ST_H3] = g * w[2], g * w[3]
+            tab[counter, N.ST_FLAGS] = float(flags)
+        return tab
+
+    def rows_for(self, start_index: int, n: int) -> torch.Tensor:
+        return self._build_table_from(start_index)[:n]
+
+    # un-fused calls: the table is rebuilt from wherever the first step() lands
+    def _init_step_index(self, timestep):
+        if self._step_index is None:
+            self._step_index = self._start = self.index_for_timestep(timestep)
+            self._programs.clear()
+
+    def _unfused_table(self, dev):
+        key = f"pndm{self._start}@{dev}"
+        if key not in self._dev:
+            full = torch.zeros(len(self._table), N.STEP_ROW, dtype=torch.float32)
+            rows = self._build_table_from(self._start)
+            full[:len(rows)] = rows
+            self._dev[key] = full.to(dev)
+        return self._dev[key]
+
+    def _unfused_counter(self) -> int:
+        return self._step_index - self._start
+
+    def add_noise(self, original_samples, noise, timesteps):
+        ts = set(int(t) for t in timesteps.reshape(-1).tolist())
+        if len(ts) != 1:
+            raise ValueError("add_noise: per-sample timesteps must be equal on this path")
+        a = self.alphas_cumprod[ts.pop()]
+        return self._elementwise(original_samples, float(a ** 0.5), noise, float((1 - a) ** 0.5))
+
+
 SCHEDULER_CLASSES = {
     "euler": (B200EulerDiscreteScheduler, {}),
     "DDIM": (B200DDIMScheduler, {}),
     "DPM++ 2M": (B200DPMSolverMultistepScheduler, {}),
     "DPM++ 2M Karras": (B200DPMSolverMultistepScheduler, dict(use_karras_sigmas=True)),
+    "euler_a": (B200EulerAncestralDiscreteScheduler, {}),
+    # the reference's own spelling of the call, typo included (models/stable_diffusion.py:215-218)
+    "DPM++ 2M SDE Karras": (B200DPMSolverSDEScheduler, dict(se_karras_sigmas=True, algorithm_type="sde-dpmsolver++")),
+    "PNDM": (B200PNDMScheduler, {}),
 }
 # names the reference accepts (models/stable_diffusion.py:205-222) that are not on the hot path yet (SURVEY §8f rank 3)
-NEXT_ROW_SCHEDULERS = ("euler_a", "DPM++ 2M SDE Karras", "PNDM", "uni_pc")
+NEXT_ROW_SCHEDULERS = ("uni_pc",)
 
 
 def make_scheduler(name: str, config) -> _SchedulerBase:

@@ -69,6 +69,67 @@ def test_step_table_reproduces_oracle_trajectory(name, n):
         torch.testing.assert_close(x, xo, rtol=2e-5, atol=2e-5)
 
 
+class _KernelState:
+    """fp32 emulation of cfg_step_kernel (csrc/bandwidth.cu) including the noise, eps-history and saved-sample terms."""
+
+    def __init__(self, x):
+        self.hist = torch.zeros_like(x)
+        self.eh = [torch.zeros_like(x) for _ in range(3)]
+        self.saved = torch.zeros_like(x)
+
+    def step(self, row, x, eps, noise, sched):
+        g = lambda c: row[c]
+        flags = int(row[N.ST_FLAGS])
+        xs = self.saved if (sched._uses_eps_history and flags & N.STF_USE_SAVED_X) else x
+        x0 = (xs - g(N.ST_K1) * eps) * g(N.ST_K2)
+        xn = g(N.ST_CX) * xs + g(N.ST_CE) * eps + g(N.ST_C0) * x0
+        if sched._uses_history:
+            if g(N.ST_C1) != 0:
+                xn = xn + g(N.ST_C1) * (x0 - self.hist)
+            self.hist = x0
+        if sched._stochastic and g(N.ST_CN) != 0:
+            xn = xn + g(N.ST_CN) * noise
+        if sched._uses_eps_history:
+            xn = xn + g(N.ST_H1) * self.eh[0] + g(N.ST_H2) * self.eh[1] + g(N.ST_H3) * self.eh[2]
+            if flags & N.STF_PUSH_EPS:
+                self.eh = [eps, self.eh[0], self.eh[1]]
+            if flags & N.STF_SAVE_X:
+                self.saved = x
+        return xn
+
+
+@pytest.mark.parametrize("name,n", [("euler_a", 20), ("euler_a", 1), ("DPM++ 2M SDE Karras", 20), ("DPM++ 2M SDE Karras", 2),
+                                    ("PNDM", 20), ("PNDM", 50), ("PNDM", 3), ("euler", 7), ("DPM++ 2M", 9)])
+def test_step_table_next_row_schedulers(name, n):
+    """the table rows of euler_a / DPM++ 2M SDE / PNDM drive the kernel's linear form to the oracle's
+    trajectory (PNDM: N + 1 evaluations, second timestep twice, averaged redo of the first step)."""
+    s = make_scheduler(name, B200EulerDiscreteScheduler(**CFG).config)
+    s.set_timesteps(n)
+    o = OS.make_scheduler(name, CFG)
+    o.set_timesteps(n)
+    assert torch.equal(s.timesteps.cpu(), o.timesteps) and len(s._table) == len(o.timesteps)
+    g = torch.Generator().manual_seed(1)
+    x = torch.randn(2, 4, 8, 8, generator=g) * float(o.init_noise_sigma)
+    xo, ks = x.clone(), _KernelState(x)
+    for i, t in enumerate(o.timesteps):
+        eps = torch.randn(2, 4, 8, 8, generator=g)
+        noise = torch.randn(2, 4, 8, 8, generator=g)
+        assert s._table[i, N.ST_TIMESTEP].item() == float(t)
+        xo = o.step(eps, t, xo, noise) if name in OS.STOCHASTIC else o.step(eps, t, xo)
+        x = ks.step(s._table[i], x, eps, noise, s)
+        torch.testing.assert_close(x, xo, rtol=5e-5, atol=5e-5)
+
+
+def test_pndm_rows_follow_the_call_counter():
+    """img2img starts mid-schedule: PNDM's special first/second step follow its call counter, not the table position."""
+    s = make_scheduler("PNDM", B200EulerDiscreteScheduler(**CFG).config)
+    s.set_timesteps(20)
+    rows = s.rows_for(8, 5)
+    assert rows.shape[0] == 5 and int(rows[0, N.ST_FLAGS]) == (N.STF_PUSH_EPS | N.STF_SAVE_X)
+    assert int(rows[1, N.ST_FLAGS]) == N.STF_USE_SAVED_X and rows[0, N.ST_TIMESTEP] == float(s.timesteps[8])
+    assert s.timesteps.tolist()[:4] == [951, 901, 901, 851] and len(s.timesteps) == 21
+
+
 def test_from_config_uses_target_class_defaults():
     e = B200EulerDiscreteScheduler(**CFG)                       # SD1.5's PNDM-style config: no timestep_spacing key
     assert e.config.timestep_spacing == "linspace"
@@ -79,7 +140,7 @@ def test_from_config_uses_target_class_defaults():
     with pytest.raises(ValueError, match="Unknown scheduler name"):
         make_scheduler("nope", e.config)
     with pytest.raises(ValueError, match="no B200 kernel yet"):
-        make_scheduler("euler_a", e.config)                      # a 'next' row: fails loudly, no CPU fallback
+        make_scheduler("uni_pc", e.config)                       # the one remaining 'next' row: fails loudly, no CPU fallback
 
 
 def test_geglu_interleave_and_conv_packing():

@@ -155,7 +155,8 @@ def test_vae_encode_vs_oracle(cuda_device):
     assert rl2 <= 2e-2
 
 
-@pytest.mark.parametrize("sched_name,steps", [("euler", 12), ("DDIM", 12), ("DPM++ 2M", 12), ("DPM++ 2M Karras", 8)])
+@pytest.mark.parametrize("sched_name,steps", [("euler", 12), ("DDIM", 12), ("DPM++ 2M", 12), ("DPM++ 2M Karras", 8),
+                                              ("euler_a", 12), ("DPM++ 2M SDE Karras", 12), ("PNDM", 12)])
 def test_fused_loop_vs_oracle(cuda_device, sched_name, steps):
     """Whole trajectory: B200 fused loop (graph replay) vs the oracle's restatement of the reference loop."""
     from oracle import pipeline as OP
@@ -175,19 +176,25 @@ def test_fused_loop_vs_oracle(cuda_device, sched_name, steps):
     pe = torch.randn(B, 77, 64, generator=g).to(torch.bfloat16)
     ne = torch.randn(B, 77, 64, generator=g).to(torch.bfloat16)
     pipe = StableDiffusionUnifiedPipeline(do_cfg=True, device=str(dev), output_type="latents")
+    step_noise = None
+    if sched_name in OS.STOCHASTIC:  # same device draws for both sides (the engine draws all steps in one randn call)
+        pipe._step_generator = torch.Generator(device=dev).manual_seed(77)
+        step_noise = torch.randn((steps, B, 4, 16 * 16), generator=torch.Generator(device=dev).manual_seed(77), device=dev,
+                                 dtype=torch.float32).view(steps, B, 4, 16, 16).cpu()
     out = pipe(model, prompt_embeds=pe.to(dev), negative_prompt_embeds=ne.to(dev), num_inference_steps=steps,
                guidance_scale=7.5, latents=lat.to(dev), height=128, width=128).float().cpu()
     osched = OS.make_scheduler(sched_name, dict(OS.SD15_SCHEDULER_CONFIG))
     osched.set_timesteps(steps)
     assert torch.equal(osched.timesteps.cpu(), model.scheduler.timesteps.cpu()), "timestep tables differ"
     x0 = lat * float(osched.init_noise_sigma)
-    ref = OP.denoise(oracle.cpu(), osched, x0, torch.cat([ne, pe]).float(), osched.timesteps, 7.5)
+    ref = OP.denoise(oracle.cpu(), osched, x0, torch.cat([ne, pe]).float(), osched.timesteps, 7.5, step_noise=step_noise)
     rl2 = _rel_l2(out, ref)
     print(f"LOOP PARITY {sched_name} x{steps}: rel-L2 {rl2:.4g}")
     assert torch.isfinite(out).all() and rl2 <= 5e-2
 
 
-def test_unfused_reference_call_pattern_matches_fused(cuda_device):
+@pytest.mark.parametrize("sched_name", ["euler", "PNDM", "euler_a", "DPM++ 2M SDE Karras"])
+def test_unfused_reference_call_pattern_matches_fused(cuda_device, sched_name):
     """Driving the B200 objects exactly like the reference loop (pipeline :465-489) gives the fused result."""
     from stablediffusion_b200.models.stable_diffusion import SDModelWrapper
     from stablediffusion_b200.pipelines.sd_unified_pipeline import StableDiffusionUnifiedPipeline
@@ -196,11 +203,28 @@ def test_unfused_reference_call_pattern_matches_fused(cuda_device):
     cfg, ours, _ = _make_unet(dev, **SMALL_UNET)
     vcfg, vae, _ = _make_vae(dev)
     model = SDModelWrapper(vae=vae, base=ours, device=str(dev))
+    model.set_scheduler(sched_name)
+    stochastic = model.scheduler._stochastic
     g = torch.Generator().manual_seed(4)
     lat = torch.randn(1, 4, 16, 16, generator=g).to(dev)
     pe = torch.randn(1, 77, 64, generator=g).to(dev, torch.bfloat16)
     ne = torch.randn(1, 77, 64, generator=g).to(dev, torch.bfloat16)
     pipe = StableDiffusionUnifiedPipeline(do_cfg=True, device=str(dev), output_type="latents")
+    if stochastic:
+        pipe._step_generator = torch.Generator(device=dev).manual_seed(5)
+        draws = torch.randn((6, 1, 4, 256), generator=torch.Generator(device=dev).manual_seed(5), device=dev)
+
+        class _Replay:  # hands scheduler.step the draw the fused engine used for the same step
+            def __init__(self):
+                self.i = 0
+        replay = _Replay()
+        real_randn = torch.randn
+
+        def fake_randn(shape, generator=None, **kw):
+            if generator is replay:
+                replay.i += 1
+                return draws[replay.i - 1].view(shape).to(kw.get("dtype", torch.float32))
+            return real_randn(shape, generator=generator, **kw)
     fused = pipe(model, prompt_embeds=pe, negative_prompt_embeds=ne, num_inference_steps=6, guidance_scale=5.0,
                  latents=lat, height=128, width=128)
     sch = model.scheduler
@@ -213,7 +237,14 @@ def test_unfused_reference_call_pattern_matches_fused(cuda_device):
         noise_pred = model.base(inp, t, ctx, return_dict=False)[0]
         u, c = noise_pred.chunk(2)
         noise_pred = 5.0 * (c - u) + u
-        latents = sch.step(noise_pred, t, latents, return_dict=False)[0]
+        if stochastic:
+            torch.randn = fake_randn
+            try:
+                latents = sch.step(noise_pred, t, latents, return_dict=False, generator=replay)[0]
+            finally:
+                torch.randn = real_randn
+        else:
+            latents = sch.step(noise_pred, t, latents, return_dict=False)[0]
     rl2 = _rel_l2(latents.cpu(), fused.cpu())
     print(f"UNFUSED vs FUSED rel-L2 {rl2:.4g}")
     # the unfused pattern rounds eps and the scaled input to bf16 between the UNet, CFG and scheduler step, the fused loop
