@@ -185,7 +185,9 @@ enum { /* columns of one step-table row */
   B200SD_ST_H1 = 10,         /* x' += H1*e[-1] + H2*e[-2] + H3*e[-3]   (linear multistep on eps: PNDM / PLMS)     */
   B200SD_ST_H2 = 11,
   B200SD_ST_H3 = 12,
-  B200SD_ST_FLAGS = 13       /* float image of B200SD_STF_* bits                                               */
+  B200SD_ST_FLAGS = 13,      /* float image of B200SD_STF_* bits                                               */
+  B200SD_ST_BA = 14,         /* inpaint blend: x' = (1-m)*(BA*image_latents + BS*noise) + m*x'   (pipeline :492-506)  */
+  B200SD_ST_BS = 15
 };
 enum {
   B200SD_STF_PUSH_EPS = 1,   /* after the update: e[-3] <- e[-2] <- e[-1] <- eps                                */
@@ -250,6 +252,9 @@ typedef struct b200sd_cfg_step {
   const float* noise;    /* fp32 [nsteps_of_noise, B, C, hw]: row `step` is this step's standard-normal draw (NULL: CN ignored) */
   float* eps_hist;       /* fp32 [3, B, C, hw] eps history for the H1..H3 terms (NULL if unused)            */
   float* x_saved;        /* fp32 [B, C, hw] for B200SD_STF_SAVE_X / USE_SAVED_X (NULL if unused)             */
+  const float* blend_mask;  /* fp32 [B, hw], 1 = repaint; NULL = no inpaint blend                            */
+  const float* blend_image; /* fp32 [B, C, hw] latents of the original image                                 */
+  const float* blend_noise; /* fp32 [B, C, hw] the noise the trajectory started from                         */
 } b200sd_cfg_step;
 
 typedef struct b200sd_axpby {

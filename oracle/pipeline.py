@@ -15,7 +15,7 @@ def cfg_combine(noise_pred: torch.Tensor, guidance_scale: float) -> torch.Tensor
 
 @torch.no_grad()
 def denoise(unet, scheduler, latents, prompt_embeds, timesteps, guidance_scale, do_cfg=True, added_cond_kwargs=None,
-            return_eps=False, step_noise=None):
+            return_eps=False, step_noise=None, inpaint=None):
     """`step_noise[i]`: the standard-normal draw of step i for the ancestral / SDE samplers (the reference draws it
     inside scheduler.step from the global RNG, pipeline :489; tests pass the draws the device used)."""
     eps_trace = []
@@ -31,6 +31,12 @@ def denoise(unet, scheduler, latents, prompt_embeds, timesteps, guidance_scale, 
             latents = scheduler.step(noise_pred, t, latents, step_noise[i])
         else:
             latents = scheduler.step(noise_pred, t, latents)
+        if inpaint is not None:  # reference :492-506 (4-channel UNet): keep the unmasked region on the original image
+            init_mask, image_latents, noise = inpaint
+            proper = image_latents
+            if i < len(timesteps) - 1:
+                proper = scheduler.add_noise(image_latents, noise, torch.as_tensor([timesteps[i + 1]]))
+            latents = (1 - init_mask) * proper + init_mask * latents
     return (latents, eps_trace) if return_eps else latents
 
 

@@ -36,7 +36,7 @@ GEMM_BIAS, GEMM_BIAS_ROW, GEMM_ROWVEC, GEMM_RESIDUAL, GEMM_SILU, GEMM_GEGLU, GEM
 GEMM_QUICK_GELU, GEMM_GELU = 128, 256
 # step-table columns
 ST_TIMESTEP, ST_IN_SCALE, ST_K1, ST_K2, ST_CX, ST_CE, ST_C0, ST_C1, ST_GUIDANCE = range(9)
-ST_CN, ST_H1, ST_H2, ST_H3, ST_FLAGS = 9, 10, 11, 12, 13
+ST_CN, ST_H1, ST_H2, ST_H3, ST_FLAGS, ST_BA, ST_BS = 9, 10, 11, 12, 13, 14, 15
 STF_PUSH_EPS, STF_SAVE_X, STF_USE_SAVED_X = 1, 2, 4
 
 ERR_INVALID, ERR_CUDA, ERR_NO_DEVICE, ERR_UNSUPPORTED = -1, -2, -3, -4
@@ -128,6 +128,7 @@ class CfgStep(C.Structure):
         ("guidance_scale", C.c_float), ("cfg", C.c_int32), ("x_dtype", C.c_int32), ("B", C.c_int32), ("C", C.c_int32),
         ("hw", C.c_int32), ("Cpad", C.c_int32), ("rep", C.c_int32), ("nsteps", C.c_int32), ("gs_from_table", C.c_int32),
         ("noise", C.c_void_p), ("eps_hist", C.c_void_p), ("x_saved", C.c_void_p),
+        ("blend_mask", C.c_void_p), ("blend_image", C.c_void_p), ("blend_noise", C.c_void_p),
     ]
 
 

@@ -506,6 +506,7 @@ struct CSParams {
   const bf16* eps; long long ld_eps; const void* x; void* x_out; float* x0_prev; bf16* next_in;
   const float* table; const int* counter; float gs; int cfg, x_dtype, B, C, hw, Cpad, rep, nsteps, gs_from_table;
   const float* noise; float* eps_hist; float* x_saved;
+  const float* blend_mask; const float* blend_image; const float* blend_noise;
 };
 __global__ void cfg_step_kernel(const CSParams p) {
   pdl_launch_dependents();
@@ -550,6 +551,11 @@ __global__ void cfg_step_kernel(const CSParams p) {
       }
     }
     if (p.x_saved && (flags & B200SD_STF_SAVE_X)) p.x_saved[xi] = x_now;
+    if (p.blend_mask) {  // inpainting: outside the mask the latents are the original image re-noised to the next level
+      const float m = p.blend_mask[static_cast<long long>(b) * p.hw + pix];
+      const float proper = row[B200SD_ST_BA] * p.blend_image[xi] + row[B200SD_ST_BS] * p.blend_noise[xi];
+      xn = (1.0f - m) * proper + m * xn;
+    }
     store_from_float(p.x_out, xi, p.x_dtype, xn);
     if (p.next_in) {
       // the UNet consumes the value the pipeline would hand it: latents in their storage dtype, scaled
@@ -815,9 +821,10 @@ int plan_cfg_step(const b200sd_cfg_step& g, PlannedOp* out) {
   B200SD_CHECK_ARG(g.eps && g.x && g.x_out && g.step_table && g.step_counter && dtype_ok(g.x_dtype), "cfg_step: bad pointers/dtype");
   B200SD_CHECK_ARG(g.B >= 1 && g.C >= 1 && g.hw >= 1 && g.ld_eps >= g.C && g.nsteps >= 1, "cfg_step: bad shape");
   B200SD_CHECK_ARG(!g.next_in || (g.Cpad >= g.C && g.rep >= 1), "cfg_step: next_in needs Cpad/rep");
+  B200SD_CHECK_ARG(!g.blend_mask || (g.blend_image && g.blend_noise), "cfg_step: the inpaint blend needs mask, image latents and noise");
   CSParams p{static_cast<const bf16*>(g.eps), g.ld_eps, g.x, g.x_out, g.x0_prev, static_cast<bf16*>(g.next_in),
              g.step_table, g.step_counter, g.guidance_scale, g.cfg, g.x_dtype, g.B, g.C, g.hw, g.Cpad, g.rep, g.nsteps, g.gs_from_table,
-             g.noise, g.eps_hist, g.x_saved};
+             g.noise, g.eps_hist, g.x_saved, g.blend_mask, g.blend_image, g.blend_noise};
   return finish_plan(out, B200SD_OP_CFG_STEP, p, launch_cfg_step);
 }
 

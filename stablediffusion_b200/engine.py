@@ -32,7 +32,7 @@ MAX_STEPS = 1000
 class DenoiseEngine:
     def __init__(self, unet: B200UNet, B: int, h: int, w: int, do_cfg: bool, ctx_dim: int, uses_history: bool,
                  pair_group=None, pair_rank: int = 0, use_graph: bool = True, eps_history: bool = False,
-                 noise_steps: int = 0):
+                 noise_steps: int = 0, blend: bool = False):
         if unet.packed is None:
             raise RuntimeError("UNet has no weights on a CUDA device")
         self.unet, self.B, self.h, self.w, self.do_cfg = unet, B, h, w, do_cfg
@@ -62,6 +62,9 @@ class DenoiseEngine:
         self.eps_hist = pre.zeros([3, B, C, h * w], torch.float32) if eps_history else None
         self.x_saved = pre.zeros([B, C, h * w], torch.float32) if eps_history else None
         self.noise = pre.zeros([noise_steps, B, C, h * w], torch.float32) if noise_steps > 0 else None
+        # inpainting (pipeline :492-506): mask (1 = repaint), latents of the original image, the start noise
+        self.blend = (pre.zeros([B, h * w], torch.float32), pre.zeros([B, C, h * w], torch.float32),
+                      pre.zeros([B, C, h * w], torch.float32)) if blend else None
         pre.prep_latents(self.latents, self.unet_in_full, rep=rep_total, step_table=self.table, step_counter=self.counter)
         self.prep = pre
 
@@ -95,7 +98,7 @@ class DenoiseEngine:
     def _emit_tail(self, b: L.Builder, eps):
         b.cfg_step(eps, self.latents, self.latents, self.table, self.counter, 1.0, self.do_cfg, MAX_STEPS,
                    x0_prev=self.hist, next_in=self.unet_in_full, rep=2 if self.do_cfg else 1, gs_from_table=True,
-                   noise=self.noise, eps_hist=self.eps_hist, x_saved=self.x_saved)
+                   noise=self.noise, eps_hist=self.eps_hist, x_saved=self.x_saved, blend=self.blend)
         b.step_advance(self.counter)
 
     @property
@@ -104,7 +107,7 @@ class DenoiseEngine:
 
     # ---- one trajectory ---------------------------------------------------------------------------------
     def load(self, latents, prompt_embeds, step_rows: torch.Tensor, guidance_scale: float, text_embeds=None, time_ids=None,
-             generator=None):
+             generator=None, inpaint=None):
         """Stage one request: latents (any float dtype, NCHW), context embeddings, the scheduler's table rows.
         `generator`: device RNG the per-step noise of a stochastic sampler is drawn from (None: the global one, which
         is what the reference's `scheduler.step(noise_pred, t, latents)` uses, pipeline :489)."""
@@ -120,6 +123,11 @@ class DenoiseEngine:
             raise ValueError("this sampler needs per-step noise: build the engine with noise_steps > 0")
         if self.eps_hist is not None:
             self.eps_hist.zero_()
+        if (self.blend is None) != (inpaint is None):
+            raise ValueError("inpaint inputs and an engine built with blend=True go together")
+        if inpaint is not None:  # (mask [B,1,h,w] in {0,1}, image latents [B,C,h,w], start noise [B,C,h,w])
+            for dst, src in zip(self.blend, inpaint):
+                dst.copy_(src.reshape(dst.shape))
         rows = step_rows.clone()
         rows[:, N.ST_GUIDANCE] = float(guidance_scale)
         rows[0, N.ST_C1] = 0.0  # a multistep solver has no history on the first executed step (img2img starts mid-table)

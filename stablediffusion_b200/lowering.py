@@ -325,7 +325,7 @@ class Builder:
         return out
 
     def cfg_step(self, eps, x, x_out, step_table, step_counter, guidance_scale, cfg, nsteps, x0_prev=None, next_in=None, rep=2,
-                 gs_from_table=False, noise=None, eps_hist=None, x_saved=None):
+                 gs_from_table=False, noise=None, eps_hist=None, x_saved=None, blend=None):
         B, Cc, h, w = x.shape
         p = N.CfgStep()
         p.eps, p.ld_eps = eps.data_ptr(), eps.shape[-1]
@@ -339,6 +339,12 @@ class Builder:
             if t is not None and (t.dtype != torch.float32 or not t.is_contiguous()):
                 raise ValueError("cfg_step: noise / eps_hist / x_saved must be contiguous fp32")
         p.noise, p.eps_hist, p.x_saved = ptr(noise), ptr(eps_hist), ptr(x_saved)
+        if blend is not None:  # (mask [B, hw], image latents [B, C, hw], start noise [B, C, hw]), all fp32
+            for t in blend:
+                if t.dtype != torch.float32 or not t.is_contiguous():
+                    raise ValueError("cfg_step: blend tensors must be contiguous fp32")
+            p.blend_mask, p.blend_image, p.blend_noise = (t.data_ptr() for t in blend)
+            self.prog.keep(*blend)
         self.prog.add(N.OP_CFG_STEP, p, self.tag, (eps, x, x_out, step_table, step_counter, x0_prev, next_in, noise, eps_hist, x_saved))
         return x_out
 

@@ -67,6 +67,24 @@ class _ImageProcessor:
         x = torch.from_numpy(np.stack(arrs)).permute(0, 3, 1, 2)
         return 2.0 * x - 1.0 if self.do_normalize else x
 
+    def preprocess_mask(self, mask, height=None, width=None):
+        """`mask_processor.preprocess` (pipeline :283-285; VaeImageProcessor(do_normalize=False, do_binarize=True,
+        do_convert_grayscale=True)): one channel in {0, 1}, 1 = repaint, resized (nearest) to (height, width)."""
+        import numpy as np
+
+        if isinstance(mask, torch.Tensor):
+            x = mask.float()
+            while x.dim() < 4:
+                x = x[None]
+            if x.shape[1] != 1:
+                x = x.mean(dim=1, keepdim=True)
+        else:
+            masks = mask if isinstance(mask, list) else [mask]
+            x = torch.from_numpy(np.stack([np.asarray(mm.convert("L"), dtype=np.float32) / 255.0 for mm in masks]))[:, None]
+        if height is not None and width is not None and tuple(x.shape[-2:]) != (height, width):
+            x = torch.nn.functional.interpolate(x, size=(height, width))
+        return (x >= 0.5).float()
+
 
 def _is_hf_clip(enc) -> bool:
     return type(enc).__name__ in ("CLIPTextModel", "CLIPTextModelWithProjection") and hasattr(enc, "state_dict")

@@ -10,7 +10,8 @@ Reference quirks kept on purpose: D3 (`output_type` argument ign
 D4 (`guidance_rescale` accepted and ignored), D5 (defaults 50 steps / guidance 5.0), D7 (img2img RNG order:
 VAE posterior sample first, then noise, same generator), D16 (image returned un-clamped in ~[-1,1]).
 Quirk D1/D2 (crashes with do_cfg=False / prompt=None) are fixed: `prompt_embeds=` may be passed directly,
-which the benchmark uses for synthetic prompts.  Inpainting (mask_image) is a "next" row.
+which the benchmark uses for synthetic prompts.  Inpainting (`mask_image`) runs the 4-channel blend of :492-506 inside
+the fused step kernel.
 """
 from __future__ import annotations
 
@@ -18,6 +19,7 @@ from typing import Any, Dict, List, Optional, Union
 
 import torch
 
+from .. import _native as N
 from ..engine import DenoiseEngine
 from ..schedulers import _SchedulerBase
 from ..unet import B200UNet, cfg_is_sdxl
@@ -57,17 +59,17 @@ class StableDiffusionUnifiedPipeline:
         if self.verbose:
             print(*a)
 
-    def _engine(self, B, h, w, ctx_dim, n_steps: int = 0) -> DenoiseEngine:
+    def _engine(self, B, h, w, ctx_dim, n_steps: int = 0, blend: bool = False) -> DenoiseEngine:
         m = self.model
         sch = m.scheduler
         noise_steps = (n_steps + 63) // 64 * 64 if sch._stochastic else 0  # capacity of the pre-drawn noise, in steps
         key = (id(m.base), id(m.base.packed), B, h, w, ctx_dim, self.do_classifier_free_guidance, sch._uses_history,
-               sch._uses_eps_history, noise_steps)
+               sch._uses_eps_history, noise_steps, blend)
         eng = self._engines.get(key)
         if eng is None:
             eng = DenoiseEngine(m.base, B, h, w, self.do_classifier_free_guidance, ctx_dim, sch._uses_history,
                                 pair_group=self.pair_group, pair_rank=self.pair_rank, use_graph=self.use_graph,
-                                eps_history=sch._uses_eps_history, noise_steps=noise_steps)
+                                eps_history=sch._uses_eps_history, noise_steps=noise_steps, blend=blend)
             self._engines = {k: v for k, v in self._engines.items() if k[1] == id(m.base.packed)}  # drop stale weights
             self._engines[key] = eng
         return eng
@@ -89,8 +91,8 @@ class StableDiffusionUnifiedPipeline:
             raise RuntimeError("StableDiffusionUnifiedPipeline(device=...) must be a CUDA device: there is no CPU path")
         if not isinstance(model.base, B200UNet) or not isinstance(model.vae, B200VAE) or not isinstance(model.scheduler, _SchedulerBase):
             raise TypeError("this pipeline drives B200UNet / B200VAE / B200 schedulers (stablediffusion_b200.models.SDModelWrapper)")
-        if mask_image is not None:
-            raise ValueError("inpainting is not on the B200 hot path yet (SURVEY §8f rank 3)")
+        if mask_image is not None and image is None:
+            raise ValueError("`mask_image` needs `image`")
         if model.device != self.device:
             model.to(self.device)
         self.model = model
@@ -119,9 +121,15 @@ class StableDiffusionUnifiedPipeline:
         # 3. timesteps
         timesteps, num_inference_steps = retrieve_timesteps(model.scheduler, num_inference_steps, self.device)
         start_index = 0
+        inpaint = None
         if image is None:
             shape = (n_img, model.base.config.in_channels, height // model.vae_scale_factor, width // model.vae_scale_factor)
             latents = self.prepare_latents_txt2img(shape, prompt_embeds.dtype, seed, latents)
+        elif mask_image is not None:
+            inpaint, latents, timesteps, num_inference_steps, start_index = self._prepare_inpaint(
+                image, mask_image, masked_image_latents, padding_mask_crop, height, width, num_inference_steps, strength,
+                denoising_start, n_img, prompt_embeds.dtype, seed, latents)
+            height, width = latents.shape[-2] * model.vae_scale_factor, latents.shape[-1] * model.vae_scale_factor
         else:
             image = model.image_processor.preprocess(image)
             timesteps, num_inference_steps = self.get_timesteps(
@@ -132,7 +140,7 @@ class StableDiffusionUnifiedPipeline:
             latents = self.prepare_latents_img2img(image, latent_timestep, batch_size, num_images_per_prompt,
                                                    prompt_embeds.dtype, seed, add_noise)
             height, width = latents.shape[-2] * model.vae_scale_factor, latents.shape[-1] * model.vae_scale_factor
-        self.is_inpaint = False
+        self.is_inpaint = inpaint is not None
 
         # 9.1 denoising_end (reference :384-403)
         if (denoising_end is not None and denoising_start is not None and denoising_value_valid(denoising_end)
@@ -145,11 +153,75 @@ class StableDiffusionUnifiedPipeline:
             timesteps = timesteps[:num_inference_steps]
         return self._denoise_and_decode(latents, timesteps, start_index, prompt_embeds, negative_prompt_embeds,
                                         pooled_prompt_embeds, negative_pooled_prompt_embeds, guidance_scale, height, width,
-                                        n_img, sdxl)
+                                        n_img, sdxl, inpaint)
+
+    def _prepare_inpaint(self, image, mask_image, masked_image_latents, padding_mask_crop, height, width,
+                         num_inference_steps, strength, denoising_start, n_img, dtype, seed, latents):
+        """reference :266-380 for a 4-channel UNet (the only inpainting mode the reference's loop implements: it never
+        concatenates mask / masked-image latents to the UNet input, :465-482).  Returns the blend inputs of :492-506."""
+        m = self.model
+        if padding_mask_crop is not None:
+            raise ValueError("padding_mask_crop is not supported on the B200 path")
+        if m.base.config.in_channels != 4:
+            raise ValueError(f"The unet {m.base.__class__} should have 4 input channels for inpainting on this path, "
+                             f"not {m.base.config.in_channels}.")
+        init_image = m.image_processor.preprocess(image, height=height, width=width).to(dtype=torch.float32)
+        mask = m.mask_processor.preprocess_mask(mask_image, height=height, width=width)
+        timesteps, num_inference_steps = self.get_timesteps(
+            num_inference_steps, strength, denoising_start if denoising_value_valid(denoising_start) else None)
+        if num_inference_steps < 1:
+            raise ValueError(f"After adjusting the num_inference_steps by strength parameter: {strength}, the number of pipeline"
+                             f"steps is {num_inference_steps} which is < 1 and not appropriate for this pipeline.")
+        start_index = len(m.scheduler.timesteps) - len(timesteps)
+        latent_timestep = timesteps[:1].repeat(n_img)
+        f = m.vae_scale_factor
+        shape = (n_img, m.vae.config.latent_channels, height // f, width // f)
+        latents, noise, image_latents = self.prepare_latents_inpaint(
+            shape, dtype, seed, latents, image=init_image, timestep=latent_timestep, is_strength_max=strength == 1.0,
+            add_noise=denoising_start is None)
+        # prepare_mask_latents (:916-976): the mask at latent resolution (F.interpolate's default: nearest), per image
+        mask = torch.nn.functional.interpolate(mask.float(), size=(height // f, width // f)).to(self.device)
+        if mask.shape[0] < n_img:
+            if n_img % mask.shape[0] != 0:
+                raise ValueError("The passed mask and the required batch size don't match. Masks are supposed to be duplicated to"
+                                 f" a total batch size of {n_img}, but {mask.shape[0]} masks were passed. Make sure the number"
+                                 " of masks that you pass is divisible by the total requested batch size.")
+            mask = mask.repeat(n_img // mask.shape[0], 1, 1, 1)
+        return (mask, image_latents.float(), noise.float()), latents, timesteps, num_inference_steps, start_index
+
+    def prepare_latents_inpaint(self, shape, dtype, seed=None, latents=None, image=None, timestep=None,
+                                is_strength_max=True, add_noise=True):
+        """reference :848-913 with return_noise = return_image_latents = True (RNG order: VAE posterior, then noise)."""
+        batch_size = shape[0]
+        generator = None
+        if seed is not None:
+            generator = torch.Generator(device=self.device).manual_seed(int(seed))
+        if (image is None or timestep is None) and not is_strength_max:
+            raise ValueError("Since strength < 1. initial latents are to be initialised as a combination of Image + Noise."
+                             "However, either the image or the noise timestep has not been provided.")
+        if image.shape[1] == 4:
+            image_latents = image.to(device=self.device, dtype=dtype)
+        else:
+            image_latents = self._encode_vae_image(image.to(device=self.device, dtype=dtype), generator)
+        image_latents = image_latents.repeat(batch_size // image_latents.shape[0], 1, 1, 1)
+        sigma0 = float(self.model.scheduler.init_noise_sigma)
+        if latents is None and add_noise:
+            noise = torch.randn(shape, generator=generator, device=self.device, dtype=dtype)
+            if is_strength_max:
+                latents = noise.float() * sigma0
+            else:
+                latents = self.model.scheduler.add_noise(image_latents.float(), noise.float(), timestep)
+        elif add_noise:
+            noise = latents.to(self.device)
+            latents = noise.float() * sigma0
+        else:
+            noise = torch.randn(shape, generator=generator, device=self.device, dtype=dtype)
+            latents = image_latents
+        return latents.float(), noise, image_latents
 
     # ---- the hot path: loop (:465-506) + un-scale (:511-521) + decode (:523) --------------------------------
     def _denoise_and_decode(self, latents, timesteps, start_index, prompt_embeds, negative_prompt_embeds, pooled,
-                            negative_pooled, guidance_scale, height, width, n_img, sdxl):
+                            negative_pooled, guidance_scale, height, width, n_img, sdxl, inpaint=None):
         m = self.model
         cfg = self.do_classifier_free_guidance
         text_embeds = time_ids = None
@@ -170,9 +242,15 @@ class StableDiffusionUnifiedPipeline:
 
         B, _, h, w = latents.shape
         n = len(timesteps)
-        eng = self._engine(B, h, w, prompt_embeds.shape[-1], n)
+        eng = self._engine(B, h, w, prompt_embeds.shape[-1], n, blend=inpaint is not None)
         rows = m.scheduler.rows_for(start_index, n)
-        eng.load(latents, prompt_embeds, rows, guidance_scale, text_embeds, time_ids, generator=self._step_generator)
+        if inpaint is not None:  # re-noising level of the kept region after step i: the NEXT timestep's (:499-504)
+            rows = rows.clone()
+            for i in range(n):
+                a, s_ = m.scheduler.noise_coeffs(timesteps[i + 1]) if i < n - 1 else (1.0, 0.0)
+                rows[i, N.ST_BA], rows[i, N.ST_BS] = a, s_
+        eng.load(latents, prompt_embeds, rows, guidance_scale, text_embeds, time_ids, generator=self._step_generator,
+                 inpaint=inpaint)
         out = eng.run(n)
         self.last_engine = eng
 

@@ -166,6 +166,17 @@ class _SchedulerBase:
         """Host table rows of the n steps executed from `start_index` (img2img starts mid-schedule)."""
         return self._table[start_index:start_index + n]
 
+    def noise_coeffs(self, timestep):
+        """(a, s) of `add_noise`: x_t = a * x_0 + s * noise at `timestep` (also the inpaint blend's re-noising, :499-504)."""
+        raise NotImplementedError
+
+    def add_noise(self, original_samples, noise, timesteps):
+        ts = set(float(t) for t in timesteps.reshape(-1).tolist())
+        if len(ts) != 1:
+            raise ValueError("add_noise: per-sample timesteps must be equal on this path")
+        a, s_ = self.noise_coeffs(ts.pop())
+        return self._elementwise(original_samples, float(a), noise, float(s_))
+
     _uses_eps_history = False   # PNDM / PLMS: eps history + remembered sample
     _stochastic = False         # the update has a noise term (ancestral / SDE samplers)
     _uses_history = False
@@ -228,11 +239,8 @@ class B200EulerDiscreteScheduler(_SchedulerBase):
         s = self.sigmas[self._step_index]
         return self._elementwise(sample, float(1.0 / ((s ** 2 + 1) ** 0.5)))
 
-    def add_noise(self, original_samples, noise, timesteps):
-        idx = [self.index_for_timestep(t) for t in timesteps.reshape(-1).tolist()]
-        if len(set(idx)) != 1:
-            raise ValueError("add_noise: per-sample timesteps must be equal on this path")
-        return self._elementwise(original_samples, 1.0, noise, float(self.sigmas[idx[0]]))
+    def noise_coeffs(self, timestep):
+        return 1.0, float(self.sigmas[self.index_for_timestep(timestep)])
 
 
 class B200DDIMScheduler(_SchedulerBase):
@@ -283,12 +291,9 @@ class B200DDIMScheduler(_SchedulerBase):
             tab[i, N.ST_C0] = a_p ** 0.5
         return tab
 
-    def add_noise(self, original_samples, noise, timesteps):
-        ts = set(int(t) for t in timesteps.reshape(-1).tolist())
-        if len(ts) != 1:
-            raise ValueError("add_noise: per-sample timesteps must be equal on this path")
-        a = self.alphas_cumprod[ts.pop()]
-        return self._elementwise(original_samples, float(a ** 0.5), noise, float((1 - a) ** 0.5))
+    def noise_coeffs(self, timestep):
+        a = self.alphas_cumprod[int(timestep)]
+        return float(a ** 0.5), float((1 - a) ** 0.5)
 
 
 class B200DPMSolverMultistepScheduler(_SchedulerBase):
@@ -368,12 +373,9 @@ class B200DPMSolverMultistepScheduler(_SchedulerBase):
                 tab[i, N.ST_C1] = -0.5 * coef * (1.0 / r0)
         return tab
 
-    def add_noise(self, original_samples, noise, timesteps):
-        idx = [self.index_for_timestep(t) for t in timesteps.reshape(-1).tolist()]
-        if len(set(idx)) != 1:
-            raise ValueError("add_noise: per-sample timesteps must be equal on this path")
-        a, s = self._alpha_sigma(self.sigmas[idx[0]])
-        return self._elementwise(original_samples, float(a), noise, float(s))
+    def noise_coeffs(self, timestep):
+        a, s = self._alpha_sigma(self.sigmas[self.index_for_timestep(timestep)])
+        return float(a), float(s)
 
 
 class B200EulerAncestralDiscreteScheduler(B200EulerDiscreteScheduler):
@@ -536,12 +538,9 @@ class B200PNDMScheduler(_SchedulerBase):
     def _unfused_counter(self) -> int:
         return self._step_index - self._start
 
-    def add_noise(self, original_samples, noise, timesteps):
-        ts = set(int(t) for t in timesteps.reshape(-1).tolist())
-        if len(ts) != 1:
-            raise ValueError("add_noise: per-sample timesteps must be equal on this path")
-        a = self.alphas_cumprod[ts.pop()]
-        return self._elementwise(original_samples, float(a ** 0.5), noise, float((1 - a) ** 0.5))
+    def noise_coeffs(self, timestep):
+        a = self.alphas_cumprod[int(timestep)]
+        return float(a ** 0.5), float((1 - a) ** 0.5)
 
 
 SCHEDULER_CLASSES = {

@@ -285,3 +285,54 @@ def test_pipeline_sd15_txt2img_20_euler(cuda_device):
     psnr = _psnr(img, ref, peak=(ref.max() - ref.min()).item())
     print(f"E2E SD1.5 20 Euler: latent rel-L2 {_rel_l2(lat_ours, zl.cpu()):.4g}, image PSNR {psnr:.1f} dB, launches/step {pipe.last_engine.launches_per_step}")
     assert torch.isfinite(img).all() and psnr >= 30.0
+
+
+@pytest.mark.parametrize("sched_name,strength", [("euler", 1.0), ("DDIM", 0.6), ("DPM++ 2M", 0.75), ("PNDM", 1.0), ("euler_a", 0.5)])
+def test_inpaint_loop_vs_oracle(cuda_device, sched_name, strength):
+    """Third pipeline mode (reference :266-380, :492-506): 4-channel inpainting — the masked region is denoised, the rest
+    is re-noised original latents after every step.  `image` is passed in latent space (skips the VAE so that both sides
+    see the same image latents); the mask is given at pixel resolution and down-sampled (nearest) by the pipeline."""
+    from oracle import pipeline as OP
+    from oracle import schedulers as OS
+    from stablediffusion_b200.models.stable_diffusion import SDModelWrapper
+    from stablediffusion_b200.pipelines.sd_unified_pipeline import StableDiffusionUnifiedPipeline
+
+    dev = cuda_device
+    cfg, ours, oracle = _make_unet(dev, **SMALL_UNET)
+    vcfg, vae, _ = _make_vae(dev)
+    model = SDModelWrapper(vae=vae, base=ours, device=str(dev))
+    model.set_scheduler(sched_name)
+    g = torch.Generator().manual_seed(31)
+    B, steps = 2, 10
+    # (the pipeline casts the image latents to the prompt-embedding dtype, reference :872: use bf16-exact values)
+    image_latents = torch.randn(B, 4, 16, 16, generator=g).bfloat16().float()
+    noise = torch.randn(B, 4, 16, 16, generator=g)
+    pe = torch.randn(B, 77, 64, generator=g).to(torch.bfloat16)
+    ne = torch.randn(B, 77, 64, generator=g).to(torch.bfloat16)
+    mask_px = torch.zeros(1, 1, 128, 128)
+    mask_px[:, :, 32:100, 20:90] = 1.0
+    pipe = StableDiffusionUnifiedPipeline(do_cfg=True, device=str(dev), output_type="latents")
+    step_noise = None
+    osched = OS.make_scheduler(sched_name, dict(OS.SD15_SCHEDULER_CONFIG))
+    osched.set_timesteps(steps)
+    init_t = min(int(steps * strength), steps)
+    ts = osched.timesteps[max(steps - init_t, 0) * osched.order:]
+    if sched_name in OS.STOCHASTIC:
+        pipe._step_generator = torch.Generator(device=dev).manual_seed(78)
+        step_noise = torch.randn((len(ts), B, 4, 256), generator=torch.Generator(device=dev).manual_seed(78), device=dev,
+                                 dtype=torch.float32).view(len(ts), B, 4, 16, 16).cpu()
+    out = pipe(model, prompt_embeds=pe.to(dev), negative_prompt_embeds=ne.to(dev), num_inference_steps=steps,
+               guidance_scale=6.0, latents=noise.to(dev), image=image_latents.to(dev), mask_image=mask_px, strength=strength,
+               height=128, width=128).float().cpu()
+    assert pipe.is_inpaint
+    # oracle: reference :848-913 with `latents` given -> noise = latents, start = noise * init_noise_sigma
+    x0 = noise * float(osched.init_noise_sigma)
+    m = torch.nn.functional.interpolate(mask_px, size=(16, 16)).repeat(B, 1, 1, 1)
+    ref = OP.denoise(oracle.cpu(), osched, x0, torch.cat([ne, pe]).float(), ts, 6.0, step_noise=step_noise,
+                     inpaint=(m, image_latents, noise))
+    rl2 = _rel_l2(out, ref)
+    print(f"INPAINT PARITY {sched_name} strength {strength}: rel-L2 {rl2:.4g}")
+    assert torch.isfinite(out).all() and rl2 <= 5e-2
+    # outside the mask the result IS the original image latents (last step: no re-noising)
+    keep = (m == 0).expand_as(out)
+    torch.testing.assert_close(out[keep], image_latents[keep], rtol=1e-6, atol=1e-6)
