@@ -192,7 +192,14 @@ enum { /* columns of one step-table row */
 enum {
   B200SD_STF_PUSH_EPS = 1,   /* after the update: e[-3] <- e[-2] <- e[-1] <- eps                                */
   B200SD_STF_SAVE_X = 2,     /* remember the sample the step started from (PNDM `cur_sample`)                   */
-  B200SD_STF_USE_SAVED_X = 4 /* update the remembered sample instead of the current one (PNDM counter == 1)     */
+  B200SD_STF_USE_SAVED_X = 4, /* update the remembered sample instead of the current one (PNDM counter == 1)    */
+  /* UniPC (predictor-corrector, order <= 2).  With this bit the row is read as
+   *   x0 = (x - K1*eps)*K2
+   *   xc = CORRECT ? H1*x_saved + H2*x0_prev + H3*(eps_hist[0] - x0_prev) + CE*(x0 - x0_prev) : x      (UniC)
+   *   x' = CX*xc + C0*x0 + C1*(x0 - x0_prev)                                                            (UniP)
+   *   x_saved <- xc ; eps_hist[0] <- x0_prev ; x0_prev <- x0          (eps_hist[0] holds the x0 before last) */
+  B200SD_STF_UNIPC = 8,
+  B200SD_STF_UNIPC_CORRECT = 16
 };
 
 typedef struct b200sd_timestep_embed {

@@ -360,11 +360,103 @@ class PNDMOracle(_Base):
         return a ** 0.5 * x0 + (1 - a) ** 0.5 * noise
 
 
+class UniPCOracle(DPMSolverMultistepOracle):
+    """UniPCMultistepScheduler (`uni_pc`, models/stable_diffusion.py:221-222), class defaults: solver_order 2, bh2,
+    predict_x0, lower_order_final, corrector on every step after the first, final sigma zero.  Restated in diffusers'
+    structure: `step` = [UniC on the incoming sample] -> shift the x0 history -> UniP."""
+
+    def set_timesteps(self, n, device=None):
+        super().set_timesteps(n, device)
+        self.model_outputs = [None, None]
+        self.lower_order_nums = 0
+        self.last_sample = None
+        self.this_order = None
+
+    def _lam(self, sigma):
+        a, s = self._alpha_sigma(sigma)
+        return a, s, torch.log(a) - torch.log(s)
+
+    def _b_coeffs(self, hh, order):
+        h_phi_1 = torch.expm1(hh)
+        B_h = torch.expm1(hh)  # bh2
+        h_phi_k = h_phi_1 / hh - 1
+        factorial_i = 1
+        b = []
+        for i in range(1, order + 1):
+            b.append(h_phi_k * factorial_i / B_h)
+            factorial_i *= i + 1
+            h_phi_k = h_phi_k / hh - 1 / factorial_i
+        return h_phi_1, B_h, torch.stack(b)
+
+    def _uni_p(self, sample, order):
+        m0 = self.model_outputs[-1]
+        x = sample
+        a_t, s_t, lam_t = self._lam(self.sigmas[self.step_index + 1])
+        a_s0, s_s0, lam_s0 = self._lam(self.sigmas[self.step_index])
+        h = lam_t - lam_s0
+        rks, D1s = [], []
+        for i in range(1, order):
+            si = self.step_index - i
+            mi = self.model_outputs[-(i + 1)]
+            _, _, lam_si = self._lam(self.sigmas[si])
+            rk = (lam_si - lam_s0) / h
+            rks.append(rk)
+            D1s.append((mi - m0) / rk)
+        h_phi_1, B_h, b = self._b_coeffs(-h, order)
+        x_t_ = s_t / s_s0 * x - a_t * h_phi_1 * m0
+        pred_res = 0.5 * D1s[0] if D1s else 0  # order 2: rhos_p = [0.5]
+        return x_t_ - a_t * B_h * pred_res
+
+    def _uni_c(self, this_model_output, last_sample, order):
+        m0 = self.model_outputs[-1]
+        x = last_sample
+        model_t = this_model_output
+        a_t, s_t, lam_t = self._lam(self.sigmas[self.step_index])
+        a_s0, s_s0, lam_s0 = self._lam(self.sigmas[self.step_index - 1])
+        h = lam_t - lam_s0
+        rks, D1s = [], []
+        for i in range(1, order):
+            si = self.step_index - (i + 1)
+            mi = self.model_outputs[-(i + 1)]
+            _, _, lam_si = self._lam(self.sigmas[si])
+            rk = (lam_si - lam_s0) / h
+            rks.append(rk)
+            D1s.append((mi - m0) / rk)
+        rks.append(torch.tensor(1.0))
+        rks = torch.stack(rks)
+        h_phi_1, B_h, b = self._b_coeffs(-h, order)
+        R = torch.stack([torch.pow(rks, i - 1) for i in range(1, order + 1)])
+        rhos_c = torch.tensor([0.5]) if order == 1 else torch.linalg.solve(R, b)
+        x_t_ = s_t / s_s0 * x - a_t * h_phi_1 * m0
+        corr_res = sum(rhos_c[k] * D1s[k] for k in range(len(D1s))) if D1s else 0
+        D1_t = model_t - m0
+        return x_t_ - a_t * B_h * (corr_res + rhos_c[-1] * D1_t)
+
+    def step(self, eps, t, x):
+        self._init_step_index(t)
+        i = self.step_index
+        x = x.to(torch.float32)
+        use_corrector = i > 0 and self.last_sample is not None
+        a_s, s_s = self._alpha_sigma(self.sigmas[i])
+        x0 = (x - s_s * eps) / a_s                                   # convert_model_output (epsilon, predict_x0)
+        if use_corrector:
+            x = self._uni_c(x0, self.last_sample, self.this_order)
+        self.model_outputs = [self.model_outputs[1], x0]
+        this_order = min(2, len(self.timesteps) - i)                 # lower_order_final
+        self.this_order = min(this_order, self.lower_order_nums + 1)  # warm-up
+        self.last_sample = x
+        out = self._uni_p(x, self.this_order)
+        if self.lower_order_nums < 2:
+            self.lower_order_nums += 1
+        self.step_index += 1
+        return out
+
+
 STOCHASTIC = ("euler_a", "DPM++ 2M SDE Karras")
 
 
 def make_scheduler(name: str, config: dict):
-    """Name table of models/stable_diffusion.py:205-222 (all but uni_pc)."""
+    """Name table of models/stable_diffusion.py:205-222."""
     if name == "euler":
         return EulerDiscreteOracle(**config)
     if name == "DDIM":
@@ -379,4 +471,6 @@ def make_scheduler(name: str, config: dict):
         return DPMSolverSDEOracle(**config)
     if name == "PNDM":
         return PNDMOracle(**config)
+    if name == "uni_pc":
+        return UniPCOracle(**config)
     raise ValueError(f"Unknown scheduler name: {name}")

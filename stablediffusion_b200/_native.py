@@ -37,7 +37,7 @@ GEMM_QUICK_GELU, GEMM_GELU = 128, 256
 # step-table columns
 ST_TIMESTEP, ST_IN_SCALE, ST_K1, ST_K2, ST_CX, ST_CE, ST_C0, ST_C1, ST_GUIDANCE = range(9)
 ST_CN, ST_H1, ST_H2, ST_H3, ST_FLAGS, ST_BA, ST_BS = 9, 10, 11, 12, 13, 14, 15
-STF_PUSH_EPS, STF_SAVE_X, STF_USE_SAVED_X = 1, 2, 4
+STF_PUSH_EPS, STF_SAVE_X, STF_USE_SAVED_X, STF_UNIPC, STF_UNIPC_CORRECT = 1, 2, 4, 8, 16
 
 ERR_INVALID, ERR_CUDA, ERR_NO_DEVICE, ERR_UNSUPPORTED = -1, -2, -3, -4
 

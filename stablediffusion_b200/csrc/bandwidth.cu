@@ -533,24 +533,37 @@ __global__ void cfg_step_kernel(const CSParams p) {
     if (p.cfg) e = gs * (__bfloat162float(ec[c]) - u) + u;
     const long long xi = (static_cast<long long>(b) * p.C + c) * p.hw + pix;
     const float x_now = load_as_float(p.x, xi, p.x_dtype);
-    const float x = (p.x_saved && (flags & B200SD_STF_USE_SAVED_X)) ? p.x_saved[xi] : x_now;
-    const float x0 = (x - K1 * e) * K2;
-    float xn = CX * x + CE * e + C0 * x0;
-    if (p.x0_prev) {
-      if (C1 != 0.f) xn += C1 * (x0 - p.x0_prev[xi]);
+    float xn;
+    if (flags & B200SD_STF_UNIPC) {  // UniPC: correct the incoming (predicted) sample, then predict the next one
+      if (!p.x0_prev || !p.eps_hist || !p.x_saved) __trap();
+      const float x0 = (x_now - K1 * e) * K2;
+      const float m1 = p.x0_prev[xi], m2 = p.eps_hist[xi];
+      float xc = x_now;
+      if (flags & B200SD_STF_UNIPC_CORRECT) xc = H1 * p.x_saved[xi] + H2 * m1 + H3 * (m2 - m1) + CE * (x0 - m1);
+      xn = CX * xc + C0 * x0 + C1 * (x0 - m1);
+      p.x_saved[xi] = xc;
+      p.eps_hist[xi] = m1;
       p.x0_prev[xi] = x0;
-    }
-    if (CN != 0.f) xn += CN * p.noise[static_cast<long long>(step) * plane + xi];
-    if (p.eps_hist) {
-      const float h1 = p.eps_hist[xi], h2 = p.eps_hist[plane + xi], h3 = p.eps_hist[2 * plane + xi];
-      xn += H1 * h1 + H2 * h2 + H3 * h3;
-      if (flags & B200SD_STF_PUSH_EPS) {
-        p.eps_hist[2 * plane + xi] = h2;
-        p.eps_hist[plane + xi] = h1;
-        p.eps_hist[xi] = e;
+    } else {
+      const float x = (p.x_saved && (flags & B200SD_STF_USE_SAVED_X)) ? p.x_saved[xi] : x_now;
+      const float x0 = (x - K1 * e) * K2;
+      xn = CX * x + CE * e + C0 * x0;
+      if (p.x0_prev) {
+        if (C1 != 0.f) xn += C1 * (x0 - p.x0_prev[xi]);
+        p.x0_prev[xi] = x0;
       }
+      if (CN != 0.f) xn += CN * p.noise[static_cast<long long>(step) * plane + xi];
+      if (p.eps_hist) {
+        const float h1 = p.eps_hist[xi], h2 = p.eps_hist[plane + xi], h3 = p.eps_hist[2 * plane + xi];
+        xn += H1 * h1 + H2 * h2 + H3 * h3;
+        if (flags & B200SD_STF_PUSH_EPS) {
+          p.eps_hist[2 * plane + xi] = h2;
+          p.eps_hist[plane + xi] = h1;
+          p.eps_hist[xi] = e;
+        }
+      }
+      if (p.x_saved && (flags & B200SD_STF_SAVE_X)) p.x_saved[xi] = x_now;
     }
-    if (p.x_saved && (flags & B200SD_STF_SAVE_X)) p.x_saved[xi] = x_now;
     if (p.blend_mask) {  // inpainting: outside the mask the latents are the original image re-noised to the next level
       const float m = p.blend_mask[static_cast<long long>(b) * p.hw + pix];
       const float proper = row[B200SD_ST_BA] * p.blend_image[xi] + row[B200SD_ST_BS] * p.blend_noise[xi];
@@ -822,6 +835,7 @@ int plan_cfg_step(const b200sd_cfg_step& g, PlannedOp* out) {
   B200SD_CHECK_ARG(g.B >= 1 && g.C >= 1 && g.hw >= 1 && g.ld_eps >= g.C && g.nsteps >= 1, "cfg_step: bad shape");
   B200SD_CHECK_ARG(!g.next_in || (g.Cpad >= g.C && g.rep >= 1), "cfg_step: next_in needs Cpad/rep");
   B200SD_CHECK_ARG(!g.blend_mask || (g.blend_image && g.blend_noise), "cfg_step: the inpaint blend needs mask, image latents and noise");
+  // (a row with B200SD_STF_UNIPC needs x0_prev, eps_hist and x_saved: the kernel traps on a NULL one rather than corrupt memory)
   CSParams p{static_cast<const bf16*>(g.eps), g.ld_eps, g.x, g.x_out, g.x0_prev, static_cast<bf16*>(g.next_in),
              g.step_table, g.step_counter, g.guidance_scale, g.cfg, g.x_dtype, g.B, g.C, g.hw, g.Cpad, g.rep, g.nsteps, g.gs_from_table,
              g.noise, g.eps_hist, g.x_saved, g.blend_mask, g.blend_image, g.blend_noise};

@@ -543,6 +543,113 @@ class B200PNDMScheduler(_SchedulerBase):
         return float(a ** 0.5), float((1 - a) ** 0.5)
 
 
+class B200UniPCMultistepScheduler(B200DPMSolverMultistepScheduler):
+    """UniPCMultistepScheduler (name `uni_pc`, models/stable_diffusion.py:221-222): predictor-corrector of order 2
+    (bh2, predict_x0, lower_order_final), same timestep / sigma tables as DPM++ 2M.  Each call first CORRECTS the sample
+    it is handed (UniC, using the fresh model output), then predicts the next one (UniP) — both are linear in
+    {last corrected sample, the x0 predictions of this and the two previous calls}, so a row of coefficients drives the
+    step kernel (B200SD_STF_UNIPC)."""
+    _class_defaults = dict(timestep_spacing="linspace", solver_order=2, solver_type="bh2", predict_x0=True,
+                           lower_order_final=True, use_karras_sigmas=False, final_sigmas_type="zero", steps_offset=0,
+                           disable_corrector=[])
+    _uses_history = True
+    _uses_eps_history = True
+
+    def __init__(self, **config):
+        _SchedulerBase.__init__(self, **config)
+        c = self.config
+        if c["solver_order"] != 2 or c["solver_type"] != "bh2" or not c["predict_x0"] or not c["lower_order_final"]:
+            raise ValueError("UniPC: only order 2 / bh2 / predict_x0 / lower_order_final (the class defaults) are supported")
+        if c["timestep_spacing"] != "linspace" or c["final_sigmas_type"] != "zero" or c["disable_corrector"]:
+            raise ValueError("UniPC: only linspace spacing, final sigma zero and the corrector on every step are supported")
+
+    def _lam(self, sigma):
+        a, s = self._alpha_sigma(sigma)
+        return a, s, torch.log(a) - torch.log(s)
+
+    def _build_table(self):
+        return self._build_table_from(0)
+
+    def _build_table_from(self, start: int):
+        n_total = self.num_inference_steps
+        n = n_total - start
+        tab = torch.zeros(n, N.STEP_ROW, dtype=torch.float32)
+        prev_order = 0
+        for j in range(n):
+            i = start + j                                   # position in the schedule; j = call counter
+            a_s0, s_s0, lam_s0 = self._lam(self.sigmas[i])
+            a_t, s_t, lam_t = self._lam(self.sigmas[i + 1])
+            flags = N.STF_UNIPC
+            tab[j, N.ST_TIMESTEP] = float(self._timesteps_host[i])
+            tab[j, N.ST_IN_SCALE] = 1.0
+            tab[j, N.ST_K1], tab[j, N.ST_K2] = s_s0, 1.0 / a_s0
+            # ---- UniC: corrects the sample predicted by the previous call, order = that call's order ----
+            if j > 0:
+                q = prev_order
+                a_c, s_c, lam_c = a_s0, s_s0, lam_s0            # "t" of the corrector is the current position
+                a_p, s_p, lam_p = self._lam(self.sigmas[i - 1])  # its "s0" the previous one
+                h = lam_c - lam_p
+                hh = -h
+                h_phi_1 = torch.expm1(hh)
+                B_h = torch.expm1(hh)
+                h_phi_k = h_phi_1 / hh - 1
+                fact = 1
+                b = []
+                for k in range(1, q + 1):
+                    b.append(h_phi_k * fact / B_h)
+                    fact *= k + 1
+                    h_phi_k = h_phi_k / hh - 1 / fact
+                tab[j, N.ST_H1] = s_c / s_p
+                tab[j, N.ST_H2] = -a_c * h_phi_1
+                if q == 1:
+                    rho_t = torch.tensor(0.5)
+                else:
+                    _, _, lam_p2 = self._lam(self.sigmas[i - 2])
+                    rk = (lam_p2 - lam_p) / h
+                    R = torch.stack([torch.ones(2), torch.stack([rk, torch.tensor(1.0)])])
+                    rhos = torch.linalg.solve(R, torch.stack(b))
+                    tab[j, N.ST_H3] = -a_c * B_h * rhos[0] / rk
+                    rho_t = rhos[1]
+                tab[j, N.ST_CE] = -a_c * B_h * rho_t
+                flags |= N.STF_UNIPC_CORRECT
+            # ---- UniP: predicts the next sample ----
+            order = min(min(2, n_total - i), min(j, 2) + 1)
+            h = lam_t - lam_s0
+            hh = -h
+            h_phi_1 = torch.expm1(hh)
+            B_h = torch.expm1(hh)
+            tab[j, N.ST_CX] = s_t / s_s0
+            tab[j, N.ST_C0] = -a_t * h_phi_1
+            if order == 2:
+                _, _, lam_s1 = self._lam(self.sigmas[i - 1])
+                rk = (lam_s1 - lam_s0) / h
+                tab[j, N.ST_C1] = a_t * B_h * 0.5 / rk
+            tab[j, N.ST_FLAGS] = float(flags)
+            prev_order = order
+        return tab
+
+    def rows_for(self, start_index: int, n: int) -> torch.Tensor:
+        return self._build_table_from(start_index)[:n]
+
+    # un-fused calls: like PNDM, the warm-up follows the call counter
+    def _init_step_index(self, timestep):
+        if self._step_index is None:
+            self._step_index = self._start = self.index_for_timestep(timestep)
+            self._programs.clear()
+
+    def _unfused_table(self, dev):
+        key = f"unipc{self._start}@{dev}"
+        if key not in self._dev:
+            full = torch.zeros(len(self._table), N.STEP_ROW, dtype=torch.float32)
+            rows = self._build_table_from(self._start)
+            full[:len(rows)] = rows
+            self._dev[key] = full.to(dev)
+        return self._dev[key]
+
+    def _unfused_counter(self) -> int:
+        return self._step_index - self._start
+
+
 SCHEDULER_CLASSES = {
     "euler": (B200EulerDiscreteScheduler, {}),
     "DDIM": (B200DDIMScheduler, {}),
@@ -552,9 +659,10 @@ SCHEDULER_CLASSES = {
     # the reference's own spelling of the call, typo included (models/stable_diffusion.py:215-218)
     "DPM++ 2M SDE Karras": (B200DPMSolverSDEScheduler, dict(se_karras_sigmas=True, algorithm_type="sde-dpmsolver++")),
     "PNDM": (B200PNDMScheduler, {}),
+    "uni_pc": (B200UniPCMultistepScheduler, {}),
 }
-# names the reference accepts (models/stable_diffusion.py:205-222) that are not on the hot path yet
-NEXT_ROW_SCHEDULERS = ("uni_pc",)
+# every name the reference accepts (models/stable_diffusion.py:205-222) has a kernel path now
+NEXT_ROW_SCHEDULERS = ()
 
 
 def make_scheduler(name: str, config) -> _SchedulerBase:

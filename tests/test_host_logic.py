@@ -83,6 +83,15 @@ class _KernelState:
         xs = self.saved if (sched._uses_eps_history and flags & N.STF_USE_SAVED_X) else x
         x0 = (xs - g(N.ST_K1) * eps) * g(N.ST_K2)
         xn = g(N.ST_CX) * xs + g(N.ST_CE) * eps + g(N.ST_C0) * x0
+        if flags & N.STF_UNIPC:
+            x0 = (x - g(N.ST_K1) * eps) * g(N.ST_K2)
+            m1, m2 = self.hist, self.eh[0]
+            xc = x
+            if flags & N.STF_UNIPC_CORRECT:
+                xc = g(N.ST_H1) * self.saved + g(N.ST_H2) * m1 + g(N.ST_H3) * (m2 - m1) + g(N.ST_CE) * (x0 - m1)
+            xn = g(N.ST_CX) * xc + g(N.ST_C0) * x0 + g(N.ST_C1) * (x0 - m1)
+            self.saved, self.eh[0], self.hist = xc, m1, x0
+            return xn
         if sched._uses_history:
             if g(N.ST_C1) != 0:
                 xn = xn + g(N.ST_C1) * (x0 - self.hist)
@@ -99,7 +108,8 @@ class _KernelState:
 
 
 @pytest.mark.parametrize("name,n", [("euler_a", 20), ("euler_a", 1), ("DPM++ 2M SDE Karras", 20), ("DPM++ 2M SDE Karras", 2),
-                                    ("PNDM", 20), ("PNDM", 50), ("PNDM", 3), ("euler", 7), ("DPM++ 2M", 9)])
+                                    ("PNDM", 20), ("PNDM", 50), ("PNDM", 3), ("euler", 7), ("DPM++ 2M", 9),
+                                    ("uni_pc", 20), ("uni_pc", 50), ("uni_pc", 2), ("uni_pc", 1), ("uni_pc", 3)])
 def test_step_table_next_row_schedulers(name, n):
     """the table rows of euler_a / DPM++ 2M SDE / PNDM drive the kernel's linear form to the oracle's
     trajectory (PNDM: N + 1 evaluations, second timestep twice, averaged redo of the first step)."""
@@ -139,8 +149,8 @@ def test_from_config_uses_target_class_defaults():
     assert isinstance(m, B200DPMSolverMultistepScheduler) and m.config.use_karras_sigmas and m.config.beta_schedule == "scaled_linear"
     with pytest.raises(ValueError, match="Unknown scheduler name"):
         make_scheduler("nope", e.config)
-    with pytest.raises(ValueError, match="no B200 kernel yet"):
-        make_scheduler("uni_pc", e.config)                       # the one remaining 'next' row: fails loudly, no CPU fallback
+    for name in ("euler", "euler_a", "DDIM", "DPM++ 2M", "DPM++ 2M Karras", "DPM++ 2M SDE Karras", "PNDM", "uni_pc"):
+        make_scheduler(name, e.config)                           # the whole name table of the reference (:205-222)
 
 
 def test_geglu_interleave_and_conv_packing():

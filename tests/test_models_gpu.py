@@ -156,7 +156,7 @@ def test_vae_encode_vs_oracle(cuda_device):
 
 
 @pytest.mark.parametrize("sched_name,steps", [("euler", 12), ("DDIM", 12), ("DPM++ 2M", 12), ("DPM++ 2M Karras", 8),
-                                              ("euler_a", 12), ("DPM++ 2M SDE Karras", 12), ("PNDM", 12)])
+                                              ("euler_a", 12), ("DPM++ 2M SDE Karras", 12), ("PNDM", 12), ("uni_pc", 12)])
 def test_fused_loop_vs_oracle(cuda_device, sched_name, steps):
     """Whole trajectory: B200 fused loop (graph replay) vs the oracle's restatement of the reference loop."""
     from oracle import pipeline as OP
@@ -193,7 +193,7 @@ def test_fused_loop_vs_oracle(cuda_device, sched_name, steps):
     assert torch.isfinite(out).all() and rl2 <= 5e-2
 
 
-@pytest.mark.parametrize("sched_name", ["euler", "PNDM", "euler_a", "DPM++ 2M SDE Karras"])
+@pytest.mark.parametrize("sched_name", ["euler", "PNDM", "euler_a", "DPM++ 2M SDE Karras", "uni_pc"])
 def test_unfused_reference_call_pattern_matches_fused(cuda_device, sched_name):
     """Driving the B200 objects exactly like the reference loop (pipeline :465-489) gives the fused result."""
     from stablediffusion_b200.models.stable_diffusion import SDModelWrapper
@@ -287,7 +287,7 @@ def test_pipeline_sd15_txt2img_20_euler(cuda_device):
     assert torch.isfinite(img).all() and psnr >= 30.0
 
 
-@pytest.mark.parametrize("sched_name,strength", [("euler", 1.0), ("DDIM", 0.6), ("DPM++ 2M", 0.75), ("PNDM", 1.0), ("euler_a", 0.5)])
+@pytest.mark.parametrize("sched_name,strength", [("euler", 1.0), ("DDIM", 0.6), ("DPM++ 2M", 0.75), ("PNDM", 1.0), ("euler_a", 0.5), ("uni_pc", 0.7)])
 def test_inpaint_loop_vs_oracle(cuda_device, sched_name, strength):
     """Third pipeline mode (reference :266-380, :492-506): 4-channel inpainting — the masked region is denoised, the rest
     is re-noised original latents after every step.  `image` is passed in latent space (skips the VAE so that both sides
