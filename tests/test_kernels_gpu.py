@@ -490,3 +490,24 @@ def test_embed_bit_exact(cuda_device):
     _run(b)
     ref = (tok[ids.long()].float() + pos.float().repeat(B, 1)).to(torch.bfloat16)
     assert torch.equal(out, ref)
+
+
+@pytest.mark.parametrize("nq_override", ["1", "wide"])
+@pytest.mark.parametrize("B,heads,Nq,Nkv,d", [(1, 2, 600, 600, 64), (2, 3, 130, 333, 40), (1, 2, 1000, 77, 80), (1, 1, 513, 513, 160),
+                                              (2, 2, 384, 4096, 40)])
+def test_attention_tile_configs_ragged(cuda_device, monkeypatch, nq_override, B, heads, Nq, Nkv, d):
+    """Both CTA shapes (one query tile / 4-or-2 tiles sharing K/V) on ragged sizes: query counts that leave the last CTA
+    with 1..3 live tiles and a partly filled last tile, key counts that end mid-block."""
+    dev = cuda_device
+    dpad = (d + 63) // 64 * 64
+    monkeypatch.setenv("B200SD_ATT_NQ", "1" if nq_override == "1" else ("4" if dpad == 64 else "2"))
+    C = heads * d
+    q = _bf(_randn((B, Nq, C), dev, 11))
+    k = _bf(_randn((B, Nkv, C), dev, 12))
+    v = _bf(_randn((B, Nkv, C), dev, 13))
+    b = _builder(dev)
+    out = b.attention(q, k, v, heads, d, d ** -0.5)
+    _run(b)
+    sp = lambda t, n: t.float().view(B, n, heads, d).transpose(1, 2)
+    ref = F.scaled_dot_product_attention(sp(q, Nq), sp(k, Nkv), sp(v, Nkv)).transpose(1, 2).reshape(B, Nq, C)
+    _check(out, ref, rtol=2 ** -6, name=f"attention NQ={nq_override}")
