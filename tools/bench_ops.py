@@ -62,6 +62,10 @@ att("attn_self_1024_d80_b2", 2, 8, 1024, 1024, 80)
 att("attn_xl_4096_d64", 4, 10, 4096, 4096, 64)
 att("attn_xl_1024_d64", 4, 20, 1024, 1024, 64)
 gn("gn_16x4096x320", 16, 4096, 320)
+gn("gn_16x1024x640", 16, 1024, 640)
+gn("gn_16x256x1280", 16, 256, 1280)
+gn("gn_16x64x1280", 16, 64, 1280)
+gn("gn_16x64x2560", 16, 64, 2560)
 ln("ln_65536x320", 65536, 320)
 
 flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
