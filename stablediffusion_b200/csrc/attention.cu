@@ -47,6 +47,14 @@ extern "C" __attribute__((visibility("default"))) int b200sd_debug_att_trace(uns
 #endif
 namespace {
 
+// P_j as the TMEM A operand of the PV product (tcgen05.mma "TS" form: P is written with tcgen05.st over the first 32
+// columns of the S_j it was computed from) instead of a swizzled shared-memory tile.  -DB200SD_ATT_SS=1 builds the
+// older shared-memory form (A/B measurements).
+#ifndef B200SD_ATT_SS
+#define B200SD_ATT_SS 0
+#endif
+constexpr bool ATT_TS = (B200SD_ATT_SS == 0);
+
 constexpr int BLK = 128;           // rows of a query tile
 constexpr int KB = 64;             // keys per KV block
 constexpr int TILE16K = BLK * 128; // [128 rows x 64 bf16] swizzled tile (Q chunk, P)
@@ -81,7 +89,8 @@ struct AttnCfg {
   static constexpr int NSTV = NQ > 1 ? (DPAD == 192 ? 2 : 3) : (DPAD == 64 ? 1 : 2);
   static constexpr int QT_BYTES = DB * TILE16K;             // one query tile
   static constexpr int KV_BYTES = DB * TILE8K;              // one K (or V) stage
-  static constexpr int SMEM = NQ * (QT_BYTES + TILE16K) + (NSTK + NSTV) * KV_BYTES + 1024 + 256;
+  static constexpr int P_BYTES = ATT_TS ? 0 : TILE16K;      // shared-memory P tile (SS form only)
+  static constexpr int SMEM = NQ * (QT_BYTES + P_BYTES) + (NSTK + NSTV) * KV_BYTES + 1024 + 256;
   static_assert(OCC * (SMEM + 1024) <= 233472, "shared memory budget");
   static_assert(OCC * TMEM_COLS <= 512 && NQ * TILE_COLS <= TMEM_COLS, "TMEM budget");
 };
@@ -94,6 +103,26 @@ __device__ __forceinline__ float ex2_approx(float x) {
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
 #endif
+}
+// Packed fp32 pairs (FFMA2 / FADD2: two results per issue slot).  The softmax warps share their schedulers' issue slots
+// with the MUFU stream, so every instruction saved raises the MUFU density.
+__device__ __forceinline__ uint64_t pack_f32x2(uint32_t lo, uint32_t hi) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "r"(lo), "r"(hi));
+  return r;
+}
+__device__ __forceinline__ void unpack_f32x2(uint64_t v, float& lo, float& hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ uint64_t fma_f32x2(uint64_t a, uint64_t b, uint64_t c) {
+  uint64_t d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+__device__ __forceinline__ uint64_t add_f32x2(uint64_t a, uint64_t b) {
+  uint64_t d;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
 }
 __device__ __forceinline__ void sts128(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
   asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
@@ -111,8 +140,8 @@ attention_kernel(const __grid_constant__ AttnParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* sQ = smem;                              // [NQ][QT_BYTES]
-  uint8_t* sP = sQ + NQ * Cfg::QT_BYTES;           // [NQ][TILE16K]
-  uint8_t* sK = sP + NQ * TILE16K;                 // [NSTK][KV_BYTES]
+  uint8_t* sP = sQ + NQ * Cfg::QT_BYTES;           // [NQ][P_BYTES]
+  uint8_t* sK = sP + NQ * Cfg::P_BYTES;            // [NSTK][KV_BYTES]
   uint8_t* sV = sK + NSTK * Cfg::KV_BYTES;         // [NSTV][KV_BYTES]
   uint64_t* bars = reinterpret_cast<uint64_t*>(sV + NSTV * Cfg::KV_BYTES);
   uint64_t* q_full = bars;             // 1
@@ -235,6 +264,38 @@ attention_kernel(const __grid_constant__ AttnParams p) {
       for (int t = t_first; t < min(live, t_first + TPW); ++t) issue_S(t, 0);
     }
     __syncwarp();
+    if constexpr (ATT_TS) {
+      // One service per tile and block: P_j (in TMEM, over S_j's first 32 columns) is ready -> PV_j, then S_{j+1}
+      // into the same columns.  The tensor core executes a thread's MMAs in issue order, so S_{j+1} cannot overwrite
+      // P_j before PV_j has consumed it, and s_full(j+1) also tells the softmax warps that PV_j is complete.
+      for (int j = 0; j < nkv; ++j) {
+        const int st = j % NSTV;
+        mbar_wait(&v_full[st], (j / NSTV) & 1);
+        if (j + 1 < nkv) mbar_wait(&k_full[(j + 1) % NSTK], ((j + 1) / NSTK) & 1);
+#pragma unroll
+        for (int tt = 0; tt < TPW; ++tt) {
+          const int t = t_first + tt;
+          if (t < live) {
+            mbar_wait(&p_full[t], j & 1);  // P_j of tile t written
+            tc_fence_after();
+            if (elect_one()) {
+              if (t == 0) ATT_TR(1, 7);
+              const uint32_t v_off = st * Cfg::KV_BYTES;
+              const uint32_t tmem_P = tmem_base + t * Cfg::TILE_COLS;
+              const uint32_t tmem_O = tmem_P + KB;
+#pragma unroll
+              for (int ks = 0; ks < KB / 16; ++ks)
+                umma_bf16_ts(tmem_O, tmem_P + ks * 8, desc_advance(dv[ks], v_off), idesc_o, (j | ks) != 0 ? 1u : 0u);
+              umma_commit(&v_empty[st]);
+              if (j + 1 < nkv) issue_S(t, j + 1);
+              else umma_commit(&pv_done[t]);
+              if (t == 0) ATT_TR(1, 8);
+            }
+            __syncwarp();
+          }
+        }
+      }
+    } else {
     for (int j = 0; j < nkv; ++j) {
       if (j + 1 < nkv) {
         mbar_wait(&k_full[(j + 1) % NSTK], ((j + 1) / NSTK) & 1);  // K_{j+1}: loaded a block or more ago
@@ -275,6 +336,7 @@ attention_kernel(const __grid_constant__ AttnParams p) {
           __syncwarp();
         }
       }
+    }
     }
   } else {
     // ===================== softmax / correction / epilogue: thread <-> query row =====================
@@ -401,16 +463,99 @@ attention_kernel(const __grid_constant__ AttnParams p) {
         }
         l_run += rsum;
       };
-      if (valid == KB && !p.causal) block_body(std::false_type{});
-      else block_body(std::true_type{});
+      // chunk c: probabilities relative to m_ref -> packed bf16 pairs in registers; returns the chunk's row sum
+      auto exp_pack = [&](auto masked_tag, int c, const uint32_t (&u)[32], const float m_ref, uint32_t (&pk)[16]) {
+        constexpr bool MASKED = decltype(masked_tag)::value;
+        const uint64_t sc2 = pack_f32x2(__float_as_uint(p.scale_log2), __float_as_uint(p.scale_log2));
+        const uint64_t nm2 = pack_f32x2(__float_as_uint(-m_ref), __float_as_uint(-m_ref));
+        uint64_t acc = 0;  // two partial row sums
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          float x0, x1;
+          unpack_f32x2(fma_f32x2(pack_f32x2(u[2 * i], u[2 * i + 1]), sc2, nm2), x0, x1);
+          float p0 = ex2_approx(x0);
+          float p1 = ex2_approx(x1);
+          if (MASKED) {
+            if (c * 32 + 2 * i >= lim) p0 = 0.f;
+            if (c * 32 + 2 * i + 1 >= lim) p1 = 0.f;
+          }
+          acc = add_f32x2(acc, pack_f32x2(__float_as_uint(p0), __float_as_uint(p1)));
+          pk[i] = pack_bf16x2(p0, p1);
+        }
+        float r0, r1;
+        unpack_f32x2(acc, r0, r1);
+        return r0 + r1;
+      };
+      // TS form.  P_j (64 keys = 32 packed columns) overwrites columns [0, 32) of S_j: the first half is stored only
+      // after the second half of S_j sits in registers and the lazy-max vote has passed, so the rare redo still finds
+      // S_j intact.  s_full(j) implies PV_{j-1} has completed (same issuing thread, in order): no other wait is needed
+      // before P_{j-1} / O are touched.
+      auto block_body_ts = [&](auto masked_tag) {
+        uint32_t u[32], pk0[16], pk1[16];
+        if (j == 0) {  // very first block: exact max (nothing to rescale yet)
+          float mx = -INFINITY;
+#pragma unroll
+          for (int c = 0; c < KB / 32; ++c) {
+            tmem_ld32(s_addr + c * 32, u);
+            tmem_ld_wait();
+            mx = fmaxf(mx, raw_max(masked_tag, c, u));
+          }
+          m_run = mx * p.scale_log2;
+        }
+        tmem_ld32(s_addr, u);
+        tmem_ld_wait();
+        float mx = raw_max(masked_tag, 0, u);
+        float rsum = exp_pack(masked_tag, 0, u, m_run, pk0);
+        tmem_ld32(s_addr + 32, u);
+        tmem_ld_wait();
+        mx = fmaxf(mx, raw_max(masked_tag, 1, u));
+        const float m_blk = mx * p.scale_log2;
+        const bool outgrown = m_blk > m_run + LAZY_TAU;
+        if (!__any_sync(0xffffffffu, outgrown)) {
+          tmem_st16(s_addr, pk0);
+          rsum += exp_pack(masked_tag, 1, u, m_run, pk1);
+          tmem_st16(s_addr + 16, pk1);
+        } else {  // rare; warp-uniform because tcgen05.ld/st are .sync.aligned
+          float alpha = 1.0f;
+          if (outgrown) {  // this row moves its reference to the exact max; the other rows just repeat
+            alpha = ex2_approx(m_run - m_blk);
+            m_run = m_blk;
+          }
+          rsum = exp_pack(masked_tag, 1, u, m_run, pk1);
+          tmem_ld32(s_addr, u);  // first half again (not yet overwritten), against the new reference
+          tmem_ld_wait();
+          rsum += exp_pack(masked_tag, 0, u, m_run, pk0);
+          tmem_st16(s_addr, pk0);
+          tmem_st16(s_addr + 16, pk1);
+          l_run *= alpha;
+#pragma unroll 1
+          for (int c = 0; c < p.n_pv / 16; ++c) {  // O *= alpha (PV_{j-1} has landed, PV_j is not issued before p_full)
+            uint32_t o[16];
+            tmem_ld16(o_addr + c * 16, o);
+            tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 16; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+            tmem_st16(o_addr + c * 16, o);
+          }
+        }
+        tmem_st_wait();
+        l_run += rsum;
+      };
+      if constexpr (ATT_TS) {
+        if (valid == KB && !p.causal) block_body_ts(std::false_type{});
+        else block_body_ts(std::true_type{});
+      } else {
+        if (valid == KB && !p.causal) block_body(std::false_type{});
+        else block_body(std::true_type{});
+        fence_proxy_async_smem();  // P (generic-proxy stores) -> visible to the MMA's async-proxy reads
+      }
       if (q == 2 && lane == 0) ATT_TR(2 + t, 2);
-      fence_proxy_async_smem();  // P (generic-proxy stores) -> visible to the MMA's async-proxy reads
       tc_fence_before();
       mbar_arrive(my_p_full);
       if (q == 2 && lane == 0) ATT_TR(2 + t, 3);
     }
     // ---- epilogue: O / l -> bf16 -> global ----
-    if (nblk > 0) mbar_wait(my_pv_done, (nkv - 1) & 1);
+    if (nblk > 0) mbar_wait(my_pv_done, ATT_TS ? 0 : (nkv - 1) & 1);  // (TS form: committed once, after the last PV)
     tc_fence_after();
     const float inv_l = 1.0f / l_run;
     const int qrow = nblk > 0 ? q0 + t * BLK + r : p.Nq;

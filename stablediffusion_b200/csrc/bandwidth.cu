@@ -2,6 +2,7 @@
 // accesses, fp32 math, warp-shuffle / shared-memory reductions.  Algorithmic bytes per unit are stated at
 // each kernel; DESIGN.md carries the roofline table.
 #include <algorithm>
+#include <cstdlib>
 #include <new>
 
 #include "common.cuh"
@@ -203,10 +204,144 @@ __global__ void gn_apply_kernel(const GNParams p) {
   for (; pix < pix_end; pix += p.R) apply_store(ldg_stream(gn_src(p, n, pix, c0)), pix);
 }
 
-struct GNPlan { GNParams p; int threads; size_t smem; };
+// Single-launch GroupNorm for small images (the 8x8 level of the UNet, where the two-kernel form is bound by its
+// launches and dependent global round trips, not by bytes).  A thread-block cluster owns ONE image: its CTAs split the
+// pixels, each keeps its slice in shared memory between the statistics and the apply pass (one global read instead of
+// two), the per-group sums are exchanged through distributed shared memory.
+// Measured in-graph on B200 (tools/bench_chain.py): 16x64x1280 9.2 us vs 10.4 for the two kernels, 2x64x1280 6.8 vs 8.4;
+// but a cluster is at most 8 SMs per image, so larger slices lose to the 4-CTAs-per-SM grid of the two-kernel form
+// (16x1024x640, 164 KB per CTA: 37.6 vs 22.2 us; 2x256x1280: 10.8 vs 9.0) — hence the 32 KB slice limit.
+constexpr int GNF_MAX_CLUSTER = 8;
+constexpr int GNF_HEADER_BYTES = 1024;           // gsum[64][2], mean[64], rstd[64]
+constexpr int GNF_MAX_DATA_BYTES = 32 * 1024;    // slice of one CTA
+
+__device__ __forceinline__ float ld_shared_cluster_f32(uint32_t addr) {
+  float v;
+  asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(addr) : "memory");
+  return v;
+}
+
+__global__ void __launch_bounds__(512) gn_fused_kernel(const GNParams p) {
+  pdl_launch_dependents();
+  pdl_wait();
+  extern __shared__ __align__(16) unsigned char gnf_smem[];
+  float* gsum = reinterpret_cast<float*>(gnf_smem);  // [groups][2]
+  float* smean = gsum + 128;
+  float* srstd = smean + 64;
+  uint4* data = reinterpret_cast<uint4*>(gnf_smem + GNF_HEADER_BYTES);
+  const int chunk = blockIdx.x, n = blockIdx.y;  // cluster = all chunks of image n (gridDim.x == cluster size)
+  const int tid = threadIdx.x, nthreads = blockDim.x;
+  const int vcol = tid % p.cols, r = tid / p.cols;
+  const int c0 = vcol * 8;
+  if (tid < p.groups) { gsum[2 * tid] = 0.f; gsum[2 * tid + 1] = 0.f; }
+  __syncthreads();
+  float s[8], ss[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) { s[j] = 0.f; ss[j] = 0.f; }
+  const int pix_end = min((chunk + 1) * p.ppc, p.HW);
+  auto accumulate = [&](const uint4& v) {
+    uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      float2 f = unpack_bf16x2(w[j]);
+      s[2 * j] += f.x; ss[2 * j] += f.x * f.x;
+      s[2 * j + 1] += f.y; ss[2 * j + 1] += f.y * f.y;
+    }
+  };
+  int pix = chunk * p.ppc + r;
+  int it = 0;
+  for (; pix + 3 * p.R < pix_end; pix += 4 * p.R, it += 4) {  // 4 independent 16-byte loads in flight per thread
+    uint4 v4[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) v4[u] = ldg_stream(gn_src(p, n, pix + u * p.R, c0));
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      data[(it + u) * nthreads + tid] = v4[u];
+      accumulate(v4[u]);
+    }
+  }
+  for (; pix < pix_end; pix += p.R, ++it) {
+    const uint4 v = ldg_stream(gn_src(p, n, pix, c0));
+    data[it * nthreads + tid] = v;
+    accumulate(v);
+  }
+  const int my_iters = it;
+  {
+    int g_prev = c0 / p.cpg;
+    float as = 0.f, ass = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      int g = (c0 + j) / p.cpg;
+      if (g != g_prev) {
+        atomicAdd(&gsum[2 * g_prev], as);
+        atomicAdd(&gsum[2 * g_prev + 1], ass);
+        as = 0.f; ass = 0.f; g_prev = g;
+      }
+      as += s[j]; ass += ss[j];
+    }
+    atomicAdd(&gsum[2 * g_prev], as);
+    atomicAdd(&gsum[2 * g_prev + 1], ass);
+  }
+  cluster_sync_all();  // every CTA's group sums are complete and visible cluster-wide
+  if (tid < p.groups) {
+    double S = 0.0, SS = 0.0;
+    const uint32_t local = smem_u32(gsum + 2 * tid);
+    for (int q = 0; q < p.chunks; ++q) {  // same order in every CTA: identical statistics across the cluster
+      const uint32_t remote = mapa_u32(local, static_cast<uint32_t>(q));
+      S += ld_shared_cluster_f32(remote);
+      SS += ld_shared_cluster_f32(remote + 4);
+    }
+    const double cnt = static_cast<double>(p.HW) * p.cpg;
+    const double mean = S / cnt;
+    double var = SS / cnt - mean * mean;
+    if (var < 0.0) var = 0.0;
+    smean[tid] = static_cast<float>(mean);
+    srstd[tid] = static_cast<float>(1.0 / sqrt(var + static_cast<double>(p.eps)));
+  }
+  cluster_sync_all();  // peers have finished reading this CTA's sums (it may exit); mean / rstd visible to the CTA
+  float a[8], b[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const int c = c0 + j;
+    const int g = c / p.cpg;
+    a[j] = srstd[g] * __ldg(p.gamma + c);
+    b[j] = __ldg(p.beta + c) - smean[g] * a[j];
+  }
+  pix = chunk * p.ppc + r;
+  for (it = 0; it < my_iters; ++it, pix += p.R) {
+    const uint4 v = data[it * nthreads + tid];
+    uint32_t w[4] = {v.x, v.y, v.z, v.w};
+    uint32_t o[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      float2 f = unpack_bf16x2(w[j]);
+      float y0 = fmaf(f.x, a[2 * j], b[2 * j]);
+      float y1 = fmaf(f.y, a[2 * j + 1], b[2 * j + 1]);
+      if (p.silu) { y0 = silu_f(y0); y1 = silu_f(y1); }
+      o[j] = pack_bf16x2(y0, y1);
+    }
+    bf16* dst = p.out + (static_cast<long long>(n) * p.HW + pix) * p.C + c0;
+    *reinterpret_cast<uint4*>(dst) = make_uint4(o[0], o[1], o[2], o[3]);
+  }
+}
+
+bool gn_fused_enabled() {
+  static const bool on = [] {
+    const char* e = getenv("B200SD_GN_FUSED");
+    return !(e && e[0] == '0');
+  }();
+  return on;
+}
+
+struct GNPlan { GNParams p; int threads; size_t smem; int fused; };
 int launch_groupnorm(const void* plan, cudaStream_t s) {
   const GNPlan& pl = *static_cast<const GNPlan*>(plan);
   dim3 grid(pl.p.chunks, pl.p.NB);
+  if (pl.fused) {
+    B200SD_CUDA(launch_kernel(gn_fused_kernel, dim3(grid), dim3(pl.threads), pl.smem, s, pl.p.chunks, pl.p));
+    B200SD_CUDA(cudaGetLastError());
+    return 0;
+  }
   B200SD_CUDA(launch_kernel(gn_stats_kernel, dim3(grid), dim3(pl.threads), 0, s, 1, pl.p));
   B200SD_CUDA(cudaGetLastError());
   B200SD_CUDA(launch_kernel(gn_apply_kernel, dim3(grid), dim3(pl.threads), pl.smem, s, 1, pl.p));
@@ -769,6 +904,30 @@ int plan_groupnorm(const b200sd_groupnorm& g, PlannedOp* out) {
   p.ld1 = g.ld1; p.ld2 = g.ld2; p.C1 = g.C1; p.C2 = g.C2; p.C = C;
   p.NB = g.NB; p.HW = g.HW; p.groups = g.groups; p.cpg = C / g.groups; p.silu = g.silu; p.eps = g.eps;
   p.gamma = g.gamma; p.beta = g.beta; p.out = static_cast<bf16*>(g.out); p.partials = g.partials;
+  p.cols = C / 8;
+  pl.fused = 0;
+  if (gn_fused_enabled() && p.cols <= 512) {
+    // fused form: the image must fit the shared memory of a cluster of <= 8 CTAs
+    const int R = std::max(1, 512 / p.cols);
+    int chunks = std::min(GNF_MAX_CLUSTER, std::max(1, g.HW / R));
+    const int ppc = (g.HW + chunks - 1) / chunks;
+    chunks = (g.HW + ppc - 1) / ppc;
+    const int iters = (ppc + R - 1) / R;
+    const size_t data_bytes = static_cast<size_t>(iters) * p.cols * R * 16;
+    if (data_bytes <= static_cast<size_t>(GNF_MAX_DATA_BYTES)) {
+      static bool attr_set = false;
+      if (!attr_set) {
+        if (cudaFuncSetAttribute(gn_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 GNF_HEADER_BYTES + GNF_MAX_DATA_BYTES) == cudaSuccess) attr_set = true;
+        else (void)cudaGetLastError();  // no device (planning arithmetic only): the launch will report it
+      }
+      p.chunks = chunks; p.ppc = ppc; p.R = R;
+      pl.threads = p.cols * R;
+      pl.smem = GNF_HEADER_BYTES + data_bytes;
+      pl.fused = 1;
+      return finish_plan(out, B200SD_OP_GROUPNORM, pl, launch_groupnorm, 1);
+    }
+  }
   p.chunks = groupnorm_chunks(g.NB, g.HW, C);
   p.ppc = (g.HW + p.chunks - 1) / p.chunks;
   p.chunks = (g.HW + p.ppc - 1) / p.ppc;

@@ -322,7 +322,10 @@ def test_attention_fused_qkv_views(cuda_device):
     "NB,HW,C1,C2,silu,eps",
     [(2, 4096, 320, 0, True, 1e-5), (2, 1024, 1280, 640, True, 1e-5), (2, 64, 1280, 1280, True, 1e-5),
      (2, 4096, 640, 320, True, 1e-5), (1, 4096, 128, 0, True, 1e-6), (2, 256, 1280, 0, False, 1e-6),
-     (3, 100, 64, 32, True, 1e-5)],
+     (3, 100, 64, 32, True, 1e-5),
+     # images that fit one cluster's shared memory take the single-launch kernel (gn_fused_kernel)
+     (16, 1024, 640, 0, True, 1e-5), (2, 1024, 320, 320, True, 1e-5), (1, 7, 32, 0, True, 1e-5),
+     (2, 256, 1280, 1280, True, 1e-5), (5, 64, 1280, 0, False, 1e-5), (2, 1000, 640, 0, True, 1e-5)],
 )
 def test_groupnorm(cuda_device, NB, HW, C1, C2, silu, eps):
     dev = cuda_device
