@@ -70,6 +70,60 @@ __device__ __forceinline__ float gelu_erf_f(float x) {
   return x * (x >= 0.f ? 1.0f - h : h);
 }
 
+// Packed fp32 pairs (sm_100 FFMA2 / FADD2 / FMUL2: two results per issue slot).
+__device__ __forceinline__ uint64_t f32x2_pack(float lo, float hi) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void f32x2_unpack(uint64_t v, float& lo, float& hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ uint64_t f32x2_fma(uint64_t a, uint64_t b, uint64_t c) {
+  uint64_t d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+__device__ __forceinline__ uint64_t f32x2_add(uint64_t a, uint64_t b) {
+  uint64_t d;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ uint64_t f32x2_mul(uint64_t a, uint64_t b) {
+  uint64_t d;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+// (h0, h1) * gelu_erf(g0, g1): the GEGLU epilogue on two outputs at once, same A&S 7.1.26 form as gelu_erf_f with
+// Phi(x) = 0.5 + copysign(0.5 - Phi(-|x|), x).  ~19 FMA-pipe issue slots + 4 MUFU per PAIR (the scalar form: ~20 slots +
+// 2 MUFU per output).  Measured neutral on the step (the exposed part of the GEGLU epilogue is the accumulator read-out
+// competing with the MMAs for tensor memory, not its arithmetic: moving the reciprocal to the FMA pipe with a Newton
+// iteration — no MUFU for it — changed nothing either); kept because it halves the epilogue's instruction count.
+__device__ __forceinline__ void geglu_f32x2(float h0, float h1, float g0, float g1, float& o0, float& o1) {
+  const uint64_t X = f32x2_pack(g0, g1);
+  const uint64_t AX = X & 0x7FFFFFFF7FFFFFFFull;
+  float d0, d1;
+  f32x2_unpack(f32x2_fma(AX, f32x2_pack(0.23164190f, 0.23164190f), f32x2_pack(1.0f, 1.0f)), d0, d1);
+  float t0, t1;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t0) : "f"(d0));
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t1) : "f"(d1));
+  const uint64_t T = f32x2_pack(t0, t1);
+  uint64_t Q = f32x2_fma(f32x2_pack(0.5307027145f, 0.5307027145f), T, f32x2_pack(-0.7265760135f, -0.7265760135f));
+  Q = f32x2_fma(Q, T, f32x2_pack(0.7107068705f, 0.7107068705f));
+  Q = f32x2_fma(Q, T, f32x2_pack(-0.142248368f, -0.142248368f));
+  Q = f32x2_fma(Q, T, f32x2_pack(0.127414796f, 0.127414796f));
+  float a0, a1;
+  f32x2_unpack(f32x2_mul(f32x2_mul(X, X), f32x2_pack(-0.72134752044f, -0.72134752044f)), a0, a1);
+  float e0, e1;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e0) : "f"(a0));
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e1) : "f"(a1));
+  const uint64_t Hh = f32x2_mul(f32x2_mul(Q, T), f32x2_pack(e0, e1));                           // Phi(-|x|) <= 0.5
+  uint64_t S = f32x2_fma(Hh, f32x2_pack(-1.0f, -1.0f), f32x2_pack(0.5f, 0.5f));                 // 0.5 - Phi(-|x|) >= 0
+  S |= X & 0x8000000080000000ull;                                                                // copysign(S, x)
+  const uint64_t Phi = f32x2_add(S, f32x2_pack(0.5f, 0.5f));
+  f32x2_unpack(f32x2_mul(f32x2_pack(h0, h1), f32x2_mul(X, Phi)), o0, o1);
+}
+
 __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
   __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
   return *reinterpret_cast<uint32_t*>(&v);

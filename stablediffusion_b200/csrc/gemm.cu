@@ -16,6 +16,8 @@
 // reduces with the same epilogue.
 #include <algorithm>
 #include <cmath>
+#include <cstdio>
+#include <cstdlib>
 #include <new>
 
 #include "common.cuh"
@@ -49,9 +51,12 @@ __host__ __device__ constexpr int gemm_stages(int bn, int ncta) {
 __host__ __device__ constexpr int tmem_cols_for(int bn) {
   return 2 * bn <= 32 ? 32 : (2 * bn <= 64 ? 64 : (2 * bn <= 128 ? 128 : (2 * bn <= 256 ? 256 : 512)));
 }
-__host__ __device__ constexpr int gemm_smem_bytes(int bn, int ncta) {
-  return gemm_stages(bn, ncta) * gemm_stage_bytes(bn, ncta) + gemm_fixed_bytes(bn);
-}
+// Bytes of the operand-stage region.  The kernel always takes the whole SM (one CTA per SM anyway): in the
+// weight-resident mode the region is re-carved as [all k-blocks of this CTA's weight rows][A-only stages].
+__host__ __device__ constexpr int gemm_region_bytes(int bn) { return (GEMM_SMEM_LIMIT - gemm_fixed_bytes(bn)) & ~1023; }
+__host__ __device__ constexpr int gemm_smem_bytes(int bn, int) { return gemm_region_bytes(bn) + gemm_fixed_bytes(bn); }
+constexpr int MAX_STAGES = 8;
+constexpr int WRES_MIN_STAGES = 4;  // A-only stages the weight-resident mode needs to keep the L2 -> SM stream busy
 static_assert(gemm_stages(256, 1) >= 3 && gemm_stages(160, 1) >= 4 && gemm_stages(256, 2) >= 4, "pipeline depth");
 
 struct alignas(64) GemmKParams {
@@ -90,6 +95,9 @@ struct alignas(64) GemmKParams {
   float alpha;
   int flags;
   float* partial;
+  // weight-resident mode (short-K linears): a work unit keeps ONE N tile for all its M tiles, its weight rows (all k-blocks)
+  // are loaded once and stay in shared memory, the pipeline stages carry activations only
+  int wres, wres_stages, units_per_nt;
 };
 
 struct TileCoord {
@@ -132,6 +140,20 @@ __device__ __forceinline__ TileCoord decode_work(const GemmKParams& p, int work,
     ks = rest / p.num_n_tiles;
   }
   return decode_tile(p, pm * p.ncta + rank, nt, ks);
+}
+
+// Work items of persistent unit `unit` (of `num_units`) and the it-th one.
+__device__ __forceinline__ int unit_items(const GemmKParams& p, int unit, int num_units) {
+  if (p.wres) {
+    const int first = unit / p.num_n_tiles;
+    return first < p.num_pm ? (p.num_pm - first + p.units_per_nt - 1) / p.units_per_nt : 0;
+  }
+  const int total_work = p.num_pm * p.num_n_tiles * p.splits;
+  return unit < total_work ? (total_work - unit + num_units - 1) / num_units : 0;
+}
+__device__ __forceinline__ TileCoord unit_tile(const GemmKParams& p, int unit, int num_units, int it, int rank) {
+  if (p.wres) return decode_tile(p, (unit / p.num_n_tiles + it * p.units_per_nt) * p.ncta + rank, unit % p.num_n_tiles, 0);
+  return decode_work(p, unit + it * num_units, rank);
 }
 
 struct RowInfo {
@@ -325,16 +347,24 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* ring = smem + NSTAGE * STAGE_BYTES;  // epilogue staging ring (1 KiB aligned: stages are multiples of 1 KiB)
+  uint8_t* ring = smem + gemm_region_bytes(BN);  // epilogue staging ring (1 KiB aligned)
   float* bias_s = reinterpret_cast<float*>(ring + RING_BYTES);  // [2 accumulators][BN]
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(bias_s + 2 * BN);
-  uint64_t* empty_bar = full_bar + NSTAGE;
-  uint64_t* tfull_bar = empty_bar + NSTAGE;
+  uint64_t* empty_bar = full_bar + MAX_STAGES;
+  uint64_t* tfull_bar = empty_bar + MAX_STAGES;
   uint64_t* tempty_bar = tfull_bar + 2;
   uint64_t* res_bar = tempty_bar + 2;            // [RING_SLOTS] residual sub-tile landed in the slot
   uint64_t* ready_bar = res_bar + RING_SLOTS;    // [RING_SLOTS] sub-tile written by its 128 epilogue threads
   uint64_t* free_bar = ready_bar + RING_SLOTS;   // [RING_SLOTS] the slot's TMA store has finished reading it
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(free_bar + RING_SLOTS);
+  uint64_t* wres_bar = free_bar + RING_SLOTS;    // resident weight rows landed (pair: the leader's collects both CTAs')
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(wres_bar + 1);
+  static_assert((2 * MAX_STAGES + 4 + 3 * RING_SLOTS + 1) * 8 + 4 <= 512, "barrier block");
+  static_assert(NSTAGE * STAGE_BYTES <= gemm_region_bytes(BN) && NSTAGE <= MAX_STAGES, "stage region");
+  // stage geometry: [A | W rows] per stage, or (weight-resident) [W rows of all k-blocks] followed by A-only stages
+  const bool wres = p.wres != 0;
+  const int nst = wres ? p.wres_stages : NSTAGE;
+  const int stage_bytes = wres ? A_STAGE_BYTES : STAGE_BYTES;
+  uint8_t* const stage_base = wres ? smem + p.kb_total * B_STAGE_BYTES : smem;
 
   pdl_launch_dependents();  // the next kernel may start its prologue as SMs free up
   const int warp = threadIdx.x >> 5;
@@ -344,10 +374,11 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
   const int num_units = gridDim.x / NCTA;
 
   if (threadIdx.x == 0) {
-    for (int i = 0; i < NSTAGE; ++i) {
+    for (int i = 0; i < MAX_STAGES; ++i) {
       mbar_init(&full_bar[i], 1);
       mbar_init(&empty_bar[i], 1);
     }
+    mbar_init(wres_bar, 1);
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tfull_bar[i], 1);
       mbar_init(&tempty_bar[i], 8 * NCTA);  // one arrival per epilogue warp of every CTA that reads the accumulator
@@ -372,15 +403,26 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
   const uint32_t tmem_base = *tmem_slot;
   pdl_wait();  // everything above overlapped the previous kernel's tail; its results are visible from here on
 
-  const int total_work = p.num_pm * p.num_n_tiles * p.splits;
+  const int n_items = unit_items(p, unit, num_units);
 
   if (warp == 0) {
     // ===================== TMA producer (one lane; in a pair BOTH CTAs load: own A rows, own half of W) =====================
     if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int work = unit; work < total_work; work += num_units) {
-        const TileCoord t = decode_work(p, work, rank);
+      if (wres && n_items > 0) {  // this unit's weight rows, every k-block, once (one segment, one tap: kb == channel block)
+        const int n0 = (unit % p.num_n_tiles) * BN + rank * B_ROWS;
+        if (NCTA == 1) {
+          mbar_arrive_expect_tx(wres_bar, p.kb_total * B_STAGE_BYTES);
+          for (int kb = 0; kb < p.kb_total; ++kb) tma_load_3d(smem + kb * B_STAGE_BYTES, &p.tmB[0], wres_bar, kb * BK, 0, n0);
+        } else {
+          if (rank == 0) mbar_arrive_expect_tx(wres_bar, 2 * p.kb_total * B_STAGE_BYTES);
+          const uint32_t wb = mapa_u32(smem_u32(wres_bar), 0);
+          for (int kb = 0; kb < p.kb_total; ++kb) tma_load_3d_2cta(smem + kb * B_STAGE_BYTES, &p.tmB[0], wb, kb * BK, 0, n0);
+        }
+      }
+      for (int it = 0; it < n_items; ++it) {
+        const TileCoord t = unit_tile(p, unit, num_units, it, rank);
         const int kb0 = t.ks * p.kb_per_split;
         const int kb1 = min(kb0 + p.kb_per_split, p.kb_total);
         int seg = 0;
@@ -390,20 +432,20 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
         int cb = local - tap * p.seg_cb[seg];
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
-          uint8_t* sa = smem + stage * STAGE_BYTES;
+          uint8_t* sa = stage_base + stage * stage_bytes;
           uint8_t* sb = sa + A_STAGE_BYTES;
           if (NCTA == 1) {
-            mbar_arrive_expect_tx(&full_bar[stage], STAGE_BYTES);
+            mbar_arrive_expect_tx(&full_bar[stage], stage_bytes);
             if (p.spatial) {
               tma_load_5d(sa, &p.tmA[seg], &full_bar[stage], cb * BK, t.w0 + p.tap_dw[seg][tap],
                           t.h0 + p.tap_dh[seg][tap], t.n0, p.tap_phase[seg][tap]);
             } else {
               tma_load_2d(sa, &p.tmA[seg], &full_bar[stage], cb * BK, t.m0);
             }
-            tma_load_3d(sb, &p.tmB[seg], &full_bar[stage], cb * BK, tap, t.nt * BN);
+            if (!wres) tma_load_3d(sb, &p.tmB[seg], &full_bar[stage], cb * BK, tap, t.nt * BN);
           } else {
             // the leader's full barrier collects the bytes of both CTAs (tx-count may go negative until it has armed)
-            if (rank == 0) mbar_arrive_expect_tx(&full_bar[stage], 2 * STAGE_BYTES);
+            if (rank == 0) mbar_arrive_expect_tx(&full_bar[stage], 2 * stage_bytes);
             const uint32_t fb = mapa_u32(smem_u32(&full_bar[stage]), 0);
             if (p.spatial) {
               tma_load_5d_2cta(sa, &p.tmA[seg], fb, cb * BK, t.w0 + p.tap_dw[seg][tap],
@@ -411,9 +453,9 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
             } else {
               tma_load_2d_2cta(sa, &p.tmA[seg], fb, cb * BK, t.m0);
             }
-            tma_load_3d_2cta(sb, &p.tmB[seg], fb, cb * BK, tap, t.nt * BN + rank * B_ROWS);
+            if (!wres) tma_load_3d_2cta(sb, &p.tmB[seg], fb, cb * BK, tap, t.nt * BN + rank * B_ROWS);
           }
-          if (++stage == NSTAGE) { stage = 0; phase ^= 1; }
+          if (++stage == nst) { stage = 0; phase ^= 1; }
           if (++cb == p.seg_cb[seg]) {
             cb = 0;
             if (++tap == p.seg_taps[seg]) { tap = 0; ++seg; }
@@ -428,8 +470,12 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
-      for (int work = unit; work < total_work; work += num_units) {
-        const int ks = work / (p.num_pm * p.num_n_tiles);
+      if (wres && n_items > 0) {
+        mbar_wait(wres_bar, 0);
+        tc_fence_after();
+      }
+      for (int it = 0; it < n_items; ++it) {
+        const int ks = wres ? 0 : (unit + it * num_units) / (p.num_pm * p.num_n_tiles);
         const int kb0 = ks * p.kb_per_split;
         const int nkb = min(kb0 + p.kb_per_split, p.kb_total) - kb0;
         mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
@@ -439,8 +485,8 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
           if (elect_one()) {
-            const uint32_t a_addr = smem_u32(smem + stage * STAGE_BYTES);
-            const uint32_t b_addr = a_addr + A_STAGE_BYTES;
+            const uint32_t a_addr = smem_u32(stage_base + stage * stage_bytes);
+            const uint32_t b_addr = wres ? smem_u32(smem + (kb0 + i) * B_STAGE_BYTES) : a_addr + A_STAGE_BYTES;
 #pragma unroll
             for (int k = 0; k < BK / 16; ++k) {
               const uint64_t da = umma_smem_desc_sw128(a_addr + k * 32, 16, 1024);
@@ -457,7 +503,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
             }
           }
           __syncwarp();
-          if (++stage == NSTAGE) { stage = 0; phase ^= 1; }
+          if (++stage == nst) { stage = 0; phase ^= 1; }
         }
         acc ^= 1;
         if (acc == 0) acc_phase ^= 1;
@@ -468,17 +514,21 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
     // Issuing a 128-row TMA box costs the issuing thread several hundred cycles, so it is kept off the epilogue warps:
     // this lane prefetches the residual sub-tiles of its group RES_AHEAD ahead into the ring slots and stores every
     // sub-tile its 128 epilogue threads have marked ready.
-    if (p.staged && unit < total_work && elect_one()) {
+    if (p.staged && n_items > 0 && elect_one()) {
       const int g = warp - 10;
       const bool geglu = (p.flags & B200SD_GEMM_GEGLU) != 0;
+#ifdef B200SD_GEMM_NORES  // diagnostic build only: residual sub-tiles are not loaded (nor added)
+      const bool has_res = false;
+#else
       const bool has_res = (p.flags & B200SD_GEMM_RESIDUAL) != 0;
+#endif
       const int bn_out = geglu ? BN / 2 : BN;
       const int nsub = bn_out / 32;
-      const int total_q = ((total_work - unit + num_units - 1) / num_units) * nsub;
+      const int total_q = n_items * nsub;
       auto locate = [&](int qq, int& sub) {
         const int k = qq / nsub;
         sub = qq - k * nsub;
-        return decode_work(p, unit + k * num_units, rank);
+        return unit_tile(p, unit, num_units, k, rank);
       };
       auto issue_residual = [&](int qq) {
         int sub;
@@ -497,7 +547,11 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
         int sub;
         const TileCoord tt = locate(qq, sub);
         mbar_wait(&ready_bar[slot], (qq / RING_SLOTS) & 1);
+#ifdef B200SD_GEMM_NOSTORE  // diagnostic build only: how fast is everything but the output stores?
+        if (false) {
+#else
         if (tt.mt < p.num_m_tiles) {  // (the phantom tile of an odd pair has nothing to store)
+#endif
           const int col0 = tt.nt * bn_out + sub * 32;
           if (p.spatial) tma_store_4d(&p.tmC, ring + slot * RING_SLOT_BYTES, col0, tt.w0, tt.h0, tt.n0);
           else tma_store_2d(&p.tmC, ring + slot * RING_SLOT_BYTES, col0, tt.m0);
@@ -532,15 +586,19 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
       // ---- staged epilogue: sub-tiles go through an 8-slot swizzled smem ring; the residual sub-tile is prefetched by
       // TMA RES_AHEAD sub-tiles ahead into the slot it is added in, results leave by TMA store (coalesced, OOB clipped).
       const bool geglu = (p.flags & B200SD_GEMM_GEGLU) != 0;
+#ifdef B200SD_GEMM_NORES
+      const bool has_res = false;
+#else
       const bool has_res = (p.flags & B200SD_GEMM_RESIDUAL) != 0;
+#endif
       const bool has_bias = (p.flags & B200SD_GEMM_BIAS) != 0;
       const bool extra = (p.flags & (B200SD_GEMM_BIAS_ROW | B200SD_GEMM_ROWVEC | B200SD_GEMM_SILU | B200SD_GEMM_QUICK_GELU | B200SD_GEMM_GELU)) != 0;
       const int bn_out = geglu ? BN / 2 : BN;
       const int nsub = bn_out / 32;
       const int sw = (r >> 1) & 3;  // SWIZZLE_64B: 16-byte chunk index ^= (row / 2) % 4
       int qbase = 0;
-      for (int work = unit; work < total_work; work += num_units, qbase += nsub) {
-        const TileCoord t = decode_work(p, work, rank);
+      for (int it = 0; it < n_items; ++it, qbase += nsub) {
+        const TileCoord t = unit_tile(p, unit, num_units, it, rank);
         const RowInfo ri = row_info(p, t, r);
         float* bs = bias_s + acc * BN;
         if (has_bias) {  // bias row of this N tile -> smem while the MMAs of the tile are still running
@@ -563,7 +621,13 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
           const int slot = qq % RING_SLOTS;
           uint8_t* srow = ring + slot * RING_SLOT_BYTES + r * 64;
           float v[32];
+#ifdef B200SD_GEMM_NOEPI  // diagnostic build only: the accumulator is neither read nor converted (main-loop rate)
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = 0.f;
+          if (false) {
+#else
           if (geglu) {
+#endif
             uint32_t uh[32], ug[32];
             tmem_ld32(taddr + sub * 32, uh);
             tmem_ld32(taddr + BN / 2 + sub * 32, ug);
@@ -586,12 +650,17 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
               }
               const float bhv[4] = {b_h.x, b_h.y, b_h.z, b_h.w}, bgv[4] = {b_g.x, b_g.y, b_g.z, b_g.w};
 #pragma unroll
-              for (int jj = 0; jj < 4; ++jj) {
+              for (int jj = 0; jj < 4; jj += 2) {
                 const int j = 4 * j4 + jj;
-                v[j] = (__uint_as_float(uh[j]) + bhv[jj]) * gelu_erf_f(__uint_as_float(ug[j]) + bgv[jj]);
+                geglu_f32x2(__uint_as_float(uh[j]) + bhv[jj], __uint_as_float(uh[j + 1]) + bhv[jj + 1],
+                            __uint_as_float(ug[j]) + bgv[jj], __uint_as_float(ug[j + 1]) + bgv[jj + 1], v[j], v[j + 1]);
               }
             }
+#ifdef B200SD_GEMM_NOEPI
+          } else if (false) {
+#else
           } else {
+#endif
             uint32_t u[32];
             tmem_ld32(taddr + sub * 32, u);
             tmem_ld_wait();
@@ -641,8 +710,8 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
       }
     } else {
       // ---- direct epilogue (split-K partials, fp32 / strided / narrow outputs): 16-column chunks alternate between groups
-      for (int work = unit; work < total_work; work += num_units) {
-        const TileCoord t = decode_work(p, work, rank);
+      for (int it = 0; it < n_items; ++it) {
+        const TileCoord t = unit_tile(p, unit, num_units, it, rank);
         const RowInfo ri = row_info(p, t, r);
         const bool tile_exists = t.mt < p.num_m_tiles;
         mbar_wait(&tfull_bar[acc], acc_phase);
@@ -864,9 +933,15 @@ int choose_gemm_tiling(const b200sd_gemm& g, GemmTiling* t) {
     B200SD_CHECK_ARG(g.block_n % 64 == 0 && g.N % g.block_n == 0,
                      "gemm: GEGLU needs N %% block_n == 0 and block_n %% 64 == 0 (N=%d, bn=%d)", g.N, g.block_n);
   }
+  // Weight-resident mode (linears with one short-K segment): a unit keeps its N tile, the tile's weight rows stay in
+  // shared memory for all its M tiles and only activations stream — a k-block then costs max(2*bn, 2.6 * 128).  The
+  // L2 -> SM stream is a chip-wide ceiling (~6300 B/clk over all SMs), so the weight re-reads it removes (39 % of the
+  // ingested rows at 256x160 pair tiles, 50 % at 256x256) are what bounded the K = 320 / 640 linears.
+  static const bool wres_enabled = [] { const char* e = getenv("B200SD_GEMM_WRES"); return !(e && e[0] == '0'); }();
+  const bool wres_shape = wres_enabled && !g.spatial && g.nseg == 1 && g.seg[0].taps == 1 && g.splits <= 1;
   const int bn_cand[5] = {256, 160, 128, 64, 32};
   double best_cost = 1e300;
-  int best_bn = 0, best_ncta = 1, best_s = 1;
+  int best_bn = 0, best_ncta = 1, best_s = 1, best_wres = 0, best_wst = 0, best_upn = 0;
   for (int bi = 0; bi < 5; ++bi) {
     const int bn = bn_cand[bi];
     if (g.block_n ? bn != g.block_n : ((bn == 64 && g.N > 64) || (bn == 32 && g.N > 32) || (geglu && (bn % 64 || g.N % bn))))
@@ -886,7 +961,19 @@ int choose_gemm_tiling(const b200sd_gemm& g, GemmTiling* t) {
         double cost = static_cast<double>(waves) * (per * t_kb + 1500.0);
         if (sp > 1)  // fp32 partials written and re-read by the reduce kernel (+ its launch)
           cost += 4000.0 + static_cast<double>(t->num_m_tiles) * BM * n_tiles * bn * 4.0 * (sp + 1) / (148.0 * 24.0);
-        if (cost < best_cost * (1.0 - 1e-9)) { best_cost = cost; best_bn = bn; best_ncta = ncta; best_s = sp; }
+        if (cost < best_cost * (1.0 - 1e-9)) { best_cost = cost; best_bn = bn; best_ncta = ncta; best_s = sp; best_wres = 0; }
+      }
+      if (wres_shape && n_tiles <= units) {
+        const int b_bytes = kb_total * (bn / ncta) * 128;
+        const int wst = std::min(MAX_STAGES, (gemm_region_bytes(bn) - b_bytes) / A_STAGE_BYTES);
+        const int upn = std::min(units / n_tiles, num_pm);  // work units per N tile
+        if (b_bytes < gemm_region_bytes(bn) && wst >= WRES_MIN_STAGES && num_pm >= 3 * upn) {
+          const long long rounds = (num_pm + upn - 1) / upn;
+          const double cost = 2.6 * kb_total * (bn / ncta) + static_cast<double>(rounds) * (kb_total * std::max(2.0 * bn, 2.6 * 128) + 1500.0);
+          if (cost < best_cost * (1.0 - 1e-9)) {
+            best_cost = cost; best_bn = bn; best_ncta = ncta; best_s = 1; best_wres = 1; best_wst = wst; best_upn = upn;
+          }
+        }
       }
     }
   }
@@ -902,6 +989,11 @@ int choose_gemm_tiling(const b200sd_gemm& g, GemmTiling* t) {
   splits = (kb_total + per - 1) / per;
   t->splits = splits;
   t->kb_per_split = per;
+  t->wres = best_wres; t->wres_stages = best_wst; t->units_per_nt = best_upn;
+  static const bool debug = [] { const char* e = getenv("B200SD_GEMM_DEBUG"); return e && e[0] == '1'; }();
+  if (debug)
+    fprintf(stderr, "gemm tiling: M-tiles %d N %d kb %d -> bn %d ncta %d splits %d wres %d (stages %d, units/nt %d) est %.0f clk\n",
+            t->num_m_tiles, g.N, kb_total, bn, best_ncta, splits, best_wres, best_wst, best_upn, best_cost);
   return 0;
 }
 
@@ -969,6 +1061,7 @@ int plan_gemm(const b200sd_gemm& g, PlannedOp* out) {
   kp.tiles_w = std::max(t.tiles_w, 1); kp.tiles_h = std::max(t.tiles_h, 1); kp.tiles_nb = std::max(t.tiles_nb, 1);
   kp.num_m_tiles = t.num_m_tiles; kp.num_n_tiles = t.num_n_tiles;
   kp.ncta = t.ncta; kp.num_pm = t.num_pm;
+  kp.wres = t.wres; kp.wres_stages = t.wres_stages; kp.units_per_nt = t.units_per_nt;
   {
     long long act_bytes = 0, w_bytes = 0;
     for (int s = 0; s < g.nseg; ++s) {
@@ -1039,6 +1132,7 @@ int plan_gemm(const b200sd_gemm& g, PlannedOp* out) {
   if (rc) { delete pl; return rc; }
   long long total_work = static_cast<long long>(t.num_pm) * t.num_n_tiles * t.splits;
   pl->grid = static_cast<int>(std::min<long long>(total_work, std::max(1, sm_count() / t.ncta))) * t.ncta;
+  if (t.wres) pl->grid = t.units_per_nt * t.num_n_tiles * t.ncta;  // unit u: N tile u % num_n_tiles, M slots u / num_n_tiles + k * units_per_nt
   pl->reduce_grid_x = t.num_m_tiles * t.num_n_tiles;
   pl->reduce_grid_y = (g.flags & B200SD_GEMM_GEGLU) ? bn / 32 : bn / 16;
   out->kind = B200SD_OP_GEMM;

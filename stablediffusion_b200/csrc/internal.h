@@ -69,6 +69,7 @@ struct GemmTiling {
   int num_m_tiles, num_n_tiles;
   int ncta, num_pm;  // CTAs per tile row block (1, or 2 = cta_group::2 pair) and ceil(num_m_tiles / ncta)
   int bw_log2, bh_log2, bn_log2, tiles_w, tiles_h, tiles_nb;
+  int wres, wres_stages, units_per_nt;  // weight-resident mode (gemm.cu): A-only stages, work units per N tile
 };
 int choose_gemm_tiling(const b200sd_gemm& g, GemmTiling* t);
 int groupnorm_chunks(int NB, int HW, int C);
