@@ -6,9 +6,11 @@
 // SM.  Warp roles: warp 0 TMA producer, warp 1 MMA issuer, then one softmax warpgroup per query tile (softmax +
 // correction + epilogue, one query row per thread: the TMEM lane IS the row, so row max / row sum need no shuffles).
 //   S_j = Q K_j^T          tcgen05.mma 128x64x16, K-major operands, into the tile's 64 TMEM columns
-//   P_j = exp2(S_j - m)    registers -> bf16 -> shared memory in the K-major SWIZZLE_128B layout the MMA expects
-//   O  += P_j V_j          tcgen05.mma 128 x round16(d) x 16, V consumed MN-major straight from its [keys, d]
-//                          row layout (no transpose anywhere), O accumulates in TMEM.
+//   P_j = exp2(S_j - m)    registers -> bf16 pairs -> tcgen05.st over columns [0, 32) of S_j (tensor memory)
+//   O  += P_j V_j          tcgen05.mma 128 x round16(d) x 16 with P as the TMEM A operand ("TS" form), V consumed
+//                          MN-major straight from its [keys, d] row layout (no transpose anywhere), O accumulates in TMEM.
+// (Until session 12 P went through a swizzled shared-memory tile — the -DB200SD_ATT_SS=1 build; measured on one box:
+//  d = 64 N = 4096: 276 -> 241 us, d = 160: 22.5 -> 19.4 us, d = 40: 653 -> 650 us, the latter being XU-bound.)
 // Measured on B200 (diagnostic builds, N = 4096, d = 40): with one 128-row tile per CTA and four CTAs per SM the
 // kernel sat on TWO equal ceilings — the softmax chain (710 us with the K/V loads removed) and the L2 -> SM traffic
 // of the K/V blocks (750 us with the softmax removed; 374 us with both removed): every 128 query rows re-read all of
