@@ -942,6 +942,8 @@ int choose_gemm_tiling(const b200sd_gemm& g, GemmTiling* t) {
   const int bn_cand[5] = {256, 160, 128, 64, 32};
   double best_cost = 1e300;
   int best_bn = 0, best_ncta = 1, best_s = 1, best_wres = 0, best_wst = 0, best_upn = 0;
+  double wres_cost[10];
+  int wres_cfg[10][4], wres_n = 0;
   for (int bi = 0; bi < 5; ++bi) {
     const int bn = bn_cand[bi];
     if (g.block_n ? bn != g.block_n : ((bn == 64 && g.N > 64) || (bn == 32 && g.N > 32) || (geglu && (bn % 64 || g.N % bn))))
@@ -959,8 +961,10 @@ int choose_gemm_tiling(const b200sd_gemm& g, GemmTiling* t) {
         if (g.splits <= 0 && (kb_total + per - 1) / per != sp) continue;
         const long long waves = (static_cast<long long>(num_pm) * n_tiles * sp + units - 1) / units;
         double cost = static_cast<double>(waves) * (per * t_kb + 1500.0);
-        if (sp > 1)  // fp32 partials written and re-read by the reduce kernel (+ its launch)
-          cost += 4000.0 + static_cast<double>(t->num_m_tiles) * BM * n_tiles * bn * 4.0 * (sp + 1) / (148.0 * 24.0);
+        if (sp > 1)  // fp32 partials written (row-strided 64-byte pieces) and re-read by the reduce kernel (+ its launch);
+                     // calibrated on tools/sweep_small_gemm.py: the 24 B/clk/SM first assumed made 4096-row convs split
+                     // 4 ways (135 us) when 256x160 pair tiles unsplit run them in 101
+          cost += 4000.0 + static_cast<double>(t->num_m_tiles) * BM * n_tiles * bn * 4.0 * (sp + 1) / (148.0 * 9.6);
         if (cost < best_cost * (1.0 - 1e-9)) { best_cost = cost; best_bn = bn; best_ncta = ncta; best_s = sp; best_wres = 0; }
       }
       if (wres_shape && n_tiles <= units) {
@@ -970,12 +974,21 @@ int choose_gemm_tiling(const b200sd_gemm& g, GemmTiling* t) {
         if (b_bytes < gemm_region_bytes(bn) && wst >= WRES_MIN_STAGES && num_pm >= 3 * upn) {
           const long long rounds = (num_pm + upn - 1) / upn;
           const double cost = 2.6 * kb_total * (bn / ncta) + static_cast<double>(rounds) * (kb_total * std::max(2.0 * bn, 2.6 * 128) + 1500.0);
-          if (cost < best_cost * (1.0 - 1e-9)) {
-            best_cost = cost; best_bn = bn; best_ncta = ncta; best_s = 1; best_wres = 1; best_wst = wst; best_upn = upn;
-          }
+          wres_cost[wres_n] = cost; wres_cfg[wres_n][0] = bn; wres_cfg[wres_n][1] = ncta; wres_cfg[wres_n][2] = wst; wres_cfg[wres_n][3] = upn;
+          ++wres_n;
         }
       }
     }
+  }
+  // the weight-resident form only where the estimate says it clearly pays (measured: 65536x320x320 -5 %, but 16384x640x640
+  // as 256x128 resident tiles 22.2 us vs 20.9 for plain 256x160 pair tiles, at an estimated 7 % advantage)
+  for (int i = 0; i < wres_n; ++i) {
+    if (wres_cost[i] < 0.9 * best_cost && (!best_wres || wres_cost[i] < wres_cost[best_wres - 1])) best_wres = i + 1;
+  }
+  if (best_wres) {
+    const int* c = wres_cfg[best_wres - 1];
+    best_cost = wres_cost[best_wres - 1]; best_bn = c[0]; best_ncta = c[1]; best_s = 1; best_wst = c[2]; best_upn = c[3];
+    best_wres = 1;
   }
   B200SD_CHECK_ARG(best_bn != 0, "gemm: no tile shape fits N=%d block_n=%d cta_pair=%d", g.N, g.block_n, g.cta_pair);
   const int bn = best_bn;

@@ -1,13 +1,19 @@
-"""Summarises an `ncu --metrics gpu__time_duration.sum[,dram__bytes_*] --csv` launch list per kernel name."""
+"""Summarises an `ncu --metrics gpu__time_duration.sum[,dram__bytes_*] --csv` launch list per kernel name.
+`--ours` keeps only this library's kernels (the capture window of `bench.py` starts with the synthetic-weight set-up, which
+runs torch `at::` kernels outside the timed region)."""
 import csv, sys, collections, re
-rows = list(csv.reader(l for l in open(sys.argv[1]) if l.startswith('"')))
+ours = "--ours" in sys.argv
+rows = list(csv.reader(l for l in open([x for x in sys.argv[1:] if not x.startswith("--")][0]) if l.startswith('"')))
 hdr = rows[0]; H = {h: i for i, h in enumerate(hdr)}
 agg = collections.defaultdict(lambda: dict(ids=set(), ns=0.0, rd=0.0, wr=0.0))
 def val(r):
     v = float(r[H["Metric Value"]].replace(",", "")); u = r[H["Metric Unit"]]
     mult = {"ns": 1, "us": 1e3, "ms": 1e6, "s": 1e9, "byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}.get(u, 1)
     return v * mult
+skipped = set()
 for r in rows[1:]:
+    if ours and ("at::" in r[H["Kernel Name"]] or "cub::" in r[H["Kernel Name"]]):
+        skipped.add(r[H["ID"]]); continue
     name = re.sub(r"\(.*", "", r[H["Kernel Name"]]).replace("b200sd::<unnamed>::", "").replace("void ", "")
     a = agg[name]; a["ids"].add(r[H["ID"]]); m = r[H["Metric Name"]]
     if m == "gpu__time_duration.sum": a["ns"] += val(r)
@@ -15,6 +21,7 @@ for r in rows[1:]:
     elif m == "dram__bytes_write.sum": a["wr"] += val(r)
 tot = sum(a["ns"] for a in agg.values())
 print(f"# {len(rows)-1} metric rows, {sum(len(a['ids']) for a in agg.values())} launches, {tot/1e6:.3f} ms of kernel time (ncu per-launch times are cold-cache and serialised)")
+if ours: print(f"# {len(skipped)} torch set-up launches (weight init / packing, outside the timed region) left out")
 print(f"{'kernel':48s} {'launches':>8s} {'total ms':>9s} {'share':>6s} {'avg us':>8s} {'dram R MB/launch':>17s} {'dram W MB/launch':>17s}")
 for name, a in sorted(agg.items(), key=lambda x: -x[1]["ns"]):
     n = len(a["ids"])
