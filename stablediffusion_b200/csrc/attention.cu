@@ -584,9 +584,264 @@ attention_kernel(const __grid_constant__ AttnParams p) {
   if (warp == 1) tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
 }
 
+
+// ======================================================================================================================
+// Short-KV attention (Nkv <= 128, no mask): the cross-attention of every BasicTransformerBlock (77 prompt tokens).
+// The general kernel spends such a launch on per-CTA latency: one 128-row tile per CTA means barrier init, TMEM
+// allocation, a cold Q/K/V load, two S -> softmax -> PV round trips and the teardown in series, ~8 us per CTA for 32 KB of
+// traffic (in-graph, 16x8x4096x77, d = 40: 55 us for 84 MB, 1.5 TB/s).  Here CTAs are persistent over a contiguous range
+// of (batch, head, query tile) items: TMEM and barriers are set up once, K/V of a (batch, head) are loaded once per run of
+// tiles, the next tile's Q is in flight while this one is computed (two Q slots), both key blocks are multiplied up front
+// (S is 128 columns) so the softmax is a single exact pass (max, then exponentials), P goes back over S in tensor memory
+// and PV_i is followed at once by S_{i+1}.
+// ======================================================================================================================
+template <int DPAD>
+struct ShortCfg {
+  static constexpr int DB = DPAD / 64;
+  static constexpr int THREADS = 192;                          // warp 0 TMA, warp 1 MMA, warps 2-5 softmax + epilogue
+  static constexpr int KVSLOTS = DPAD == 64 ? 2 : 1;
+  static constexpr int OCC = DPAD == 64 ? 2 : 1;
+  static constexpr int QT_BYTES = DB * TILE16K;
+  static constexpr int KV_BYTES = 2 * DB * TILE8K;             // K (or V) of one (batch, head): two 64-key blocks
+  static constexpr int TMEM_COLS = 128 + DPAD <= 256 ? 256 : 512;  // S (128) then O
+  static constexpr int SMEM = 2 * QT_BYTES + KVSLOTS * 2 * KV_BYTES + 1024 + 256;
+  static_assert(OCC * (SMEM + 1024) <= 233472 && OCC * TMEM_COLS <= 512, "budget");
+};
+
+template <int DPAD>
+__global__ void __launch_bounds__(ShortCfg<DPAD>::THREADS, ShortCfg<DPAD>::OCC)
+attention_shortkv_kernel(const __grid_constant__ AttnParams p) {
+  using Cfg = ShortCfg<DPAD>;
+  constexpr int DB = Cfg::DB, KVS = Cfg::KVSLOTS;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sQ = smem;                               // [2][QT_BYTES]
+  uint8_t* sK = sQ + 2 * Cfg::QT_BYTES;             // [KVS][KV_BYTES]
+  uint8_t* sV = sK + KVS * Cfg::KV_BYTES;           // [KVS][KV_BYTES]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sV + KVS * Cfg::KV_BYTES);
+  uint64_t* q_full = bars;            // 2
+  uint64_t* q_empty = bars + 2;       // 2
+  uint64_t* kv_full = bars + 4;       // KVS
+  uint64_t* kv_empty = bars + 6;      // KVS
+  uint64_t* s_full = bars + 8;        // S_i complete
+  uint64_t* p_full = bars + 9;        // P_i written (128 arrivals)
+  uint64_t* o_full = bars + 10;       // PV_i complete
+  uint64_t* o_free = bars + 11;       // O_i read out (128 arrivals)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 12);
+
+  pdl_launch_dependents();
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int tiles = (p.Nq + BLK - 1) / BLK;
+  const int total = tiles * p.heads * p.B;
+  const int per_cta = (total + gridDim.x - 1) / gridDim.x;
+  const int item0 = blockIdx.x * per_cta;
+  const int n_items = max(0, min(per_cta, total - item0));
+  const int nkb = p.kv_blocks;                        // 1 or 2
+  const int n1 = nkb > 1 ? ((p.Nkv - KB + 15) / 16) * 16 : 0;  // UMMA N of the second key block
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < 2; ++i) { mbar_init(&q_full[i], 1); mbar_init(&q_empty[i], 1); }
+    for (int i = 0; i < KVS; ++i) { mbar_init(&kv_full[i], 1); mbar_init(&kv_empty[i], 1); }
+    mbar_init(s_full, 1); mbar_init(p_full, 128); mbar_init(o_full, 1); mbar_init(o_free, 128);
+    fence_barrier_init();
+  }
+  if (warp == 1) { tmem_alloc(tmem_slot, Cfg::TMEM_COLS); tmem_relinquish(); }
+  if (warp == 0 && lane == 0) { tma_prefetch_desc(&p.tmQ); tma_prefetch_desc(&p.tmK); tma_prefetch_desc(&p.tmV); }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (elect_one()) {
+      int run = -1, prev_bh = -1;
+      for (int it = 0; it < n_items; ++it) {
+        const int item = item0 + it;
+        const int bh = item / tiles, qt = item - bh * tiles;
+        const int batch = bh / p.heads, head = bh - batch * p.heads;
+        if (bh != prev_bh) {  // new (batch, head): its K and V, once
+          prev_bh = bh; ++run;
+          const int sl = run % KVS;
+          mbar_wait(&kv_empty[sl], ((run / KVS) & 1) ^ 1);
+          mbar_arrive_expect_tx(&kv_full[sl], 2 * nkb * DB * TILE8K);
+          for (int b = 0; b < nkb; ++b)
+            for (int db = 0; db < DB; ++db) {
+              tma_load_4d(sK + sl * Cfg::KV_BYTES + (b * DB + db) * TILE8K, &p.tmK, &kv_full[sl], db * 64, head, b * KB, batch);
+              tma_load_4d(sV + sl * Cfg::KV_BYTES + (b * DB + db) * TILE8K, &p.tmV, &kv_full[sl], db * 64, head, b * KB, batch);
+            }
+        }
+        const int qs = it & 1;
+        mbar_wait(&q_empty[qs], ((it >> 1) & 1) ^ 1);
+        mbar_arrive_expect_tx(&q_full[qs], Cfg::QT_BYTES);
+        for (int db = 0; db < DB; ++db)
+          tma_load_4d(sQ + qs * Cfg::QT_BYTES + db * TILE16K, &p.tmQ, &q_full[qs], db * 64, head, qt * BLK, batch);
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    constexpr int KS_MAX = DPAD / 16;
+    const uint32_t idesc_s0 = umma_idesc_bf16(BLK, KB, 0);
+    const uint32_t idesc_s1 = umma_idesc_bf16(BLK, n1 > 0 ? n1 : 16, 0);
+    const uint32_t idesc_o = umma_idesc_bf16(BLK, p.n_pv, 1);
+    uint64_t dq[KS_MAX], dk[KS_MAX];
+    const uint32_t q_addr = smem_u32(sQ), k_addr = smem_u32(sK), v_addr = smem_u32(sV);
+#pragma unroll
+    for (int ks = 0; ks < KS_MAX; ++ks) {
+      dq[ks] = umma_smem_desc_sw128(q_addr + (ks >> 2) * TILE16K + (ks & 3) * 32, 16, 1024);
+      dk[ks] = umma_smem_desc_sw128(k_addr + (ks >> 2) * TILE8K + (ks & 3) * 32, 16, 1024);
+    }
+    const uint64_t dv0 = umma_smem_desc_sw128(v_addr, TILE8K, 1024);  // MN-major; 16 keys = 2048 bytes further on
+    const int pv_steps = (p.Nkv + 15) / 16;
+    int run = -1, prev_bh = -1;
+    auto item_bh = [&](int it) { return (item0 + it) / tiles; };
+    // S_i = Q_i [K_0 | K_1]^T into columns [0, 64) and [64, 64 + n1)
+    auto issue_S = [&](int it, int sl) {
+      const uint32_t q_off = (it & 1) * Cfg::QT_BYTES, k_off = sl * Cfg::KV_BYTES;
+#pragma unroll
+      for (int ks = 0; ks < KS_MAX; ++ks)
+        if (ks < p.ksteps_qk)
+          umma_bf16_ss(tmem_base, desc_advance(dq[ks], q_off), desc_advance(dk[ks], k_off), idesc_s0, ks != 0 ? 1u : 0u);
+      if (n1 > 0) {
+#pragma unroll
+        for (int ks = 0; ks < KS_MAX; ++ks)
+          if (ks < p.ksteps_qk)
+            umma_bf16_ss(tmem_base + KB, desc_advance(dq[ks], q_off), desc_advance(dk[ks], k_off + DB * TILE8K), idesc_s1,
+                         ks != 0 ? 1u : 0u);
+      }
+      umma_commit(s_full);
+    };
+    auto wait_inputs = [&](int it) {  // Q of item `it` (and K/V when it opens a new run); returns the K/V slot
+      const int bh = item_bh(it);
+      if (bh != prev_bh) {
+        prev_bh = bh; ++run;
+        mbar_wait(&kv_full[run % KVS], (run / KVS) & 1);
+      }
+      mbar_wait(&q_full[it & 1], (it >> 1) & 1);
+      tc_fence_after();
+      return run % KVS;
+    };
+    int sl = 0;
+    if (n_items > 0) {
+      sl = wait_inputs(0);
+      if (elect_one()) issue_S(0, sl);
+      __syncwarp();
+    }
+    for (int it = 0; it < n_items; ++it) {
+      mbar_wait(p_full, it & 1);                      // P_it sits over S_it
+      if (it > 0) mbar_wait(o_free, (it - 1) & 1);    // O_{it-1} has been read out
+      tc_fence_after();
+      const bool last_of_run = it + 1 >= n_items || item_bh(it + 1) != item_bh(it);
+      if (elect_one()) {
+        const uint32_t v_off = sl * Cfg::KV_BYTES;
+        for (int ks = 0; ks < pv_steps; ++ks) {
+          // key group ks: block ks / 4 (KV_BYTES / 2 apart), 16 keys = 2048 bytes within the block
+          const uint32_t off = v_off + (ks >> 2) * (DB * TILE8K) + (ks & 3) * 2048;
+          umma_bf16_ts(tmem_base + 128, tmem_base + ks * 8, desc_advance(dv0, off), idesc_o, ks != 0 ? 1u : 0u);
+        }
+        umma_commit(o_full);
+        umma_commit(&q_empty[it & 1]);
+        if (last_of_run) umma_commit(&kv_empty[sl]);
+      }
+      __syncwarp();
+      if (it + 1 < n_items) {
+        sl = wait_inputs(it + 1);
+        if (elect_one()) issue_S(it + 1, sl);   // after PV_it in issue order: it cannot overwrite P_it early
+        __syncwarp();
+      }
+    }
+  } else {
+    // ===================== softmax + epilogue: thread <-> query row =====================
+    const int q = warp & 3;
+    const int r = q * 32 + lane;
+    const uint32_t s_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
+    const uint32_t o_addr = s_addr + 128;
+    const int nch = (p.Nkv + 31) / 32;  // 32-key chunks that hold valid keys
+    for (int it = 0; it < n_items; ++it) {
+      const int item = item0 + it;
+      const int bh = item / tiles, qt = item - bh * tiles;
+      const int batch = bh / p.heads, head = bh - batch * p.heads;
+      mbar_wait(s_full, it & 1);
+      tc_fence_after();
+      uint32_t u[32];
+      float mx = -INFINITY;
+      for (int c = 0; c < nch; ++c) {
+        tmem_ld32(s_addr + c * 32, u);
+        tmem_ld_wait();
+        if (c * 32 + 32 <= p.Nkv) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(u[i]));
+        } else {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) if (c * 32 + i < p.Nkv) mx = fmaxf(mx, __uint_as_float(u[i]));
+        }
+      }
+      const float m_ref = mx * p.scale_log2;
+      const uint64_t sc2 = pack_f32x2(__float_as_uint(p.scale_log2), __float_as_uint(p.scale_log2));
+      const uint64_t nm2 = pack_f32x2(__float_as_uint(-m_ref), __float_as_uint(-m_ref));
+      uint64_t acc = 0;
+      for (int c = 0; c < nch; ++c) {
+        tmem_ld32(s_addr + c * 32, u);
+        tmem_ld_wait();
+        uint32_t pk[16];
+        const bool full = c * 32 + 32 <= p.Nkv;
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          float x0, x1;
+          unpack_f32x2(fma_f32x2(pack_f32x2(u[2 * i], u[2 * i + 1]), sc2, nm2), x0, x1);
+          float p0 = ex2_approx(x0), p1 = ex2_approx(x1);
+          if (!full) {
+            if (c * 32 + 2 * i >= p.Nkv) p0 = 0.f;
+            if (c * 32 + 2 * i + 1 >= p.Nkv) p1 = 0.f;
+          }
+          acc = add_f32x2(acc, pack_f32x2(__float_as_uint(p0), __float_as_uint(p1)));
+          pk[i] = pack_bf16x2(p0, p1);
+        }
+        tmem_st16(s_addr + c * 16, pk);  // P chunk c over columns already consumed (16c + 16 <= 32c + 32)
+      }
+      tmem_st_wait();
+      tc_fence_before();
+      mbar_arrive(p_full);
+      float l0, l1;
+      unpack_f32x2(acc, l0, l1);
+      const float inv_l = 1.0f / (l0 + l1);
+      // ---- epilogue: O / l -> bf16 -> global ----
+      mbar_wait(o_full, it & 1);
+      tc_fence_after();
+      const int qrow = qt * BLK + r;
+      bf16* orow = p.out + (static_cast<long long>(batch) * p.Nq + qrow) * p.ldo + head * p.d;
+#pragma unroll 1
+      for (int c = 0; c < p.n_pv / 16; ++c) {
+        uint32_t o[16];
+        tmem_ld16(o_addr + c * 16, o);
+        tmem_ld_wait();
+        if (c == p.n_pv / 16 - 1) {  // O is in registers: PV of the next item may overwrite it
+          tc_fence_before();
+          mbar_arrive(o_free);
+        }
+        if (qrow < p.Nq) {
+          uint32_t w[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i)
+            w[i] = pack_bf16x2(__uint_as_float(o[2 * i]) * inv_l, __uint_as_float(o[2 * i + 1]) * inv_l);
+          if (c * 16 + 8 <= p.d) *reinterpret_cast<uint4*>(orow + c * 16) = make_uint4(w[0], w[1], w[2], w[3]);
+          if (c * 16 + 16 <= p.d) *reinterpret_cast<uint4*>(orow + c * 16 + 8) = make_uint4(w[4], w[5], w[6], w[7]);
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  if (warp == 1) tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+}
+
 struct AttnPlan {
   AttnParams kp;
-  int dpad, nq;
+  int dpad, nq;  // nq == 0: the short-KV kernel
   dim3 grid;
 };
 
@@ -619,8 +874,36 @@ int dispatch_attention(int dpad, int nq, const AttnPlan* pl, cudaStream_t s) {
 #undef B200SD_ATT_CASE
   return fail(B200SD_ERR_UNSUPPORTED, "attention: padded head dim %d with %d query tiles per CTA unsupported", dpad, nq);
 }
+template <int DPAD>
+int prepare_shortkv_t() {
+  static bool attr_set = false;
+  if (!attr_set) {
+    B200SD_CUDA(cudaFuncSetAttribute(attention_shortkv_kernel<DPAD>, cudaFuncAttributeMaxDynamicSharedMemorySize, ShortCfg<DPAD>::SMEM));
+    attr_set = true;
+  }
+  return 0;
+}
+template <bool LAUNCH>
+int dispatch_shortkv(int dpad, const AttnPlan* pl, cudaStream_t s) {
+#define B200SD_ATT_SHORT_CASE(D)                                                                                        \
+  if (dpad == D) {                                                                                                      \
+    if constexpr (LAUNCH) {                                                                                             \
+      B200SD_CUDA(launch_kernel(attention_shortkv_kernel<D>, pl->grid, dim3(ShortCfg<D>::THREADS), ShortCfg<D>::SMEM, s, 1, pl->kp)); \
+      return 0;                                                                                                         \
+    } else {                                                                                                            \
+      return prepare_shortkv_t<D>();                                                                                    \
+    }                                                                                                                   \
+  }
+  B200SD_ATT_SHORT_CASE(64)
+  B200SD_ATT_SHORT_CASE(128)
+  B200SD_ATT_SHORT_CASE(192)
+#undef B200SD_ATT_SHORT_CASE
+  return fail(B200SD_ERR_UNSUPPORTED, "attention: padded head dim %d unsupported", dpad);
+}
+int shortkv_occupancy(int dpad) { return dpad == 64 ? 2 : 1; }
 int launch_attention(const void* plan, cudaStream_t s) {
   const AttnPlan& pl = *static_cast<const AttnPlan*>(plan);
+  if (pl.nq == 0) return dispatch_shortkv<true>(pl.dpad, &pl, s);
   return dispatch_attention<true>(pl.dpad, pl.nq, &pl, s);
 }
 int wide_tiles(int dpad) { return dpad == 64 ? 4 : 2; }
@@ -683,10 +966,18 @@ int plan_attention(const b200sd_attention& a, PlannedOp* out) {
   kp.scale_log2 = a.scale * 1.4426950408889634f;
   kp.causal = a.causal ? 1 : 0;
   pl->dpad = (a.d + 63) / 64 * 64;
-  pl->nq = choose_tiles(pl->dpad, a.B, a.heads, a.Nq, kp.kv_blocks);
-  const int rows_per_cta = BLK * pl->nq;
-  pl->grid = dim3((a.Nq + rows_per_cta - 1) / rows_per_cta, a.heads, a.B);
-  rc = dispatch_attention<false>(pl->dpad, pl->nq, nullptr, nullptr);
+  static const bool shortkv_on = [] { const char* e = std::getenv("B200SD_ATT_SHORTKV"); return !(e && e[0] == '0'); }();
+  if (shortkv_on && !a.causal && a.Nkv <= 2 * KB) {
+    pl->nq = 0;
+    const long long items = static_cast<long long>((a.Nq + BLK - 1) / BLK) * a.heads * a.B;
+    pl->grid = dim3(static_cast<unsigned>(std::min<long long>(items, static_cast<long long>(sm_count()) * shortkv_occupancy(pl->dpad))));
+    rc = dispatch_shortkv<false>(pl->dpad, nullptr, nullptr);
+  } else {
+    pl->nq = choose_tiles(pl->dpad, a.B, a.heads, a.Nq, kp.kv_blocks);
+    const int rows_per_cta = BLK * pl->nq;
+    pl->grid = dim3((a.Nq + rows_per_cta - 1) / rows_per_cta, a.heads, a.B);
+    rc = dispatch_attention<false>(pl->dpad, pl->nq, nullptr, nullptr);
+  }
   if (rc) { delete pl; return rc; }
   out->kind = B200SD_OP_ATTENTION;
   out->plan = pl;
