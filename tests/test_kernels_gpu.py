@@ -495,6 +495,32 @@ def test_embed_bit_exact(cuda_device):
     assert torch.equal(out, ref)
 
 
+@pytest.mark.parametrize("B,heads,Nq,Nkv,d", [
+    (3, 2, 200, 64, 64),     # one key block exactly
+    (2, 3, 130, 128, 40),    # two full key blocks
+    (1, 2, 300, 65, 160),    # second block holds one key
+    (2, 2, 128, 16, 80),
+    (5, 8, 64, 77, 160),     # one query tile per (batch, head): K/V reloaded for every item (single K/V slot)
+    (1, 40, 384, 100, 64),   # more (batch, head) runs than CTAs need: several runs per CTA through both K/V slots
+    (16, 8, 1024, 77, 40),   # more items than resident CTAs: the persistent loop proper
+    (1, 1, 100, 1, 40),      # a single key: softmax is 1 everywhere, O = V
+])
+def test_attention_short_kv(cuda_device, B, heads, Nq, Nkv, d):
+    """The persistent short-KV kernel (Nkv <= 128, the cross-attention path): key counts around the block boundaries,
+    ragged query tiles, contiguous item ranges that cross (batch, head) runs."""
+    dev = cuda_device
+    C = heads * d
+    q = _bf(_randn((B, Nq, C), dev, 21))
+    k = _bf(_randn((B, Nkv, C), dev, 22))
+    v = _bf(_randn((B, Nkv, C), dev, 23))
+    b = _builder(dev)
+    out = b.attention(q, k, v, heads, d, d ** -0.5)
+    _run(b)
+    sp = lambda t, n: t.float().view(B, n, heads, d).transpose(1, 2)
+    ref = F.scaled_dot_product_attention(sp(q, Nq), sp(k, Nkv), sp(v, Nkv)).transpose(1, 2).reshape(B, Nq, C)
+    _check(out, ref, rtol=2 ** -6, name=f"short-KV attention Nkv={Nkv} d={d}")
+
+
 @pytest.mark.parametrize("nq_override", ["1", "wide"])
 @pytest.mark.parametrize("B,heads,Nq,Nkv,d", [(1, 2, 600, 600, 64), (2, 3, 130, 333, 40), (1, 2, 1000, 77, 80), (1, 1, 513, 513, 160),
                                               (2, 2, 384, 4096, 40)])
