@@ -23,6 +23,9 @@ import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+# stdout carries exactly ONE JSON line: NCCL's own banner ("NCCL version ...", printed to stdout when NCCL_DEBUG is set in
+# the environment, as it is on the GPU boxes) goes to stderr
+os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
 
 WORKLOADS = {
     # name: (model_type, H, W, batch per GPU, scheduler, sampler steps, guidance)
