@@ -8,7 +8,7 @@ from stablediffusion_b200.lowering import Builder
 
 ap = argparse.ArgumentParser()
 ap.add_argument("--copies", type=int, default=8); ap.add_argument("--reps", type=int, default=10)
-ap.add_argument("--out", default="gpurun_out/sweep_small_gemm.txt")
+ap.add_argument("--out", default="gpurun_out/sweep_small_gemm.txt"); ap.add_argument("--set", default="small", choices=["small", "n640"])
 a = ap.parse_args()
 dev = torch.device("cuda:0")
 bf = lambda *s: (torch.randn(*s, device=dev) * 0.5).to(torch.bfloat16)
@@ -35,7 +35,12 @@ out = []
 def emit(line):
     print(line, flush=True); out.append(line)
 
-lin_shapes = [(4096, 1280, 1280, True), (16384, 640, 640, True), (4096, 1280, 5120, True), (4096, 3840, 1280, False), (1024, 1280, 1280, True),
+if a.set == "n640":  # the 32x32 level (N = 640 = 2.5 tiles of 256): is 4 x 160 better than 3 x 256?
+    lin_shapes = [(16384, 640, 640, True), (16384, 640, 2560, True), (16384, 1920, 640, False)]
+    conv_shapes_sel = [(16, 32, 640, 640), (16, 32, 1280, 640), (16, 32, 960, 640), (16, 64, 320, 320), (16, 64, 640, 320)]
+else:
+    conv_shapes_sel = None
+lin_shapes = lin_shapes if a.set == "n640" else [(4096, 1280, 1280, True), (16384, 640, 640, True), (4096, 1280, 5120, True), (4096, 3840, 1280, False), (1024, 1280, 1280, True),
               (16384, 1920, 640, False), (16384, 640, 2560, True)]
 for M, N, K, res in lin_shapes:
     xs = [bf(M, K) for _ in range(a.copies)]; w = bf(N, K); r = bf(M, N) if res else None
@@ -48,9 +53,9 @@ for M, N, K, res in lin_shapes:
     t = time_prog(mk())
     emit(f"lin {M}x{N}x{K} res={int(res)} chooser: {t:7.1f} us {flops / t / 1e6:7.0f} TFLOP/s")
     for bn in (128, 160, 256):
-        if N % bn and bn != 160: continue
+        if N % bn and bn not in (160, 256): continue
         for pair in (1, 2):
-            for sp in (1, 2, 3, 4):
+            for sp in ((1,) if a.set == "n640" else (1, 2, 3, 4)):
                 t = time_prog(mk(bn, pair, sp))
                 if t is not None:
                     emit(f"    bn={bn} pair={pair} splits={sp}: {t:7.1f} us {flops / t / 1e6:7.0f} TFLOP/s")
@@ -64,7 +69,7 @@ for M, N, K, res in lin_shapes:
     t = e0.elapsed_time(e1) * 1e3 / (a.reps * a.copies)
     emit(f"    cuBLAS (no epilogue, eager launches): {t:7.1f} us {flops / t / 1e6:7.0f} TFLOP/s")
 
-conv_shapes = [(16, 8, 1280, 1280), (16, 16, 1280, 1280), (16, 16, 640, 1280), (16, 8, 2560, 1280)]
+conv_shapes = conv_shapes_sel or [(16, 8, 1280, 1280), (16, 16, 1280, 1280), (16, 16, 640, 1280), (16, 8, 2560, 1280)]
 for NB, H, C, Co in conv_shapes:
     xs = [bf(NB, H, H, C) for _ in range(a.copies)]; w = bf(Co, 9 * C)
     it = iter(range(10 ** 9))
@@ -77,7 +82,7 @@ for NB, H, C, Co in conv_shapes:
     emit(f"conv {NB}x{H}x{H} {C}->{Co} chooser: {t:7.1f} us {flops / t / 1e6:7.0f} TFLOP/s")
     for bn in (128, 160, 256):
         for pair in (1, 2):
-            for sp in (1, 2, 3, 4, 6, 8):
+            for sp in ((1,) if a.set == "n640" else (1, 2, 3, 4, 6, 8)):
                 t = time_prog(mkc(bn, pair, sp))
                 if t is not None:
                     emit(f"    bn={bn} pair={pair} splits={sp}: {t:7.1f} us {flops / t / 1e6:7.0f} TFLOP/s")
