@@ -23,9 +23,26 @@ import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
-# stdout carries exactly ONE JSON line: NCCL's own banner ("NCCL version ...", printed to stdout when NCCL_DEBUG is set in
-# the environment, as it is on the GPU boxes) goes to stderr
-os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+# stdout carries exactly ONE JSON line.  Native libraries write to file descriptor 1 behind Python's back (NCCL prints its
+# "NCCL version ..." banner with printf when NCCL_DEBUG is set in the environment, as it is on the GPU boxes; NCCL_DEBUG_FILE
+# does not catch it), so main() points descriptor 1 at stderr for the whole run and the result line is written to the saved
+# original descriptor.
+_RESULT_FD = None
+
+
+def capture_stdout() -> None:
+    global _RESULT_FD
+    sys.stdout.flush()
+    _RESULT_FD = os.dup(1)
+    os.dup2(2, 1)
+
+
+def emit_result(line: dict) -> None:
+    sys.stdout.flush()
+    if _RESULT_FD is None:
+        print(json.dumps(line), flush=True)
+    else:
+        os.write(_RESULT_FD, (json.dumps(line) + "\n").encode())
 
 WORKLOADS = {
     # name: (model_type, H, W, batch per GPU, scheduler, sampler steps, guidance)
@@ -163,7 +180,7 @@ def run_reference(args, wl, rank):
             "dtype": "f32", "data": "synthetic prompts (random embeddings), random-init weights",
             "config": {"workload": wl, "note": "CPU oracle of the reference's diffusers path; per-image rate (batch 1)"},
             "cpu_baseline": cb, "e2e": {"value": v, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line))
+    emit_result(line)
 
 
 def run_b200(args, wl, rank, world, local_rank):
@@ -284,7 +301,7 @@ def run_b200(args, wl, rank, world, local_rank):
                         "d2h_bytes_per_step": himg.numel() * himg.element_size()},
                 "gpu_launches": launches_per_job * args.steps, "launches_per_sampler_step": eng.launches_per_step,
                 "clocks": clk.summary(), "roofline": roof, "cpu_baseline": cb}
-        print(json.dumps(line))
+        emit_result(line)
     if world > 1:
         dist.destroy_process_group()
 
@@ -298,6 +315,7 @@ def main():
     ap.add_argument("--workload", default="sd15_512_b8_ddim50_cfg", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
+    capture_stdout()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
