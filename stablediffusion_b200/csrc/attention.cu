@@ -126,6 +126,32 @@ __device__ __forceinline__ uint64_t add_f32x2(uint64_t a, uint64_t b) {
   asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
   return d;
 }
+// 2^x for a PAIR of scores on the FMA pipe (no MUFU): round-to-nearest split x = n + f with the 1.5 * 2^23 trick, cubic
+// minimax for 2^f on [-0.5, 0.5] (relative error 7.5e-5, a 50th of a bf16 ulp of P), n added into the exponent field.
+// The softmax of the d = 40 heads is bound by the XU pipe (16 ex2 per clock and SM); with the packed-pair arithmetic the
+// warps' issue slots are only ~40 % used, so every B200SD_ATT_POLY_EVERY-th pair takes this path instead (0 = none).
+// Measured (tools/ab_attention_poly.sh, N = 4096, d = 40, same box): none 637.8 us, every 8th 613.4, every 4th 640.0, every
+// 3rd 654.3, every 2nd 697.3 — a pair costs ~10 issue slots on this path, so beyond one in eight the issue slots become the
+// bound the MUFU pipe was.
+#ifndef B200SD_ATT_POLY_EVERY
+#define B200SD_ATT_POLY_EVERY 8
+#endif
+__device__ __forceinline__ void ex2_poly_f32x2(float x0, float x1, float& p0, float& p1) {
+  const uint64_t X = pack_f32x2(__float_as_uint(fmaxf(x0, -125.0f)), __float_as_uint(fmaxf(x1, -125.0f)));
+  const uint64_t MAGIC = pack_f32x2(0x4B400000u, 0x4B400000u);    // 12582912.0f
+  const uint64_t NMAGIC = pack_f32x2(0xCB400000u, 0xCB400000u);
+  const uint64_t XR = add_f32x2(X, MAGIC);                          // low mantissa bits = round(x)
+  const uint64_t N = add_f32x2(XR, NMAGIC);
+  const uint64_t F = fma_f32x2(N, pack_f32x2(0xBF800000u, 0xBF800000u), X);  // x - n
+  uint64_t P = fma_f32x2(pack_f32x2(__float_as_uint(0.05517115f), __float_as_uint(0.05517115f)), F,
+                         pack_f32x2(__float_as_uint(0.24260987f), __float_as_uint(0.24260987f)));
+  P = fma_f32x2(P, F, pack_f32x2(__float_as_uint(0.69326097f), __float_as_uint(0.69326097f)));
+  P = fma_f32x2(P, F, pack_f32x2(__float_as_uint(0.99992818f), __float_as_uint(0.99992818f)));
+  const uint32_t lo = static_cast<uint32_t>(P) + (static_cast<uint32_t>(XR) << 23);
+  const uint32_t hi = static_cast<uint32_t>(P >> 32) + (static_cast<uint32_t>(XR >> 32) << 23);
+  p0 = __uint_as_float(lo);
+  p1 = __uint_as_float(hi);
+}
 __device__ __forceinline__ void sts128(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
   asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
@@ -475,8 +501,14 @@ attention_kernel(const __grid_constant__ AttnParams p) {
         for (int i = 0; i < 16; ++i) {
           float x0, x1;
           unpack_f32x2(fma_f32x2(pack_f32x2(u[2 * i], u[2 * i + 1]), sc2, nm2), x0, x1);
-          float p0 = ex2_approx(x0);
-          float p1 = ex2_approx(x1);
+          float p0, p1;
+          constexpr int PE = B200SD_ATT_POLY_EVERY > 0 ? B200SD_ATT_POLY_EVERY : 1;
+          if (B200SD_ATT_POLY_EVERY > 0 && i % PE == PE - 1) {
+            ex2_poly_f32x2(x0, x1, p0, p1);
+          } else {
+            p0 = ex2_approx(x0);
+            p1 = ex2_approx(x1);
+          }
           if (MASKED) {
             if (c * 32 + 2 * i >= lim) p0 = 0.f;
             if (c * 32 + 2 * i + 1 >= lim) p1 = 0.f;
