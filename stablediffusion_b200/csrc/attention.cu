@@ -503,7 +503,7 @@ attention_kernel(const __grid_constant__ AttnParams p) {
           unpack_f32x2(fma_f32x2(pack_f32x2(u[2 * i], u[2 * i + 1]), sc2, nm2), x0, x1);
           float p0, p1;
           constexpr int PE = B200SD_ATT_POLY_EVERY > 0 ? B200SD_ATT_POLY_EVERY : 1;
-          if (B200SD_ATT_POLY_EVERY > 0 && i % PE == PE - 1) {
+          if (B200SD_ATT_POLY_EVERY > 0 && DPAD == 64 && i % PE == PE - 1) {  // (d > 64: two tiles per CTA, not XU-bound: 93.2 vs 91.1 us)
             ex2_poly_f32x2(x0, x1, p0, p1);
           } else {
             p0 = ex2_approx(x0);
