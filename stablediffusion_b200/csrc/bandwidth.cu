@@ -352,6 +352,9 @@ int launch_groupnorm(const void* plan, cudaStream_t s) {
 // ======================================================================================================
 // LayerNorm: warp per row, the row lives in registers (C <= 2048), two-pass mean/variance like torch.
 // Reference: BasicTransformerBlock.norm1/2/3 (eps 1e-5, affine).  Algorithmic bytes = 1R + 1W.
+// (A persistent variant with the next row group's loads in flight won on cold inputs — 65536x320 in-graph from HBM: 21.2 ->
+// 19.2 us — but lost inside the sampler step, where the input was just written and sits in L2 and its 128 registers halve the
+// occupancy of the small grids: 22.6 -> 23.5 us at 65536x320, 12.2 -> 14.0 at 4096x1280.  One-shot CTAs kept.)
 // ======================================================================================================
 struct LNParams {
   const bf16* x; bf16* out; long long ldx, ldo; int rows, C; float eps; const float* gamma; const float* beta;
@@ -366,76 +369,58 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const LNParams p, int lp
   const int lane = threadIdx.x & 31;
   const int rows_per_warp = 32 / lpr;
   const int sub = lane / lpr, sl = lane % lpr;
+  const int warp_global = blockIdx.x * 8 + (threadIdx.x >> 5);
+  const int row = warp_global * rows_per_warp + sub;
+  const bool active = row < p.rows;
   const int nvec = p.C >> 3;
-  const int ngroups = (p.rows + rows_per_warp - 1) / rows_per_warp;  // a warp normalises one group of rows at a time
-  const int total_warps = gridDim.x * 8;
-  // Persistent warps: the next group's row is already in flight while this one is reduced and stored (one-shot CTAs left
-  // the memory pipe idle between a CTA's loads and its successor's: 3.96 TB/s of R+W at 65536x320).
-  auto load_group = [&](int grp, uint4 (&raw)[VPL]) {
-    const int row = grp * rows_per_warp + sub;
-    const bf16* xr = p.x + static_cast<long long>(row < p.rows ? row : 0) * p.ldx;
-#pragma unroll
-    for (int i = 0; i < VPL; ++i) {
-      const int vi = sl + lpr * i;
-      raw[i] = (row < p.rows && vi < nvec) ? ldg_stream(xr + vi * 8) : make_uint4(0, 0, 0, 0);
-    }
-  };
-  int grp = blockIdx.x * 8 + (threadIdx.x >> 5);
+  const bf16* xr = p.x + static_cast<long long>(active ? row : 0) * p.ldx;
   uint4 raw[VPL];
-  if (grp < ngroups) load_group(grp, raw);
-  for (; grp < ngroups; grp += total_warps) {
-    uint4 nxt[VPL];
-    const bool more = grp + total_warps < ngroups;
-    if (more) load_group(grp + total_warps, nxt);
-    const int row = grp * rows_per_warp + sub;
-    const bool active = row < p.rows;
-    float v[VPL][8];
-    float sum = 0.f;
 #pragma unroll
-    for (int i = 0; i < VPL; ++i) {
-      uint32_t w[4] = {raw[i].x, raw[i].y, raw[i].z, raw[i].w};
+  for (int i = 0; i < VPL; ++i) {
+    const int vi = sl + lpr * i;
+    raw[i] = (active && vi < nvec) ? ldg_stream(xr + vi * 8) : make_uint4(0, 0, 0, 0);
+  }
+  float v[VPL][8];
+  float sum = 0.f;
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        float2 f = unpack_bf16x2(w[j]);
-        v[i][2 * j] = f.x; v[i][2 * j + 1] = f.y;
-        sum += f.x + f.y;
-      }
+  for (int i = 0; i < VPL; ++i) {
+    uint32_t w[4] = {raw[i].x, raw[i].y, raw[i].z, raw[i].w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      float2 f = unpack_bf16x2(w[j]);
+      v[i][2 * j] = f.x; v[i][2 * j + 1] = f.y;
+      sum += f.x + f.y;
     }
-    for (int o = lpr >> 1; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
-    const float mean = sum / static_cast<float>(p.C);
-    float sq = 0.f;
+  }
+  for (int o = lpr >> 1; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+  const float mean = sum / static_cast<float>(p.C);
+  float sq = 0.f;
 #pragma unroll
-    for (int i = 0; i < VPL; ++i) {
-      if (sl + lpr * i < nvec) {
+  for (int i = 0; i < VPL; ++i) {
+    if (sl + lpr * i < nvec) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j) { float d = v[i][j] - mean; sq += d * d; }
-      }
+      for (int j = 0; j < 8; ++j) { float d = v[i][j] - mean; sq += d * d; }
     }
-    for (int o = lpr >> 1; o > 0; o >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, o);
-    const float rstd = rsqrtf(sq / static_cast<float>(p.C) + p.eps);
-    if (active) {
-      bf16* orow = p.out + static_cast<long long>(row) * p.ldo;
+  }
+  for (int o = lpr >> 1; o > 0; o >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, o);
+  const float rstd = rsqrtf(sq / static_cast<float>(p.C) + p.eps);
+  if (!active) return;
+  bf16* orow = p.out + static_cast<long long>(row) * p.ldo;
 #pragma unroll
-      for (int i = 0; i < VPL; ++i) {
-        const int vi = sl + lpr * i;
-        if (vi < nvec) {
-          const float4* g4 = reinterpret_cast<const float4*>(p.gamma + vi * 8);
-          const float4* b4 = reinterpret_cast<const float4*>(p.beta + vi * 8);
-          float4 g0 = __ldg(g4), g1 = __ldg(g4 + 1), b0 = __ldg(b4), b1 = __ldg(b4 + 1);
-          float g[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
-          float b[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
-          uint32_t o[4];
+  for (int i = 0; i < VPL; ++i) {
+    const int vi = sl + lpr * i;
+    if (vi < nvec) {
+      const float4* g4 = reinterpret_cast<const float4*>(p.gamma + vi * 8);
+      const float4* b4 = reinterpret_cast<const float4*>(p.beta + vi * 8);
+      float4 g0 = __ldg(g4), g1 = __ldg(g4 + 1), b0 = __ldg(b4), b1 = __ldg(b4 + 1);
+      float g[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+      float b[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+      uint32_t o[4];
 #pragma unroll
-          for (int j = 0; j < 4; ++j)
-            o[j] = pack_bf16x2((v[i][2 * j] - mean) * rstd * g[2 * j] + b[2 * j],
-                               (v[i][2 * j + 1] - mean) * rstd * g[2 * j + 1] + b[2 * j + 1]);
-          *reinterpret_cast<uint4*>(orow + vi * 8) = make_uint4(o[0], o[1], o[2], o[3]);
-        }
-      }
-    }
-    if (more) {
-#pragma unroll
-      for (int i = 0; i < VPL; ++i) raw[i] = nxt[i];
+      for (int j = 0; j < 4; ++j)
+        o[j] = pack_bf16x2((v[i][2 * j] - mean) * rstd * g[2 * j] + b[2 * j],
+                           (v[i][2 * j + 1] - mean) * rstd * g[2 * j + 1] + b[2 * j + 1]);
+      *reinterpret_cast<uint4*>(orow + vi * 8) = make_uint4(o[0], o[1], o[2], o[3]);
     }
   }
 }
@@ -448,11 +433,7 @@ int launch_layernorm(const void* plan, cudaStream_t s) {
   }
   const int vpl = (nvec + lpr - 1) / lpr;
   const int rows_per_cta = 8 * (32 / lpr);
-  // Large inputs run as persistent CTAs, two per SM (what 128 registers allow; in-graph at 65536x320: 19.2 us vs 21.2 for
-  // one-shot CTAs, 1 / 3 / 4 / 8 per SM: 23.7 / 23.7 / 21.0 / 23.8); below ~6 CTAs per SM the one-shot grid is faster.
-  static const int ln_ctas = [] { const char* e = getenv("B200SD_LN_CTAS_PER_SM"); return e ? std::max(1, atoi(e)) : 2; }();
-  int grid = (p.rows + rows_per_cta - 1) / rows_per_cta;
-  if (grid > 6 * sm_count()) grid = sm_count() * ln_ctas;
+  const int grid = (p.rows + rows_per_cta - 1) / rows_per_cta;
   switch (vpl) {
     case 1: B200SD_CUDA(launch_kernel(layernorm_kernel<1>, dim3(grid), dim3(256), 0, s, 1, p, lpr)); break;
     case 2: B200SD_CUDA(launch_kernel(layernorm_kernel<2>, dim3(grid), dim3(256), 0, s, 1, p, lpr)); break;
