@@ -146,14 +146,29 @@ __device__ __forceinline__ void fence_barrier_init() {
 __device__ __forceinline__ void fence_proxy_async_smem() {
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 }
+// Suspend-time hint of mbarrier.try_wait in ns (0: hardware default).  A waiting thread sleeps until the phase completes or the
+// hint expires; with the default the idle epilogue / softmax warps wake up often enough to show in the power draw, and the
+// sampler step runs under the software power cap: same box, back to back (tools/ab_wait_hint.sh): 9.037 / 9.024 images/s with
+// the default, 9.097 with 20 us, 9.089 with 1 ms.
+#ifndef B200SD_WAIT_HINT_NS
+#define B200SD_WAIT_HINT_NS 20000
+#endif
 __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
   uint32_t ok;
   asm volatile(
       "{\n\t.reg .pred p;\n\t"
+#if B200SD_WAIT_HINT_NS > 0
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+#else
       "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+#endif
       "selp.b32 %0, 1, 0, p;\n\t}"
       : "=r"(ok)
+#if B200SD_WAIT_HINT_NS > 0
+      : "r"(smem_u32(bar)), "r"(parity), "r"(static_cast<uint32_t>(B200SD_WAIT_HINT_NS))
+#else
       : "r"(smem_u32(bar)), "r"(parity)
+#endif
       : "memory");
   return ok != 0;
 }
