@@ -138,6 +138,46 @@ def test_gemm_geglu(cuda_device, M, C, splits, cta_pair):
     _check(out, h * F.gelu(g), name="geglu")
 
 
+@pytest.mark.parametrize("cta_pair", [0, 1])
+@pytest.mark.parametrize("M,N,K,res", [(65536, 320, 320, True), (40200, 320, 320, True), (65536, 320, 192, False)])
+def test_gemm_weight_resident(cuda_device, M, N, K, res, cta_pair):
+    """Shapes the tiling chooser runs in the weight-resident mode (short K, many M tiles per N tile: the level-0 linears of a
+    batch-8 step; `B200SD_GEMM_DEBUG=1` prints the choice): a work unit keeps one N tile, its weight rows stay in shared memory.
+    40200 rows = 315 tiles: an odd tile count (phantom tile of the last CTA pair) and a ragged last tile."""
+    dev = cuda_device
+    a = _bf(_randn((M, K), dev, 1))
+    w = _bf(_randn((N, K), dev, 2, 1.0 / math.sqrt(K)))
+    bias = _randn((N,), dev, 3)
+    r = _bf(_randn((M, N), dev, 4)) if res else None
+    b = _builder(dev)
+    out = b.linear(a, w, bias=bias, residual=r, cta_pair=cta_pair)
+    _run(b)
+    ref = a.float() @ w.float().t() + bias
+    if res:
+        ref = ref + r.float()
+    _check(out, ref, name=f"weight-resident gemm {M}x{N}x{K}")
+
+
+def test_gemm_weight_resident_geglu(cuda_device):
+    """The level-0 GEGLU up-projection at batch 8 (65536 x 2560 x 320): weight-resident 256x256 pair tiles + GEGLU epilogue."""
+    from stablediffusion_b200.packing import geglu_interleave, geglu_block_n
+
+    dev = cuda_device
+    M, C = 65536, 320
+    w = _randn((8 * C, C), dev, 2, 1.0 / math.sqrt(C))
+    bias = _randn((8 * C,), dev, 3)
+    a = _bf(_randn((M, C), dev, 1))
+    bn = geglu_block_n(8 * C)
+    wp = _bf(geglu_interleave(w, bn))
+    bp = geglu_interleave(bias, bn).contiguous()
+    b = _builder(dev)
+    out = b.linear(a, wp, bias=bp, geglu=True, block_n=bn)
+    _run(b)
+    proj = a.float() @ _bf(w).float().t() + bias
+    h, g = proj.chunk(2, dim=-1)
+    _check(out, h * F.gelu(g), name="weight-resident geglu")
+
+
 # ---------------------------------------------------------------------------------------------------
 # GEMM (spatial mode = implicit conv)
 # ---------------------------------------------------------------------------------------------------
