@@ -39,7 +39,7 @@ extern "C" {
 #define B200SD_API
 #endif
 
-#define B200SD_ABI_VERSION 2
+#define B200SD_ABI_VERSION 3
 #define B200SD_MAX_SEG 3
 #define B200SD_MAX_TAPS 9
 
@@ -66,7 +66,8 @@ typedef enum b200sd_op_kind {
   B200SD_OP_IMAGE_OUT = 12,    /* NHWC bf16 -> NCHW image tensor                                          */
   B200SD_OP_STEP_ADVANCE = 13, /* ++(*step_counter)                                                       */
   B200SD_OP_IMAGE_U8 = 14,     /* NCHW image in [-1,1] -> uint8 HWC (runpod-worker/handler_logic.py:21-29) */
-  B200SD_OP_EMBED = 15         /* token + position embedding lookup of the CLIP text encoders             */
+  B200SD_OP_EMBED = 15,        /* token + position embedding lookup of the CLIP text encoders             */
+  B200SD_OP_GAUSS_SAMPLE = 16  /* VAE posterior sample: mean + exp(0.5*clamp(logvar)) * noise (pipeline :1027)  */
 } b200sd_op_kind;
 
 /* element types of host-visible tensors (latents, images) */
@@ -125,6 +126,9 @@ typedef struct b200sd_gemm {
   int64_t workspace_bytes;
   int32_t block_n;        /* 0 = auto; else one of 32, 64, 128, 160, 256                                  */
   int32_t cta_pair;       /* 0 = auto; 1 = one CTA per 128-row tile; 2 = CTA pair (cta_group::2) per 256 rows */
+  int32_t rows_per_sample; /* linear mode: rows that belong to one image (0 = unknown).  Only read in the batch-invariant
+                              mode (b200sd_set_batch_invariant), where split-K is chosen from the per-image shape      */
+  int32_t pad2_;
 } b200sd_gemm;
 
 /* ---- GroupNorm (+SiLU) ---------------------------------------------------------------------------- */
@@ -272,6 +276,8 @@ typedef struct b200sd_axpby {
   int32_t x_dtype, y_dtype, out_dtype;
   int32_t pad_;
   int64_t n;
+  const float* coef; /* optional DEVICE pointer to {a, b}: read at run time instead of the baked a, b, so one planned op
+                        serves every sampler step (scheduler.scale_model_input / add_noise called the reference's way) */
 } b200sd_axpby;
 
 typedef struct b200sd_image_out {
@@ -301,6 +307,18 @@ typedef struct b200sd_embed {
   int32_t rows, L, D, vocab;
 } b200sd_embed;
 
+/* DiagonalGaussianDistribution.sample of the VAE encoder output (diffusers; called at pipeline :98-106, :1027):
+ *   out[b,c,p] = scale * (mom[b,c,p] + exp(0.5 * clamp(mom[b,C+c,p], -30, 20)) * noise[b,c,p])      c < C
+ * moments are NCHW [B, 2C, hw] (mean | logvar); arithmetic in fp32. */
+typedef struct b200sd_gauss_sample {
+  const void* moments; /* [B, 2C, hw] dtype m_dtype */
+  const void* noise;   /* [B, C, hw] dtype n_dtype: standard-normal draws                                */
+  void* out;           /* [B, C, hw] dtype out_dtype                                                       */
+  float scale;         /* 1.0, or vae.config.scaling_factor when the caller fuses pipeline :1039           */
+  int32_t m_dtype, n_dtype, out_dtype;
+  int32_t B, C, hw, pad_;
+} b200sd_gauss_sample;
+
 typedef struct b200sd_step_advance {
   int32_t* step_counter;
 } b200sd_step_advance;
@@ -324,6 +342,7 @@ typedef struct b200sd_op {
     b200sd_step_advance step_advance;
     b200sd_image_u8 image_u8;
     b200sd_embed embed;
+    b200sd_gauss_sample gauss_sample;
   } u;
 } b200sd_op;
 
@@ -335,6 +354,14 @@ B200SD_API const char* b200sd_last_error(void);          /* thread-local message
 B200SD_API size_t b200sd_sizeof_op(void);                /* layout self-check for foreign-language bindings          */
 B200SD_API size_t b200sd_sizeof_struct(int32_t kind);    /* size of the payload struct of `kind`                     */
 B200SD_API int b200sd_device_check(int device);          /* 0 iff `device` exists and is sm_100                      */
+
+/* Batch-invariant mode (process-wide switch; default off, or 1 when B200SD_BATCH_INVARIANT=1 is in the environment at
+ * first use).  When on, every choice that changes the ORDER of a floating-point reduction — the split-K factor of a GEMM,
+ * the chunking of the GroupNorm statistics — is made from the per-image shape only (N, K, H*W, rows_per_sample), never
+ * from the batch size, so image i of a batch-B run is bit-identical to image i computed in any other batch (the
+ * data-parallel shard == full-batch guarantee of SURVEY section 4).  Ops planned before a change keep their plan. */
+B200SD_API int b200sd_set_batch_invariant(int on);       /* returns the previous setting                              */
+B200SD_API int b200sd_get_batch_invariant(void);
 
 /* workspace sizing helpers (pure host arithmetic; callable without a GPU) */
 B200SD_API int b200sd_groupnorm_chunks(int32_t NB, int32_t HW, int32_t C);

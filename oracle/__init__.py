@@ -1,7 +1,7 @@
 """CPU oracle for the denoising hot path — TEST INFRASTRUCTURE, not product code.
 
 Only `tests/`, `__graft_entry__.smoke()` and `bench.py`'s cpu_baseline / `--impl reference` legs may import
-this package; nothing under `stablediffusion_b200/` does (tests/test_no_oracle_in_product.py enforces it).
+this package; nothing under `stablediffusion_b200/` does (tests/test_abi.py::test_product_never_imports_the_oracle enforces it).
 
 PARITY UNPINNED.  The reference (GrafikXxxxxxxYyyyyyyyyyy/StableDiffusion) owns no arithmetic on this path: every tensor op is
 executed by the un-vendored third-party package `diffusers==0.27.2` (requirements.txt:39) on

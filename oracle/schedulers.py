@@ -74,7 +74,7 @@ class EulerDiscreteOracle(_Base):
         else:
             ts = (np.arange(N, 0, -N / n)).round().copy().astype(np.float32)
             ts -= 1
-        sig = np.array(((1 - self.alphas_cumprod) / self.alphas_cumprod) ** 0.5)
+        sig = (((1 - self.alphas_cumprod) / self.alphas_cumprod) ** 0.5).numpy()
         sig = np.interp(ts, np.arange(0, len(sig)), sig)
         sig = torch.from_numpy(sig).to(dtype=torch.float32)
         self.timesteps = torch.from_numpy(ts.astype(np.float32))
@@ -152,17 +152,29 @@ class DPMSolverMultistepOracle(_Base):
     """DPM-Solver++(2M), midpoint, epsilon prediction, final sigma 0, optional Karras sigmas."""
     init_noise_sigma = 1.0
 
-    def __init__(self, use_karras_sigmas=False, **config):
+    def __init__(self, **config):
         super().__init__(**config)
-        self.use_karras = use_karras_sigmas
+        self.use_karras = bool(self.config.get("use_karras_sigmas", False))
         self.m = [None, None]
         self.lower_order_nums = 0
 
     def set_timesteps(self, n, device=None):
         N = self.config["num_train_timesteps"]
         self.num_inference_steps = n
-        ts = np.linspace(0, N - 1, n + 1).round()[::-1][:-1].copy().astype(np.int64)
-        sig = np.array(((1 - self.alphas_cumprod) / self.alphas_cumprod) ** 0.5)
+        # diffusers 0.27.2 DPMSolverMultistepScheduler.set_timesteps (UniPC: the same three forms); lambda_min_clipped = -inf
+        spacing = self.config.get("timestep_spacing", "linspace")
+        if spacing == "linspace":
+            ts = np.linspace(0, N - 1, n + 1).round()[::-1][:-1].copy().astype(np.int64)
+        elif spacing == "leading":
+            step_ratio = N // (n + 1)
+            ts = (np.arange(0, n + 1) * step_ratio).round()[::-1][:-1].copy().astype(np.int64)
+            ts += self.config.get("steps_offset", 0)
+        elif spacing == "trailing":
+            ts = np.arange(N, 0, -(N / n)).round().copy().astype(np.int64)
+            ts -= 1
+        else:
+            raise ValueError(f"{spacing} is not supported")
+        sig = (((1 - self.alphas_cumprod) / self.alphas_cumprod) ** 0.5).numpy()
         log_sig = np.log(sig)
         if self.use_karras:
             sflip = np.flip(sig).copy()
@@ -464,10 +476,10 @@ def make_scheduler(name: str, config: dict):
     if name == "DPM++ 2M":
         return DPMSolverMultistepOracle(**config)
     if name == "DPM++ 2M Karras":
-        return DPMSolverMultistepOracle(use_karras_sigmas=True, **config)
+        return DPMSolverMultistepOracle(**dict(config, use_karras_sigmas=True))
     if name == "euler_a":
         return EulerAncestralOracle(**config)
-    if name == "DPM++ 2M SDE Karras":
+    if name == "DPM++ 2M SDE Karras":  # (`se_karras_sigmas=True` of the reference is dropped by from_config: not Karras)
         return DPMSolverSDEOracle(**config)
     if name == "PNDM":
         return PNDMOracle(**config)

@@ -22,12 +22,12 @@ STEP_ROW = 16
 # enum b200sd_op_kind
 OP_GEMM, OP_GROUPNORM, OP_LAYERNORM, OP_ATTENTION, OP_TIMESTEP_EMBED, OP_PREP_LATENTS = 1, 2, 3, 4, 5, 6
 OP_UPSAMPLE2X, OP_PHASE_SPLIT, OP_SOFTMAX_ROWS, OP_CFG_STEP, OP_AXPBY, OP_IMAGE_OUT, OP_STEP_ADVANCE = 7, 8, 9, 10, 11, 12, 13
-OP_IMAGE_U8, OP_EMBED = 14, 15
-ABI_VERSION = 2  # include/b200sd.h B200SD_ABI_VERSION
+OP_IMAGE_U8, OP_EMBED, OP_GAUSS_SAMPLE = 14, 15, 16
+ABI_VERSION = 3  # include/b200sd.h B200SD_ABI_VERSION
 OP_NAMES = {
     1: "gemm", 2: "groupnorm", 3: "layernorm", 4: "attention", 5: "timestep_embed", 6: "prep_latents",
     7: "upsample2x", 8: "phase_split", 9: "softmax_rows", 10: "cfg_step", 11: "axpby", 12: "image_out",
-    13: "step_advance", 14: "image_u8", 15: "embed",
+    13: "step_advance", 14: "image_u8", 15: "embed", 16: "gauss_sample",
 }
 # enum b200sd_dtype
 BF16, F32, F16 = 0, 1, 2
@@ -60,7 +60,7 @@ class Gemm(C.Structure):
         ("bias", C.c_void_p), ("rowvec", C.c_void_p), ("ld_rowvec", C.c_int64),
         ("rows_per_group", C.c_int32), ("flags", C.c_int32), ("residual", C.c_void_p), ("ldr", C.c_int64),
         ("alpha", C.c_float), ("splits", C.c_int32), ("workspace", C.c_void_p), ("workspace_bytes", C.c_int64),
-        ("block_n", C.c_int32), ("cta_pair", C.c_int32),
+        ("block_n", C.c_int32), ("cta_pair", C.c_int32), ("rows_per_sample", C.c_int32), ("pad2_", C.c_int32),
     ]
 
 
@@ -136,6 +136,7 @@ class Axpby(C.Structure):
     _fields_ = [
         ("x", C.c_void_p), ("y", C.c_void_p), ("out", C.c_void_p), ("a", C.c_float), ("b", C.c_float),
         ("x_dtype", C.c_int32), ("y_dtype", C.c_int32), ("out_dtype", C.c_int32), ("pad_", C.c_int32), ("n", C.c_int64),
+        ("coef", C.c_void_p),
     ]
 
 
@@ -159,12 +160,19 @@ class Embed(C.Structure):
                 ("rows", C.c_int32), ("L", C.c_int32), ("D", C.c_int32), ("vocab", C.c_int32)]
 
 
+class GaussSample(C.Structure):
+    _fields_ = [("moments", C.c_void_p), ("noise", C.c_void_p), ("out", C.c_void_p), ("scale", C.c_float),
+                ("m_dtype", C.c_int32), ("n_dtype", C.c_int32), ("out_dtype", C.c_int32),
+                ("B", C.c_int32), ("C", C.c_int32), ("hw", C.c_int32), ("pad_", C.c_int32)]
+
+
 class _OpUnion(C.Union):
     _fields_ = [
         ("gemm", Gemm), ("groupnorm", GroupNorm), ("layernorm", LayerNorm), ("attention", Attention),
         ("timestep_embed", TimestepEmbed), ("prep_latents", PrepLatents), ("upsample2x", Upsample2x),
         ("phase_split", PhaseSplit), ("softmax_rows", SoftmaxRows), ("cfg_step", CfgStep), ("axpby", Axpby),
         ("image_out", ImageOut), ("step_advance", StepAdvance), ("image_u8", ImageU8), ("embed", Embed),
+        ("gauss_sample", GaussSample),
     ]
 
 
@@ -176,13 +184,13 @@ STRUCT_OF_KIND = {
     OP_GEMM: Gemm, OP_GROUPNORM: GroupNorm, OP_LAYERNORM: LayerNorm, OP_ATTENTION: Attention,
     OP_TIMESTEP_EMBED: TimestepEmbed, OP_PREP_LATENTS: PrepLatents, OP_UPSAMPLE2X: Upsample2x,
     OP_PHASE_SPLIT: PhaseSplit, OP_SOFTMAX_ROWS: SoftmaxRows, OP_CFG_STEP: CfgStep, OP_AXPBY: Axpby,
-    OP_IMAGE_OUT: ImageOut, OP_STEP_ADVANCE: StepAdvance, OP_IMAGE_U8: ImageU8, OP_EMBED: Embed, 100: GemmSeg,
+    OP_IMAGE_OUT: ImageOut, OP_STEP_ADVANCE: StepAdvance, OP_IMAGE_U8: ImageU8, OP_EMBED: Embed, OP_GAUSS_SAMPLE: GaussSample, 100: GemmSeg,
 }
 FIELD_OF_KIND = {
     OP_GEMM: "gemm", OP_GROUPNORM: "groupnorm", OP_LAYERNORM: "layernorm", OP_ATTENTION: "attention",
     OP_TIMESTEP_EMBED: "timestep_embed", OP_PREP_LATENTS: "prep_latents", OP_UPSAMPLE2X: "upsample2x",
     OP_PHASE_SPLIT: "phase_split", OP_SOFTMAX_ROWS: "softmax_rows", OP_CFG_STEP: "cfg_step", OP_AXPBY: "axpby",
-    OP_IMAGE_OUT: "image_out", OP_STEP_ADVANCE: "step_advance", OP_IMAGE_U8: "image_u8", OP_EMBED: "embed",
+    OP_IMAGE_OUT: "image_out", OP_STEP_ADVANCE: "step_advance", OP_IMAGE_U8: "image_u8", OP_EMBED: "embed", OP_GAUSS_SAMPLE: "gauss_sample",
 }
 
 ENTRY_POINTS = {
@@ -191,6 +199,8 @@ ENTRY_POINTS = {
     "b200sd_sizeof_op": (C.c_size_t, []),
     "b200sd_sizeof_struct": (C.c_size_t, [C.c_int32]),
     "b200sd_device_check": (C.c_int, [C.c_int]),
+    "b200sd_set_batch_invariant": (C.c_int, [C.c_int]),
+    "b200sd_get_batch_invariant": (C.c_int, []),
     "b200sd_groupnorm_chunks": (C.c_int, [C.c_int32, C.c_int32, C.c_int32]),
     "b200sd_gemm_workspace_bytes": (C.c_int64, [C.POINTER(Gemm)]),
     "b200sd_program_create": (C.c_int, [C.POINTER(C.c_void_p), C.c_int]),
@@ -261,6 +271,16 @@ def check(rc: int) -> int:
     if rc == ERR_INVALID:
         raise ValueError(msg)
     raise RuntimeError(f"libb200sd error {rc}: {msg}")
+
+
+def set_batch_invariant(on: bool) -> bool:
+    """Process-wide switch (include/b200sd.h): reduction-order choices from the per-image shape only, so an image's result
+    does not depend on the batch it is computed in.  Affects ops planned AFTER the call; returns the previous setting."""
+    return bool(lib().b200sd_set_batch_invariant(1 if on else 0))
+
+
+def batch_invariant() -> bool:
+    return bool(lib().b200sd_get_batch_invariant())
 
 
 def make_op(kind: int, payload: C.Structure, tag: int = 0) -> Op:

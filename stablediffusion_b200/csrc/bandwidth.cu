@@ -65,16 +65,54 @@ __device__ __forceinline__ const bf16* gn_src(const GNParams& p, int n, int pix,
   return (c0 < p.C1) ? p.x1 + row * p.ld1 + c0 : p.x2 + row * p.ld2 + (c0 - p.C1);
 }
 
+// Deterministic fold of the per-thread channel sums (s, ss: 8 channels of pixel-row slot r) into per-group sums.
+// No atomics: every addition happens in an order fixed by the CTA geometry (cols, R, groups), which depends on the
+// per-image shape only — so the statistics of an image do not depend on the batch it is computed in, nor on warp
+// scheduling.  scratch: [2][R][C] channel sums + [parts][groups][2] partial group sums (GN_FOLD_FLOATS per thread).
+constexpr int GN_FOLD_FLOATS = 18;
+__device__ __forceinline__ void gn_fold_groups(const GNParams& p, float* scratch, const float (&s)[8], const float (&ss)[8],
+                                               int r, int c0, int tid, int nthreads, float* gsum /*[groups][2]*/) {
+  const int RC = p.R * p.C;
+  float* ch_s = scratch;
+  float* ch_ss = scratch + RC;
+  float* red = scratch + 2 * RC;
+  *reinterpret_cast<float4*>(ch_s + r * p.C + c0) = make_float4(s[0], s[1], s[2], s[3]);
+  *reinterpret_cast<float4*>(ch_s + r * p.C + c0 + 4) = make_float4(s[4], s[5], s[6], s[7]);
+  *reinterpret_cast<float4*>(ch_ss + r * p.C + c0) = make_float4(ss[0], ss[1], ss[2], ss[3]);
+  *reinterpret_cast<float4*>(ch_ss + r * p.C + c0 + 4) = make_float4(ss[4], ss[5], ss[6], ss[7]);
+  __syncthreads();
+  const int parts = nthreads / p.groups;  // >= 1 (the plan keeps nthreads >= groups)
+  const int g = tid % p.groups, part = tid / p.groups;
+  if (part < parts) {
+    float S = 0.f, SS = 0.f;
+    const int n = p.cpg * p.R;
+    for (int e = part; e < n; e += parts) {
+      const int rr = e / p.cpg;
+      const int c = g * p.cpg + (e - rr * p.cpg);
+      S += ch_s[rr * p.C + c];
+      SS += ch_ss[rr * p.C + c];
+    }
+    red[(part * p.groups + g) * 2] = S;
+    red[(part * p.groups + g) * 2 + 1] = SS;
+  }
+  __syncthreads();
+  if (tid < p.groups) {
+    float S = 0.f, SS = 0.f;
+    for (int q = 0; q < parts; ++q) { S += red[(q * p.groups + tid) * 2]; SS += red[(q * p.groups + tid) * 2 + 1]; }
+    gsum[2 * tid] = S;
+    gsum[2 * tid + 1] = SS;
+  }
+}
+
 __global__ void gn_stats_kernel(const GNParams p) {
   pdl_launch_dependents();
   pdl_wait();
-  __shared__ float gsum[64][2];
+  extern __shared__ __align__(16) float gn_scratch[];
+  __shared__ float gsum[64 * 2];
   const int chunk = blockIdx.x, n = blockIdx.y;
   const int tid = threadIdx.x;
   const int vcol = tid % p.cols, r = tid / p.cols;
   const int c0 = vcol * 8;
-  if (tid < p.groups) { gsum[tid][0] = 0.f; gsum[tid][1] = 0.f; }
-  __syncthreads();
   float s[8], ss[8];
 #pragma unroll
   for (int j = 0; j < 8; ++j) { s[j] = 0.f; ss[j] = 0.f; }
@@ -105,26 +143,11 @@ __global__ void gn_stats_kernel(const GNParams p) {
       s[2 * j + 1] += f.y; ss[2 * j + 1] += f.y * f.y;
     }
   }
-  // fold the 8 channels into their groups (a vector can straddle group boundaries when cpg % 8 != 0)
-  int g_prev = c0 / p.cpg;
-  float as = 0.f, ass = 0.f;
-#pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    int g = (c0 + j) / p.cpg;
-    if (g != g_prev) {
-      atomicAdd(&gsum[g_prev][0], as);
-      atomicAdd(&gsum[g_prev][1], ass);
-      as = 0.f; ass = 0.f; g_prev = g;
-    }
-    as += s[j]; ass += ss[j];
-  }
-  atomicAdd(&gsum[g_prev][0], as);
-  atomicAdd(&gsum[g_prev][1], ass);
-  __syncthreads();
+  gn_fold_groups(p, gn_scratch, s, ss, r, c0, tid, blockDim.x, gsum);
   if (tid < p.groups) {
     float* dst = p.partials + ((static_cast<long long>(n) * p.chunks + chunk) * p.groups + tid) * 2;
-    dst[0] = gsum[tid][0];
-    dst[1] = gsum[tid][1];
+    dst[0] = gsum[2 * tid];
+    dst[1] = gsum[2 * tid + 1];
   }
 }
 
@@ -233,8 +256,6 @@ __global__ void __launch_bounds__(512) gn_fused_kernel(const GNParams p) {
   const int tid = threadIdx.x, nthreads = blockDim.x;
   const int vcol = tid % p.cols, r = tid / p.cols;
   const int c0 = vcol * 8;
-  if (tid < p.groups) { gsum[2 * tid] = 0.f; gsum[2 * tid + 1] = 0.f; }
-  __syncthreads();
   float s[8], ss[8];
 #pragma unroll
   for (int j = 0; j < 8; ++j) { s[j] = 0.f; ss[j] = 0.f; }
@@ -266,22 +287,8 @@ __global__ void __launch_bounds__(512) gn_fused_kernel(const GNParams p) {
     accumulate(v);
   }
   const int my_iters = it;
-  {
-    int g_prev = c0 / p.cpg;
-    float as = 0.f, ass = 0.f;
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      int g = (c0 + j) / p.cpg;
-      if (g != g_prev) {
-        atomicAdd(&gsum[2 * g_prev], as);
-        atomicAdd(&gsum[2 * g_prev + 1], ass);
-        as = 0.f; ass = 0.f; g_prev = g;
-      }
-      as += s[j]; ass += ss[j];
-    }
-    atomicAdd(&gsum[2 * g_prev], as);
-    atomicAdd(&gsum[2 * g_prev + 1], ass);
-  }
+  // group sums of this CTA's slice, deterministic order (scratch sits behind the slice data)
+  gn_fold_groups(p, reinterpret_cast<float*>(gnf_smem + GNF_HEADER_BYTES + GNF_MAX_DATA_BYTES), s, ss, r, c0, tid, nthreads, gsum);
   cluster_sync_all();  // every CTA's group sums are complete and visible cluster-wide
   if (tid < p.groups) {
     double S = 0.0, SS = 0.0;
@@ -333,7 +340,7 @@ bool gn_fused_enabled() {
   return on;
 }
 
-struct GNPlan { GNParams p; int threads; size_t smem; int fused; };
+struct GNPlan { GNParams p; int threads; size_t smem; size_t smem_stats; int fused; };
 int launch_groupnorm(const void* plan, cudaStream_t s) {
   const GNPlan& pl = *static_cast<const GNPlan*>(plan);
   dim3 grid(pl.p.chunks, pl.p.NB);
@@ -342,7 +349,7 @@ int launch_groupnorm(const void* plan, cudaStream_t s) {
     B200SD_CUDA(cudaGetLastError());
     return 0;
   }
-  B200SD_CUDA(launch_kernel(gn_stats_kernel, dim3(grid), dim3(pl.threads), 0, s, 1, pl.p));
+  B200SD_CUDA(launch_kernel(gn_stats_kernel, dim3(grid), dim3(pl.threads), pl.smem_stats, s, 1, pl.p));
   B200SD_CUDA(cudaGetLastError());
   B200SD_CUDA(launch_kernel(gn_apply_kernel, dim3(grid), dim3(pl.threads), pl.smem, s, 1, pl.p));
   B200SD_CUDA(cudaGetLastError());
@@ -732,14 +739,15 @@ int launch_cfg_step(const void* plan, cudaStream_t s) {
 // ======================================================================================================
 // small utilities
 // ======================================================================================================
-struct AXParams { const void* x; const void* y; void* out; float a, b; int xd, yd, od; long long n; };
+struct AXParams { const void* x; const void* y; void* out; float a, b; int xd, yd, od; long long n; const float* coef; };
 __global__ void axpby_kernel(const AXParams p) {
   pdl_launch_dependents();
   pdl_wait();
+  const float a = p.coef ? p.coef[0] : p.a, b = p.coef ? p.coef[1] : p.b;
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < p.n;
        i += static_cast<long long>(gridDim.x) * blockDim.x) {
-    float v = p.a * load_as_float(p.x, i, p.xd);
-    if (p.y) v += p.b * load_as_float(p.y, i, p.yd);
+    float v = a * load_as_float(p.x, i, p.xd);
+    if (p.y) v += b * load_as_float(p.y, i, p.yd);
     store_from_float(p.out, i, p.od, v);
   }
 }
@@ -747,6 +755,32 @@ int launch_axpby(const void* plan, cudaStream_t s) {
   const AXParams& p = *static_cast<const AXParams*>(plan);
   const int blocks = static_cast<int>(std::min<long long>((p.n + 255) / 256, 148 * 8));
   B200SD_CUDA(launch_kernel(axpby_kernel, dim3(blocks), dim3(256), 0, s, 1, p));
+  B200SD_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// VAE posterior sample (diffusers DiagonalGaussianDistribution.sample; pipeline :98-106, :1027): elementwise, fp32.
+struct GSParams { const void* mom; const void* noise; void* out; float scale; int md, nd, od, B, C, hw; };
+__global__ void gauss_sample_kernel(const GSParams p) {
+  pdl_launch_dependents();
+  pdl_wait();
+  const long long per = static_cast<long long>(p.C) * p.hw;
+  const long long total = static_cast<long long>(p.B) * per;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const long long b = i / per, rest = i - b * per;
+    const float mean = load_as_float(p.mom, b * 2 * per + rest, p.md);
+    float logvar = load_as_float(p.mom, b * 2 * per + per + rest, p.md);
+    logvar = fminf(fmaxf(logvar, -30.0f), 20.0f);
+    const float std_ = expf(0.5f * logvar);
+    store_from_float(p.out, i, p.od, p.scale * (mean + std_ * load_as_float(p.noise, i, p.nd)));
+  }
+}
+int launch_gauss_sample(const void* plan, cudaStream_t s) {
+  const GSParams& p = *static_cast<const GSParams*>(plan);
+  const long long total = static_cast<long long>(p.B) * p.C * p.hw;
+  const int blocks = static_cast<int>(std::min<long long>((total + 255) / 256, 148 * 8));
+  B200SD_CUDA(launch_kernel(gauss_sample_kernel, dim3(blocks), dim3(256), 0, s, 1, p));
   B200SD_CUDA(cudaGetLastError());
   return 0;
 }
@@ -884,7 +918,9 @@ bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 
 int groupnorm_chunks(int NB, int HW, int C) {
   if (NB < 1 || HW < 1 || C < 8) return 1;
   // One full wave: both kernels keep 4 CTAs of <= 256 threads resident per SM, so NB * chunks is sized to 4 * SMs
-  // (a grid of 1.2 or 1.5 waves runs as long as 2).
+  // (a grid of 1.2 or 1.5 waves runs as long as 2).  The chunking fixes the order in which an image's partial sums are
+  // added, so the batch-invariant mode sizes it for the canonical batch instead of the actual one.
+  if (batch_invariant()) NB = kCanonBatch;
   int target = std::max(1, (4 * sm_count()) / NB);
   const int R = std::max(1, 256 / (C / 8));           // pixel rows a CTA walks in parallel
   int max_chunks = std::max(1, HW / (4 * R));         // keep >= 4 loads per thread so one unrolled batch covers a chunk
@@ -921,12 +957,13 @@ int plan_groupnorm(const b200sd_groupnorm& g, PlannedOp* out) {
       static bool attr_set = false;
       if (!attr_set) {
         if (cudaFuncSetAttribute(gn_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 GNF_HEADER_BYTES + GNF_MAX_DATA_BYTES) == cudaSuccess) attr_set = true;
+                                 GNF_HEADER_BYTES + GNF_MAX_DATA_BYTES + 512 * GN_FOLD_FLOATS * 4) == cudaSuccess) attr_set = true;
         else (void)cudaGetLastError();  // no device (planning arithmetic only): the launch will report it
       }
       p.chunks = chunks; p.ppc = ppc; p.R = R;
       pl.threads = p.cols * R;
-      pl.smem = GNF_HEADER_BYTES + data_bytes;
+      pl.smem = GNF_HEADER_BYTES + GNF_MAX_DATA_BYTES + static_cast<size_t>(pl.threads) * GN_FOLD_FLOATS * 4;
+      pl.smem_stats = 0;
       pl.fused = 1;
       return finish_plan(out, B200SD_OP_GROUPNORM, pl, launch_groupnorm, 1);
     }
@@ -940,6 +977,15 @@ int plan_groupnorm(const b200sd_groupnorm& g, PlannedOp* out) {
   if (pl.threads < g.groups) { p.R = (g.groups + p.cols - 1) / p.cols; pl.threads = p.cols * p.R; }
   pl.smem = (2 * static_cast<size_t>(C) + 2 * g.groups) * sizeof(float) + 8 +
             static_cast<size_t>(pl.threads / g.groups + 1) * g.groups * 2 * sizeof(double);
+  pl.smem_stats = static_cast<size_t>(pl.threads) * GN_FOLD_FLOATS * 4;
+  if (pl.smem_stats > 48 * 1024) {
+    static bool stats_attr_set = false;
+    if (!stats_attr_set) {
+      if (cudaFuncSetAttribute(gn_stats_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 1024 * GN_FOLD_FLOATS * 4) == cudaSuccess)
+        stats_attr_set = true;
+      else (void)cudaGetLastError();
+    }
+  }
   const long long need = static_cast<long long>(g.NB) * groupnorm_chunks(g.NB, g.HW, C) * g.groups * 2 * 4;
   B200SD_CHECK_ARG(g.partials_bytes >= need, "groupnorm: partials workspace %lld < %lld bytes", (long long)g.partials_bytes, need);
   return finish_plan(out, B200SD_OP_GROUPNORM, pl, launch_groupnorm, 2);
@@ -1006,7 +1052,7 @@ int plan_cfg_step(const b200sd_cfg_step& g, PlannedOp* out) {
 
 int plan_axpby(const b200sd_axpby& g, PlannedOp* out) {
   B200SD_CHECK_ARG(g.x && g.out && g.n >= 1 && dtype_ok(g.x_dtype) && dtype_ok(g.out_dtype) && (!g.y || dtype_ok(g.y_dtype)), "axpby: bad arguments");
-  AXParams p{g.x, g.y, g.out, g.a, g.b, g.x_dtype, g.y_dtype, g.out_dtype, g.n};
+  AXParams p{g.x, g.y, g.out, g.a, g.b, g.x_dtype, g.y_dtype, g.out_dtype, g.n, g.coef};
   return finish_plan(out, B200SD_OP_AXPBY, p, launch_axpby);
 }
 
@@ -1029,6 +1075,14 @@ int plan_embed(const b200sd_embed& g, PlannedOp* out) {
   B200SD_CHECK_ARG(aligned16(g.tok) && aligned16(g.pos) && aligned16(g.out), "embed: tables and output must be 16-byte aligned");
   EmbParams p{g.ids, static_cast<const bf16*>(g.tok), static_cast<const bf16*>(g.pos), static_cast<bf16*>(g.out), g.rows, g.L, g.D, g.vocab};
   return finish_plan(out, B200SD_OP_EMBED, p, launch_embed);
+}
+
+int plan_gauss_sample(const b200sd_gauss_sample& g, PlannedOp* out) {
+  B200SD_CHECK_ARG(g.moments && g.noise && g.out, "gauss_sample: NULL pointer");
+  B200SD_CHECK_ARG(g.B >= 1 && g.C >= 1 && g.hw >= 1 && dtype_ok(g.m_dtype) && dtype_ok(g.n_dtype) && dtype_ok(g.out_dtype),
+                   "gauss_sample: bad shape or dtype");
+  GSParams p{g.moments, g.noise, g.out, g.scale == 0.0f ? 1.0f : g.scale, g.m_dtype, g.n_dtype, g.out_dtype, g.B, g.C, g.hw};
+  return finish_plan(out, B200SD_OP_GAUSS_SAMPLE, p, launch_gauss_sample);
 }
 
 int plan_step_advance(const b200sd_step_advance& g, PlannedOp* out) {

@@ -8,12 +8,14 @@
 //     zero-filled by TMA's out-of-bounds handling, so no im2col buffer ever exists.
 //   * K may be the concatenation of up to 3 segments (e.g. conv2's 9*C taps followed by the 1x1 shortcut's
 //     C_in columns), each with its own activation and weight tensor map.
-// Structure: persistent CTAs (one per SM), warp-specialised — warp 0 TMA producer, warp 1 MMA issuer
-// (single thread, tcgen05.mma.cta_group::1 128xBNx16, fp32 accumulators in TMEM, double-buffered so the
-// epilogue of tile i overlaps the main loop of tile i+1), warps 2-5 epilogue (tcgen05.ld -> registers ->
-// fused bias / time-embedding row vector / residual / SiLU / GEGLU -> bf16 stores).
+// Structure: persistent work units — one CTA, or a CTA PAIR (cluster of 2, tcgen05.mma.cta_group::2, 256 x BN tile:
+// each CTA stages its own 128 rows of A and half of the weight tile).  12 warps: warp 0 TMA producer, warp 1 MMA
+// issuer (elect.sync-gated single thread; fp32 accumulators double-buffered in TMEM so the epilogue of tile i
+// overlaps the main loop of tile i+1), warps 2-9 epilogue in two groups that take alternate 32-column sub-tiles
+// (tcgen05.ld -> bias / time-embedding row vector / SiLU / GEGLU -> residual from a TMA-prefetched smem slot ->
+// bf16 -> swizzled smem ring -> TMA store), warps 10-11 issue the epilogue's TMA loads / stores.
 // Split-K (for the M=128..512 low-resolution levels) writes fp32 partial tiles that a second small kernel
-// reduces with the same epilogue.
+// reduces with the same epilogue; a weight-resident mode serves the short-K linears (see choose_gemm_tiling).
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
@@ -938,58 +940,75 @@ int choose_gemm_tiling(const b200sd_gemm& g, GemmTiling* t) {
   // L2 -> SM stream is a chip-wide ceiling (~6300 B/clk over all SMs), so the weight re-reads it removes (39 % of the
   // ingested rows at 256x160 pair tiles, 50 % at 256x256) are what bounded the K = 320 / 640 linears.
   static const bool wres_enabled = [] { const char* e = getenv("B200SD_GEMM_WRES"); return !(e && e[0] == '0'); }();
-  const bool wres_shape = wres_enabled && !g.spatial && g.nseg == 1 && g.seg[0].taps == 1 && g.splits <= 1;
   const int bn_cand[5] = {256, 160, 128, 64, 32};
   double best_cost = 1e300;
   int best_bn = 0, best_ncta = 1, best_s = 1, best_wres = 0, best_wst = 0, best_upn = 0;
-  double wres_cost[10];
-  int wres_cfg[10][4], wres_n = 0;
-  for (int bi = 0; bi < 5; ++bi) {
-    const int bn = bn_cand[bi];
-    if (g.block_n ? bn != g.block_n : ((bn == 64 && g.N > 64) || (bn == 32 && g.N > 32) || (geglu && (bn % 64 || g.N % bn))))
-      continue;  // the narrow tiles only serve narrow outputs; a GEGLU tile holds whole h|g column pairs
-    const int n_tiles = (g.N + bn - 1) / bn;
-    for (int ncta = 1; ncta <= 2; ++ncta) {
-      if (g.cta_pair && ncta != g.cta_pair) continue;
-      if (ncta == 2 && (bn % 32 != 0 || (!g.cta_pair && t->num_m_tiles < 2))) continue;
-      const int num_pm = (t->num_m_tiles + ncta - 1) / ncta;
-      const int units = std::max(1, sm_count() / ncta);
-      const double t_kb = std::max(2.0 * bn, 2.6 * (128 + bn / ncta));
-      const int max_s = g.splits > 0 ? g.splits : std::min(32, std::max(1, kb_total / 4));
-      for (int sp = g.splits > 0 ? g.splits : 1; sp <= max_s; ++sp) {
-        const int per = (kb_total + sp - 1) / sp;
-        if (g.splits <= 0 && (kb_total + per - 1) / per != sp) continue;
-        const long long waves = (static_cast<long long>(num_pm) * n_tiles * sp + units - 1) / units;
-        double cost = static_cast<double>(waves) * (per * t_kb + 1500.0);
-        if (sp > 1)  // fp32 partials written (row-strided 64-byte pieces) and re-read by the reduce kernel (+ its launch);
-                     // calibrated on tools/sweep_small_gemm.py: the 24 B/clk/SM first assumed made 4096-row convs split
-                     // 4 ways (135 us) when 256x160 pair tiles unsplit run them in 101
-          cost += 4000.0 + static_cast<double>(t->num_m_tiles) * BM * n_tiles * bn * 4.0 * (sp + 1) / (148.0 * 9.6);
-        if (cost < best_cost * (1.0 - 1e-9)) { best_cost = cost; best_bn = bn; best_ncta = ncta; best_s = sp; best_wres = 0; }
-      }
-      if (wres_shape && n_tiles <= units) {
-        const int b_bytes = kb_total * (bn / ncta) * 128;
-        const int wst = std::min(MAX_STAGES, (gemm_region_bytes(bn) - b_bytes) / A_STAGE_BYTES);
-        const int upn = std::min(units / n_tiles, num_pm);  // work units per N tile
-        if (b_bytes < gemm_region_bytes(bn) && wst >= WRES_MIN_STAGES && num_pm >= 3 * upn) {
-          const long long rounds = (num_pm + upn - 1) / upn;
-          const double cost = 2.6 * kb_total * (bn / ncta) + static_cast<double>(rounds) * (kb_total * std::max(2.0 * bn, 2.6 * 128) + 1500.0);
-          wres_cost[wres_n] = cost; wres_cfg[wres_n][0] = bn; wres_cfg[wres_n][1] = ncta; wres_cfg[wres_n][2] = wst; wres_cfg[wres_n][3] = upn;
-          ++wres_n;
+  // One search over (block_n, CTA pair, split-K[, weight-resident]) for a problem of `m_tiles` 128-row tiles;
+  // `force_splits` > 0 pins the split factor.
+  auto search = [&](int m_tiles, int force_splits) {
+    const bool wres_shape = wres_enabled && !g.spatial && g.nseg == 1 && g.seg[0].taps == 1 && force_splits <= 1;
+    best_cost = 1e300; best_bn = 0; best_ncta = 1; best_s = 1; best_wres = 0; best_wst = 0; best_upn = 0;
+    double wres_cost[10];
+    int wres_cfg[10][4], wres_n = 0;
+    for (int bi = 0; bi < 5; ++bi) {
+      const int bn = bn_cand[bi];
+      if (g.block_n ? bn != g.block_n : ((bn == 64 && g.N > 64) || (bn == 32 && g.N > 32) || (geglu && (bn % 64 || g.N % bn))))
+        continue;  // the narrow tiles only serve narrow outputs; a GEGLU tile holds whole h|g column pairs
+      const int n_tiles = (g.N + bn - 1) / bn;
+      for (int ncta = 1; ncta <= 2; ++ncta) {
+        if (g.cta_pair && ncta != g.cta_pair) continue;
+        if (ncta == 2 && (bn % 32 != 0 || (!g.cta_pair && m_tiles < 2))) continue;
+        const int num_pm = (m_tiles + ncta - 1) / ncta;
+        const int units = std::max(1, sm_count() / ncta);
+        const double t_kb = std::max(2.0 * bn, 2.6 * (128 + bn / ncta));
+        const int max_s = force_splits > 0 ? force_splits : std::min(32, std::max(1, kb_total / 4));
+        for (int sp = force_splits > 0 ? force_splits : 1; sp <= max_s; ++sp) {
+          const int per = (kb_total + sp - 1) / sp;
+          if (force_splits <= 0 && (kb_total + per - 1) / per != sp) continue;
+          const long long waves = (static_cast<long long>(num_pm) * n_tiles * sp + units - 1) / units;
+          double cost = static_cast<double>(waves) * (per * t_kb + 1500.0);
+          if (sp > 1)  // fp32 partials written (row-strided 64-byte pieces) and re-read by the reduce kernel (+ its launch);
+                       // calibrated on tools/sweep_small_gemm.py: the 24 B/clk/SM first assumed made 4096-row convs split
+                       // 4 ways (135 us) when 256x160 pair tiles unsplit run them in 101
+            cost += 4000.0 + static_cast<double>(m_tiles) * BM * n_tiles * bn * 4.0 * (sp + 1) / (148.0 * 9.6);
+          if (cost < best_cost * (1.0 - 1e-9)) { best_cost = cost; best_bn = bn; best_ncta = ncta; best_s = sp; best_wres = 0; }
+        }
+        if (wres_shape && n_tiles <= units) {
+          const int b_bytes = kb_total * (bn / ncta) * 128;
+          const int wst = std::min(MAX_STAGES, (gemm_region_bytes(bn) - b_bytes) / A_STAGE_BYTES);
+          const int upn = std::min(units / n_tiles, num_pm);  // work units per N tile
+          if (b_bytes < gemm_region_bytes(bn) && wst >= WRES_MIN_STAGES && num_pm >= 3 * upn) {
+            const long long rounds = (num_pm + upn - 1) / upn;
+            const double cost = 2.6 * kb_total * (bn / ncta) + static_cast<double>(rounds) * (kb_total * std::max(2.0 * bn, 2.6 * 128) + 1500.0);
+            wres_cost[wres_n] = cost; wres_cfg[wres_n][0] = bn; wres_cfg[wres_n][1] = ncta; wres_cfg[wres_n][2] = wst; wres_cfg[wres_n][3] = upn;
+            ++wres_n;
+          }
         }
       }
     }
+    // the weight-resident form only where the estimate says it clearly pays (measured: 65536x320x320 -5 %, but 16384x640x640
+    // as 256x128 resident tiles 22.2 us vs 20.9 for plain 256x160 pair tiles, at an estimated 7 % advantage)
+    for (int i = 0; i < wres_n; ++i) {
+      if (wres_cost[i] < 0.9 * best_cost && (!best_wres || wres_cost[i] < wres_cost[best_wres - 1])) best_wres = i + 1;
+    }
+    if (best_wres) {
+      const int* c = wres_cfg[best_wres - 1];
+      best_cost = wres_cost[best_wres - 1]; best_bn = c[0]; best_ncta = c[1]; best_s = 1; best_wst = c[2]; best_upn = c[3];
+      best_wres = 1;
+    }
+  };
+  int force_splits = g.splits > 0 ? g.splits : 0;
+  if (force_splits == 0 && batch_invariant()) {
+    // Batch-invariant mode: split-K changes the order of the K summation, so its factor is decided for a canonical batch
+    // of kCanonBatch images of this op's per-image shape (H*W pixels, or rows_per_sample rows) and then pinned; block_n,
+    // CTA pairs and the weight-resident form only change which CTA computes a row, not how, and stay free.
+    long long rows_ps = g.spatial ? static_cast<long long>(g.H) * g.W : static_cast<long long>(g.rows_per_sample);
+    if (rows_ps > 0) {
+      search(static_cast<int>((rows_ps * kCanonBatch + BM - 1) / BM), 0);
+      force_splits = best_s;
+    }
   }
-  // the weight-resident form only where the estimate says it clearly pays (measured: 65536x320x320 -5 %, but 16384x640x640
-  // as 256x128 resident tiles 22.2 us vs 20.9 for plain 256x160 pair tiles, at an estimated 7 % advantage)
-  for (int i = 0; i < wres_n; ++i) {
-    if (wres_cost[i] < 0.9 * best_cost && (!best_wres || wres_cost[i] < wres_cost[best_wres - 1])) best_wres = i + 1;
-  }
-  if (best_wres) {
-    const int* c = wres_cfg[best_wres - 1];
-    best_cost = wres_cost[best_wres - 1]; best_bn = c[0]; best_ncta = c[1]; best_s = 1; best_wst = c[2]; best_upn = c[3];
-    best_wres = 1;
-  }
+  search(t->num_m_tiles, force_splits);
   B200SD_CHECK_ARG(best_bn != 0, "gemm: no tile shape fits N=%d block_n=%d cta_pair=%d", g.N, g.block_n, g.cta_pair);
   const int bn = best_bn;
   t->block_n = bn;

@@ -62,6 +62,7 @@ int plan_image_out(const b200sd_image_out& g, PlannedOp* out);
 int plan_step_advance(const b200sd_step_advance& g, PlannedOp* out);
 int plan_image_u8(const b200sd_image_u8& g, PlannedOp* out);
 int plan_embed(const b200sd_embed& g, PlannedOp* out);
+int plan_gauss_sample(const b200sd_gauss_sample& g, PlannedOp* out);
 
 // host-only helpers used by sizing entry points
 struct GemmTiling {
@@ -74,6 +75,10 @@ struct GemmTiling {
 int choose_gemm_tiling(const b200sd_gemm& g, GemmTiling* t);
 int groupnorm_chunks(int NB, int HW, int C);
 int sm_count();  // of the current device; 148 when no device is visible (planning arithmetic only)
+// Batch-invariant mode (b200sd_set_batch_invariant): reduction-order choices are made for a canonical batch of
+// kCanonBatch images of the op's per-image shape, whatever the actual batch is.
+bool batch_invariant();
+constexpr int kCanonBatch = 8;
 
 // Every kernel launch of the library: programmatic stream serialization (see pdl_wait() in common.cuh; B200SD_PDL=0 in
 // the environment turns it off) and, for the CTA-pair GEMM, a cluster dimension.  Works under stream capture.

@@ -31,6 +31,20 @@ bool pdl_enabled() {
   return on;
 }
 
+static int g_batch_invariant = -1;  // -1: not decided yet (environment read at first use)
+bool batch_invariant() {
+  if (g_batch_invariant < 0) {
+    const char* e = getenv("B200SD_BATCH_INVARIANT");
+    g_batch_invariant = (e && e[0] == '1') ? 1 : 0;
+  }
+  return g_batch_invariant != 0;
+}
+int set_batch_invariant(int on) {
+  const int prev = batch_invariant() ? 1 : 0;
+  g_batch_invariant = on ? 1 : 0;
+  return prev;
+}
+
 int sm_count() {
   static int cached = -1;
   if (cached > 0) return cached;
@@ -141,6 +155,7 @@ size_t b200sd_sizeof_struct(int32_t kind) {
     case B200SD_OP_STEP_ADVANCE: return sizeof(b200sd_step_advance);
     case B200SD_OP_IMAGE_U8: return sizeof(b200sd_image_u8);
     case B200SD_OP_EMBED: return sizeof(b200sd_embed);
+    case B200SD_OP_GAUSS_SAMPLE: return sizeof(b200sd_gauss_sample);
     case 100: return sizeof(b200sd_gemm_seg);
   }
   return 0;
@@ -159,6 +174,9 @@ int b200sd_device_check(int device) {
   if (major != 10) return fail(B200SD_ERR_NO_DEVICE, "device %d is sm_%d%d; this library only contains sm_100a code", device, major, minor);
   return 0;
 }
+
+int b200sd_set_batch_invariant(int on) { return set_batch_invariant(on); }
+int b200sd_get_batch_invariant(void) { return batch_invariant() ? 1 : 0; }
 
 int b200sd_groupnorm_chunks(int32_t NB, int32_t HW, int32_t C) { return groupnorm_chunks(NB, HW, C); }
 
@@ -205,6 +223,7 @@ int b200sd_program_add(b200sd_program* p, const b200sd_op* op) {
     case B200SD_OP_STEP_ADVANCE: rc = plan_step_advance(op->u.step_advance, &po); break;
     case B200SD_OP_IMAGE_U8: rc = plan_image_u8(op->u.image_u8, &po); break;
     case B200SD_OP_EMBED: rc = plan_embed(op->u.embed, &po); break;
+    case B200SD_OP_GAUSS_SAMPLE: rc = plan_gauss_sample(op->u.gauss_sample, &po); break;
     default: return fail(B200SD_ERR_INVALID, "unknown op kind %d", op->kind);
   }
   if (rc) return rc;

@@ -47,6 +47,7 @@ class DenoiseEngine:
         self.NB = B if self.split else rep_total * B      # UNet batch on THIS rank
         NB = self.NB
         pk = unet.packed
+        self.packed = pk  # the programs below point into these tensors: the engine owns a reference
         self.use_graph = use_graph
 
         # ---- static device state ----------------------------------------------------------------------

@@ -48,6 +48,7 @@ def parse_lora_state_dict(sd: Dict[str, torch.Tensor], unet_modules=None) -> Dic
     if not all("lora" in k for k in sd.keys()):
         raise ValueError("Invalid LoRA checkpoint.")  # models/stable_diffusion.py:264-266
     out: Dict[str, Dict[str, dict]] = {"unet": {}, "text_encoder": {}, "text_encoder_2": {}}
+    unresolved = set()
     for key, val in sd.items():
         sp = _split_suffix(key)
         if sp is None:
@@ -57,7 +58,8 @@ def parse_lora_state_dict(sd: Dict[str, torch.Tensor], unet_modules=None) -> Dic
             if unet_modules is None:
                 raise ValueError("kohya-format LoRA needs the UNet module list to resolve names")
             path = _kohya_unet_module(mod, unet_modules)
-            if path is None:
+            if path is None:  # e.g. SGM / LDM block names (lora_unet_input_blocks_*): not a diffusers module path
+                unresolved.add(mod)
                 continue
             part = "unet"
         elif mod.startswith("lora_te"):
@@ -76,6 +78,11 @@ def parse_lora_state_dict(sd: Dict[str, torch.Tensor], unet_modules=None) -> Dic
             path = path.replace(".to_k_lora", ".to_k").replace(".to_v_lora", ".to_v")
         ent = out[part].setdefault(path, {"down": None, "up": None, "alpha": None})
         ent[kind] = float(val) if kind == "alpha" else val
+    if unresolved:
+        # a file whose modules cannot be placed must not load as a silent no-op adapter
+        ex = sorted(unresolved)[:3]
+        raise ValueError(f"LoRA checkpoint targets {len(unresolved)} UNet modules this model does not have, e.g. {ex} "
+                         "(SGM/LDM-style block names are not supported: convert the file to diffusers/kohya-diffusers names)")
     for part in out.values():
         for path, ent in list(part.items()):
             if ent["down"] is None or ent["up"] is None:

@@ -124,8 +124,9 @@ class Builder:
         g.alpha = alpha
 
     def linear(self, a, w, out=None, bias=None, residual=None, rowvec=None, rows_per_group=0, silu=False, geglu=False,
-               out_f32=False, bias_row=False, alpha=1.0, a2=None, splits=0, block_n=0, cta_pair=0, act=None):
-        """out[M,N] = a[M,K] @ w[N,K]^T (+ epilogue).  `a2` appends a second K segment ([M,K2], weights w[:, K:])."""
+               out_f32=False, bias_row=False, alpha=1.0, a2=None, splits=0, block_n=0, cta_pair=0, act=None, rows_per_sample=0):
+        """out[M,N] = a[M,K] @ w[N,K]^T (+ epilogue).  `a2` appends a second K segment ([M,K2], weights w[:, K:]).
+        `rows_per_sample`: rows of `a` that belong to one image (only read in the batch-invariant mode)."""
         ap, M, K, lda = _rows_view(a)
         wp, Nn, Kw, ldw = _rows_view(w)
         K2 = 0
@@ -150,6 +151,7 @@ class Builder:
         g.M, g.N = M, Nn
         g.out, g.ldc = out.data_ptr(), out.stride(0)
         g.splits, g.block_n, g.cta_pair = splits, block_n, cta_pair
+        g.rows_per_sample = int(rows_per_sample)
         ldr = 0
         if residual is not None:
             _, rm, rn, ldr = _rows_view(residual)
@@ -228,8 +230,9 @@ class Builder:
             out = self.empty([NB, HW, C1 + C2])
         chunks = N.lib().b200sd_groupnorm_chunks(NB, HW, C1 + C2)
         need = NB * chunks * groups * 2 * 4
-        if need > self._gn_ws.numel():
-            raise ValueError("groupnorm: partials workspace too small")
+        if need > self._gn_ws.numel():  # (sequential ops share one partials buffer; it only ever grows)
+            self._gn_ws = torch.empty(need, dtype=torch.uint8, device=self.device)
+            self.prog.keep(self._gn_ws)
         p = N.GroupNorm()
         p.x1, p.ld1, p.C1 = x1.data_ptr(), x1.stride(1), C1
         if x2 is not None:
@@ -348,14 +351,16 @@ class Builder:
         self.prog.add(N.OP_CFG_STEP, p, self.tag, (eps, x, x_out, step_table, step_counter, x0_prev, next_in, noise, eps_hist, x_saved))
         return x_out
 
-    def axpby(self, x, a, y=None, b=0.0, out=None):
+    def axpby(self, x, a, y=None, b=0.0, out=None, coef=None):
+        """out = a*x + b*y.  `coef`: optional fp32 device tensor {a, b} read at run time (overrides the baked a, b)."""
         if out is None:
             out = self.empty(x.shape, x.dtype)
         p = N.Axpby()
+        p.coef = ptr(coef)
         p.x, p.y, p.out, p.a, p.b = x.data_ptr(), ptr(y), out.data_ptr(), float(a), float(b)
         p.x_dtype, p.y_dtype, p.out_dtype = dtype_code(x), (dtype_code(y) if y is not None else 0), dtype_code(out)
         p.n = x.numel()
-        self.prog.add(N.OP_AXPBY, p, self.tag, (x, y, out))
+        self.prog.add(N.OP_AXPBY, p, self.tag, (x, y, out, coef))
         return out
 
     def image_out(self, x, C_valid, out):
@@ -384,6 +389,21 @@ class Builder:
         p.ids, p.tok, p.pos, p.out = ids.data_ptr(), tok.data_ptr(), pos.data_ptr(), out.data_ptr()
         p.rows, p.L, p.D, p.vocab = rows, Lp, D, vocab
         self.prog.add(N.OP_EMBED, p, self.tag, (ids, tok, pos, out))
+        return out
+
+    def gauss_sample(self, moments, noise, out, scale=1.0):
+        """moments [B, 2C, h, w] (mean | logvar), noise [B, C, h, w] -> out [B, C, h, w] = scale*(mean + std*noise)."""
+        B, C2, h, w = moments.shape
+        if C2 % 2 or noise.shape != (B, C2 // 2, h, w) or out.shape != noise.shape:
+            raise ValueError("gauss_sample: shapes must be [B,2C,h,w], [B,C,h,w], [B,C,h,w]")
+        for t in (moments, noise, out):
+            if not t.is_contiguous():
+                raise ValueError("gauss_sample: tensors must be contiguous NCHW")
+        p = N.GaussSample()
+        p.moments, p.noise, p.out, p.scale = moments.data_ptr(), noise.data_ptr(), out.data_ptr(), float(scale)
+        p.m_dtype, p.n_dtype, p.out_dtype = dtype_code(moments), dtype_code(noise), dtype_code(out)
+        p.B, p.C, p.hw = B, C2 // 2, h * w
+        self.prog.add(N.OP_GAUSS_SAMPLE, p, self.tag, (moments, noise, out))
         return out
 
     def step_advance(self, step_counter):

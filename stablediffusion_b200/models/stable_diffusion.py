@@ -221,18 +221,31 @@ class SDModelWrapper:
                 self._merge_text_encoder_lora(enc, parsed[part], adapter_name)
 
     def _merge_text_encoder_lora(self, enc, layers, adapter_name):
-        """Text-encoder LoRA (outside the hot path): kept as (module, delta) pairs and applied to the torch weights."""
+        """Text-encoder LoRA (outside the hot path): kept as (module, delta) pairs; the encoder's weights are always
+        RE-MERGED from an fp32 pristine copy (like the UNet's), so load / set / delete cycles do not accumulate rounding."""
         store = enc.__dict__.setdefault("_b200_lora", {})
         mods = dict(enc.named_modules())
+        flat = {name.replace(".", "_"): name for name in mods}  # kohya spelling: lora_te_text_model_encoder_layers_0_...
         from ..lora import lora_delta
 
-        ent = []
+        ent, missing = [], []
         for path, e in layers.items():
-            path = path.replace("lora_te_", "").replace("lora_te1_", "").replace("lora_te2_", "")
-            m = mods.get(path) or mods.get(path.replace("_", "."))
-            if m is None:
+            body = path
+            for pfx in ("lora_te1_", "lora_te2_", "lora_te_"):
+                if body.startswith(pfx):
+                    body = body[len(pfx):]
+                    break
+            name = body if body in mods else flat.get(body)
+            if name is None:
+                missing.append(path)
                 continue
+            m = mods[name]
+            if not hasattr(m, "_b200_pristine"):
+                m._b200_pristine = m.weight.data.detach().float().clone()
             ent.append((m, lora_delta(e)))
+        if missing:
+            raise ValueError(f"LoRA adapter '{adapter_name}' targets {len(missing)} text-encoder modules that do not exist, "
+                             f"e.g. {missing[:3]}")
         store[adapter_name] = dict(layers=ent, weight=0.0)
         enc.peft_config = {k: True for k in store}
 
@@ -241,14 +254,23 @@ class SDModelWrapper:
         if not store:
             return
         want = {n: (1.0 if w is None else float(w)) for n, w in zip(names, weights)}
+        changed = False
         for name, st in store.items():
             new_w = want.get(name, 0.0)
-            if new_w != st["weight"]:
-                for m, delta in st["layers"]:
-                    m.weight.data += ((new_w - st["weight"]) * delta).to(m.weight.device, m.weight.dtype)
-                st["weight"] = new_w
-                if isinstance(enc, B200CLIPTextModel):
-                    enc.refresh_weights()
+            changed |= new_w != st["weight"]
+            st["weight"] = new_w
+        if not changed:
+            return
+        touched = {}
+        for st in store.values():
+            for m, delta in st["layers"]:
+                acc = touched.setdefault(id(m), [m, m._b200_pristine.clone()])
+                if st["weight"] != 0.0:
+                    acc[1] += st["weight"] * delta.reshape(acc[1].shape).to(acc[1].device)
+        for m, w in touched.values():
+            m.weight.data.copy_(w.to(m.weight.device, m.weight.dtype))
+        if isinstance(enc, B200CLIPTextModel):
+            enc.refresh_weights()
 
     def set_adapters(self, adapter_names: Union[List[str], str], adapter_weights: Optional[List[float]] = None):
         names = [adapter_names] if isinstance(adapter_names, str) else list(adapter_names)

@@ -63,14 +63,16 @@ class StableDiffusionUnifiedPipeline:
         m = self.model
         sch = m.scheduler
         noise_steps = (n_steps + 63) // 64 * 64 if sch._stochastic else 0  # capacity of the pre-drawn noise, in steps
-        key = (id(m.base), id(m.base.packed), B, h, w, ctx_dim, self.do_classifier_free_guidance, sch._uses_history,
-               sch._uses_eps_history, noise_steps, blend)
+        # keyed on the UNet's pack version (monotonic; bumped by every LoRA change): an id() of the packed weights could
+        # be recycled by the allocator after a re-pack and hand back an engine that still points at the old weights
+        key = (id(m.base), m.base.pack_version, B, h, w, ctx_dim, self.do_classifier_free_guidance, sch._uses_history,
+               sch._uses_eps_history, noise_steps, blend, N.batch_invariant())
         eng = self._engines.get(key)
         if eng is None:
             eng = DenoiseEngine(m.base, B, h, w, self.do_classifier_free_guidance, ctx_dim, sch._uses_history,
                                 pair_group=self.pair_group, pair_rank=self.pair_rank, use_graph=self.use_graph,
                                 eps_history=sch._uses_eps_history, noise_steps=noise_steps, blend=blend)
-            self._engines = {k: v for k, v in self._engines.items() if k[1] == id(m.base.packed)}  # drop stale weights
+            self._engines = {k: v for k, v in self._engines.items() if k[:2] == key[:2]}  # drop engines of stale weights
             self._engines[key] = eng
         return eng
 
@@ -87,6 +89,11 @@ class StableDiffusionUnifiedPipeline:
                  # extensions (not in the reference): precomputed embeddings for synthetic / pre-encoded prompts
                  prompt_embeds=None, negative_prompt_embeds=None, pooled_prompt_embeds=None,
                  negative_pooled_prompt_embeds=None):
+        if cross_attention_kwargs and cross_attention_kwargs.get("scale", None) not in (None, 1.0):
+            # the reference forwards this to PEFT, which scales every LoRA layer for the call (:190, :479); here adapters are
+            # MERGED into the packed weights, so a per-call scale cannot be honoured silently
+            raise ValueError("cross_attention_kwargs['scale'] != 1 is applied at merge time on this path: "
+                             "use model.set_adapters(names, weights) instead")
         if self.device.type != "cuda":
             raise RuntimeError("StableDiffusionUnifiedPipeline(device=...) must be a CUDA device: there is no CPU path")
         if not isinstance(model.base, B200UNet) or not isinstance(model.vae, B200VAE) or not isinstance(model.scheduler, _SchedulerBase):

@@ -61,6 +61,9 @@ class _SchedulerBase:
         self._table: Optional[torch.Tensor] = None       # host fp32 [n, STEP_ROW]
         self._dev: Dict[str, torch.Tensor] = {}
         self._programs: Dict[tuple, dict] = {}
+        self._ew_programs: Dict[tuple, dict] = {}        # shape-keyed AXPBY programs (independent of the timestep table)
+        self._coef_dev: Dict[tuple, torch.Tensor] = {}   # device copies of the (a, b) pairs they are run with
+        self._start = 0                                  # schedule position of the first un-fused step() call
         self.device = torch.device("cpu")
 
     @classmethod
@@ -100,19 +103,36 @@ class _SchedulerBase:
 
     def _init_step_index(self, timestep):
         if self._step_index is None:
-            self._step_index = self.index_for_timestep(timestep)
+            self._step_index = self._start = self.index_for_timestep(timestep)
 
     # ---- un-fused device calls (the reference's call pattern) ----------------------------------------
     def _elementwise(self, x, a, y=None, bcoef=0.0):
-        """out = a*x + b*y via the library's AXPBY kernel (shape-cached one-op program)."""
+        """out = a*x + b*y via the library's AXPBY kernel: ONE planned op per (shape, dtype), its coefficients read from
+        device memory, enqueued on the caller's stream without any host synchronisation."""
         if x.device.type != "cuda":
             raise RuntimeError("B200 schedulers operate on CUDA tensors only (no CPU path)")
-        x = x.contiguous()
-        b = L.Builder(x.device, workspace_bytes=16)
-        out = b.axpby(x, a, y=None if y is None else y.contiguous().to(x.dtype), b=bcoef)
-        b.prog.run(torch.cuda.current_stream(x.device).cuda_stream)
-        torch.cuda.current_stream(x.device).synchronize()
-        return out
+        key = ("axpby", tuple(x.shape), x.dtype, y is not None, x.device)
+        st = self._ew_programs.get(key)
+        if st is None:
+            b = L.Builder(x.device, workspace_bytes=16)
+            st = dict(b=b, x=b.empty(x.shape, x.dtype), y=b.empty(x.shape, x.dtype) if y is not None else None,
+                      coef=b.zeros([2], torch.float32), out=b.empty(x.shape, x.dtype))
+            b.axpby(st["x"], 1.0, y=st["y"], b=0.0, out=st["out"], coef=st["coef"])
+            self._ew_programs[key] = st
+        st["x"].copy_(x)
+        if y is not None:
+            st["y"].copy_(y)
+        # the coefficient pair lives on the device: uploaded once per distinct (a, b) — i.e. once per sampler step of the
+        # first trajectory of a schedule — and moved into the op's slot by a device-to-device copy afterwards
+        ck = (float(a), float(bcoef), x.device)
+        cd = self._coef_dev.get(ck)
+        if cd is None:
+            if len(self._coef_dev) > 4096:
+                self._coef_dev.clear()
+            cd = self._coef_dev[ck] = torch.tensor([float(a), float(bcoef)], dtype=torch.float32, device=x.device)
+        st["coef"].copy_(cd)
+        st["b"].prog.run(torch.cuda.current_stream(x.device).cuda_stream)
+        return st["out"].clone()
 
     def scale_model_input(self, sample, timestep=None):
         return sample
@@ -125,7 +145,7 @@ class _SchedulerBase:
         if dev.type != "cuda":
             raise RuntimeError("B200 schedulers operate on CUDA tensors only (no CPU path)")
         B, C, h, w = sample.shape
-        key = ("step", B, C, h, w, sample.dtype, model_output.dtype)
+        key = ("step", self._start, B, C, h, w, sample.dtype, model_output.dtype)
         st = self._programs.get(key)
         if st is None:
             b = L.Builder(dev, workspace_bytes=16)
@@ -157,7 +177,15 @@ class _SchedulerBase:
         return (prev,)
 
     def _unfused_table(self, dev):
-        return self.step_table(dev)
+        """Table of the un-fused calls.  A multistep solver has no history on its FIRST call wherever that lands in the
+        schedule (img2img starts mid-table; diffusers runs that step first-order: lower_order_nums == 0), so the row of
+        the first executed position gets C1 = 0 — the same thing DenoiseEngine.load does for the fused loop."""
+        key = f"unfused{self._start}@{dev}"
+        if key not in self._dev:
+            tab = self._table.clone()
+            tab[self._start, N.ST_C1] = 0.0
+            self._dev[key] = tab.to(dev)
+        return self._dev[key]
 
     def _unfused_counter(self) -> int:
         return self._step_index
@@ -214,7 +242,7 @@ class B200EulerDiscreteScheduler(_SchedulerBase):
             ts -= 1
         else:
             raise ValueError(f"{sp} is not supported")
-        sig = np.array(((1 - self.alphas_cumprod) / self.alphas_cumprod) ** 0.5)
+        sig = (((1 - self.alphas_cumprod) / self.alphas_cumprod) ** 0.5).numpy()
         sig = np.interp(ts, np.arange(0, len(sig)), sig)
         sig = torch.from_numpy(sig).to(dtype=torch.float32)
         self._timesteps_host = ts.astype(np.float32)
@@ -309,8 +337,26 @@ class B200DPMSolverMultistepScheduler(_SchedulerBase):
         c = self.config
         if c["algorithm_type"] != "dpmsolver++" or c["solver_order"] != 2 or c["solver_type"] != "midpoint":
             raise ValueError("only dpmsolver++ / order 2 / midpoint (DPM++ 2M) is on the hot path; the SDE variant is a 'next' row")
-        if c["timestep_spacing"] != "linspace" or c["final_sigmas_type"] != "zero":
-            raise ValueError("DPM++ 2M: only linspace spacing with final sigma zero is supported")
+        if c["timestep_spacing"] not in ("linspace", "leading", "trailing") or c["final_sigmas_type"] != "zero":
+            raise ValueError("DPM++ 2M: timestep_spacing must be linspace / leading / trailing, final sigma zero")
+
+    def _spaced_timesteps(self, n: int) -> np.ndarray:
+        """diffusers 0.27.2 DPMSolverMultistepScheduler / UniPCMultistepScheduler.set_timesteps (lambda_min_clipped = -inf,
+        so last_timestep = num_train_timesteps).  The SDXL scheduler config sets timestep_spacing="leading" explicitly
+        (scripts/convert_from_A1111.py:947-959), and `from_config` carries it over to these classes."""
+        c = self.config
+        ntrain = c["num_train_timesteps"]
+        sp = c["timestep_spacing"]
+        if sp == "linspace":
+            return np.linspace(0, ntrain - 1, n + 1).round()[::-1][:-1].copy().astype(np.int64)
+        if sp == "leading":
+            step_ratio = ntrain // (n + 1)
+            ts = (np.arange(0, n + 1) * step_ratio).round()[::-1][:-1].copy().astype(np.int64)
+            return ts + c["steps_offset"]
+        if sp == "trailing":
+            step_ratio = ntrain / n
+            return np.arange(ntrain, 0, -step_ratio).round().copy().astype(np.int64) - 1
+        raise ValueError(f"{sp} is not supported")
 
     @staticmethod
     def _sigma_to_t(sigma, log_sigmas):
@@ -327,8 +373,8 @@ class B200DPMSolverMultistepScheduler(_SchedulerBase):
         c = self.config
         ntrain = c["num_train_timesteps"]
         n = self.num_inference_steps = int(num_inference_steps)
-        ts = np.linspace(0, ntrain - 1, n + 1).round()[::-1][:-1].copy().astype(np.int64)
-        sig = np.array(((1 - self.alphas_cumprod) / self.alphas_cumprod) ** 0.5)
+        ts = self._spaced_timesteps(n)
+        sig = (((1 - self.alphas_cumprod) / self.alphas_cumprod) ** 0.5).numpy()
         log_sig = np.log(sig)
         if c["use_karras_sigmas"]:
             sflip = np.flip(sig).copy()
@@ -407,8 +453,8 @@ class B200DPMSolverSDEScheduler(B200DPMSolverMultistepScheduler):
         c = self.config
         if c["algorithm_type"] != "sde-dpmsolver++" or c["solver_order"] != 2 or c["solver_type"] != "midpoint":
             raise ValueError("only sde-dpmsolver++ / order 2 / midpoint is supported")
-        if c["timestep_spacing"] != "linspace" or c["final_sigmas_type"] != "zero":
-            raise ValueError("DPM++ 2M SDE: only linspace spacing with final sigma zero is supported")
+        if c["timestep_spacing"] not in ("linspace", "leading", "trailing") or c["final_sigmas_type"] != "zero":
+            raise ValueError("DPM++ 2M SDE: timestep_spacing must be linspace / leading / trailing, final sigma zero")
 
     def _build_table(self):
         n = self.num_inference_steps
@@ -560,8 +606,9 @@ class B200UniPCMultistepScheduler(B200DPMSolverMultistepScheduler):
         c = self.config
         if c["solver_order"] != 2 or c["solver_type"] != "bh2" or not c["predict_x0"] or not c["lower_order_final"]:
             raise ValueError("UniPC: only order 2 / bh2 / predict_x0 / lower_order_final (the class defaults) are supported")
-        if c["timestep_spacing"] != "linspace" or c["final_sigmas_type"] != "zero" or c["disable_corrector"]:
-            raise ValueError("UniPC: only linspace spacing, final sigma zero and the corrector on every step are supported")
+        if (c["timestep_spacing"] not in ("linspace", "leading", "trailing") or c["final_sigmas_type"] != "zero"
+                or c["disable_corrector"]):
+            raise ValueError("UniPC: timestep_spacing must be linspace / leading / trailing, final sigma zero, corrector on")
 
     def _lam(self, sigma):
         a, s = self._alpha_sigma(sigma)

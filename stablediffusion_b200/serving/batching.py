@@ -67,7 +67,9 @@ class RequestBatcher:
         kind = "embeds" if "prompt_embeds" in c else "text"
         if kind == "embeds" and ("pooled_prompt_embeds" in c):
             return None  # SDXL pre-encoded jobs: run alone (keeps this helper small)
-        return (kind, getattr(self.model, "scheduler_name", None)) + tuple(c.get(k) for k in _MERGE_KEYS)
+        # pre-encoded jobs with and without negative embeddings do not mix (a merged call needs all or none)
+        has_neg = kind == "embeds" and c.get("negative_prompt_embeds") is not None
+        return (kind, has_neg, getattr(self.model, "scheduler_name", None)) + tuple(c.get(k) for k in _MERGE_KEYS)
 
     def plan(self) -> List[List[_Request]]:
         """Greedy first-fit in arrival order: a batch takes later compatible jobs while they fit."""
@@ -112,17 +114,30 @@ class RequestBatcher:
                 kw["negative_prompt_embeds"] = torch.cat([r.config["negative_prompt_embeds"] for r in batch])
             dtype = kw["prompt_embeds"].dtype
         else:
-            prompts, negs = [], []
+            # the second text encoder's prompts (SDXL; the reference worker sets both, handler_logic.py:315-327) follow the
+            # pipeline's own defaults per request: prompt_2 = prompt, negative_prompt_2 = negative_prompt (:600, :620-621)
+            prompts, negs, prompts2, negs2 = [], [], [], []
             for r in batch:
                 c = r.config
                 per = int(c.get("num_images_per_prompt") or 1)
                 p = _as_list(c["prompt"])
-                npmt = c.get("negative_prompt") or ""
-                npmt = [npmt] * len(p) if isinstance(npmt, str) else list(npmt)
-                for a, b in zip(p, npmt):   # num_images_per_prompt is unrolled so that one merged call serves all
+
+                def per_prompt(v, default):
+                    v = v or default
+                    return [v] * len(p) if isinstance(v, str) else list(v)
+                npmt = per_prompt(c.get("negative_prompt"), "")
+                p2 = per_prompt(c.get("prompt_2"), p)
+                n2 = per_prompt(c.get("negative_prompt_2"), npmt)
+                if not (len(npmt) == len(p2) == len(n2) == len(p)):
+                    raise ValueError("prompt, prompt_2, negative_prompt and negative_prompt_2 of a job must have the same length")
+                for a, b, a2, b2 in zip(p, npmt, p2, n2):   # num_images_per_prompt is unrolled so that one merged call serves all
                     prompts += [a] * per
                     negs += [b] * per
+                    prompts2 += [a2] * per
+                    negs2 += [b2] * per
             kw["prompt"], kw["negative_prompt"] = prompts, negs
+            if any(r.config.get("prompt_2") is not None or r.config.get("negative_prompt_2") is not None for r in batch):
+                kw["prompt_2"], kw["negative_prompt_2"] = prompts2, negs2
             dtype = getattr(self.model.base, "dtype", torch.bfloat16)
         kw["latents"] = torch.cat([self._latents_for(r, device, dtype) for r in batch])
         self.calls += 1

@@ -4,7 +4,7 @@ Mirrors `convert_pt_to_numpy` of the reference (runpod-worker/handler_logic.py:2
 ([-1, 1], NCHW) becomes a list of uint8 HWC arrays.  The reference does it image by image with five eager torch
 ops and a blocking `.cpu()` each; here ONE kernel (`B200SD_OP_IMAGE_U8`) converts the whole batch, and ONE copy
 into pinned host memory brings 3 bytes per pixel back instead of 6 (fp16) — the arithmetic is rounded exactly like
-torch's eager ops on the tensor's dtype, so the bytes are the reference's bytes (tests/test_output_stage_gpu.py).
+torch's eager ops on the tensor's dtype, so the bytes are the reference's bytes (tests/test_output_stage.py).
 
 No CPU fallback: a tensor that is not on an sm_100 device raises.
 """

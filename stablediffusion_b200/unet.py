@@ -296,23 +296,24 @@ class UNetLowering:
         tok = NB * H * W
         d = C // heads
         hn = b.groupnorm(x.view(NB, H * W, C), T[f"{p}.norm.g"], T[f"{p}.norm.b"], 1e-6, False)
-        t = b.linear(hn.view(tok, C), T[f"{p}.proj_in.w"], bias=T[f"{p}.proj_in.b"])
+        rps = H * W  # rows per image (batch-invariant tiling hint)
+        t = b.linear(hn.view(tok, C), T[f"{p}.proj_in.w"], bias=T[f"{p}.proj_in.b"], rows_per_sample=rps)
         for k in range(layers):
             blk = f"{p}.transformer_blocks.{k}"
             n1 = b.layernorm(t, T[f"{blk}.norm1.g"], T[f"{blk}.norm1.b"], 1e-5)
-            qkv = b.linear(n1, T[f"{blk}.attn1.qkv.w"]).view(NB, H * W, 3 * C)
+            qkv = b.linear(n1, T[f"{blk}.attn1.qkv.w"], rows_per_sample=rps).view(NB, H * W, 3 * C)
             a1 = b.attention(qkv[:, :, :C], qkv[:, :, C:2 * C], qkv[:, :, 2 * C:], heads, d, d ** -0.5)
-            b.linear(a1.view(tok, C), T[f"{blk}.attn1.out.w"], bias=T[f"{blk}.attn1.out.b"], residual=t, out=t)
+            b.linear(a1.view(tok, C), T[f"{blk}.attn1.out.w"], bias=T[f"{blk}.attn1.out.b"], residual=t, out=t, rows_per_sample=rps)
             n2 = b.layernorm(t, T[f"{blk}.norm2.g"], T[f"{blk}.norm2.b"], 1e-5)
-            q2 = b.linear(n2, T[f"{blk}.attn2.q.w"]).view(NB, H * W, C)
+            q2 = b.linear(n2, T[f"{blk}.attn2.q.w"], rows_per_sample=rps).view(NB, H * W, C)
             off = self.pk.kv_off[p][k]
             kv = self.ctx_kv.view(NB, self.ctx_len, -1)
             a2 = b.attention(q2, kv[:, :, off:off + C], kv[:, :, off + C:off + 2 * C], heads, d, d ** -0.5)
-            b.linear(a2.view(tok, C), T[f"{blk}.attn2.out.w"], bias=T[f"{blk}.attn2.out.b"], residual=t, out=t)
+            b.linear(a2.view(tok, C), T[f"{blk}.attn2.out.w"], bias=T[f"{blk}.attn2.out.b"], residual=t, out=t, rows_per_sample=rps)
             n3 = b.layernorm(t, T[f"{blk}.norm3.g"], T[f"{blk}.norm3.b"], 1e-5)
-            gg = b.linear(n3, T[f"{blk}.ff1.w"], bias=T[f"{blk}.ff1.b"], geglu=True, block_n=geglu_block_n(8 * C))
-            b.linear(gg, T[f"{blk}.ff2.w"], bias=T[f"{blk}.ff2.b"], residual=t, out=t)
-        out = b.linear(t, T[f"{p}.proj_out.w"], bias=T[f"{p}.proj_out.b"], residual=x.view(tok, C))
+            gg = b.linear(n3, T[f"{blk}.ff1.w"], bias=T[f"{blk}.ff1.b"], geglu=True, block_n=geglu_block_n(8 * C), rows_per_sample=rps)
+            b.linear(gg, T[f"{blk}.ff2.w"], bias=T[f"{blk}.ff2.b"], residual=t, out=t, rows_per_sample=rps)
+        out = b.linear(t, T[f"{p}.proj_out.w"], bias=T[f"{p}.proj_out.b"], residual=x.view(tok, C), rows_per_sample=rps)
         return out.view(NB, H, W, C)
 
     def emit(self, unet_in, ctx, t_explicit=None, step_table=None, step_counter=None, text_embeds=None, time_ids=None):
@@ -324,25 +325,25 @@ class UNetLowering:
         # --- time embedding ---------------------------------------------------------
         te = b.timestep_embed(NB, c0, t=t_explicit, t_stride=0, step_table=step_table, step_counter=step_counter,
                               flip_sin_to_cos=cfg["flip_sin_to_cos"], freq_shift=cfg["freq_shift"])
-        e1 = b.linear(te, T["time_embedding.linear_1.w"], bias=T["time_embedding.linear_1.b"], silu=True)
+        e1 = b.linear(te, T["time_embedding.linear_1.w"], bias=T["time_embedding.linear_1.b"], silu=True, rows_per_sample=1)
         if cfg.get("addition_embed_type") == "text_time":
             # SDXL: emb = time_embedding(t) + add_embedding([text_embeds | embed(time_ids)]); resnets consume silu(emb).
             # emb is kept fp32 and enters the last GEMM as a per-row vector, which the epilogue adds BEFORE the SiLU.
-            emb = b.linear(e1, T["time_embedding.linear_2.w"], bias=T["time_embedding.linear_2.b"], out_f32=True)
+            emb = b.linear(e1, T["time_embedding.linear_2.w"], bias=T["time_embedding.linear_2.b"], out_f32=True, rows_per_sample=1)
             adim = cfg["addition_time_embed_dim"]
             nids = time_ids.shape[1]
             tid = b.timestep_embed(NB * nids, adim, t=time_ids.view(-1), t_stride=1,
                                    flip_sin_to_cos=cfg["flip_sin_to_cos"], freq_shift=cfg["freq_shift"])
             a1 = b.linear(text_embeds, T["add_embedding.linear_1.w"], bias=T["add_embedding.linear_1.b"], silu=True,
-                          a2=tid.view(NB, nids * adim))
+                          a2=tid.view(NB, nids * adim), rows_per_sample=1)
             silu_emb = b.linear(a1, T["add_embedding.linear_2.w"], bias=T["add_embedding.linear_2.b"], rowvec=emb,
-                                rows_per_group=1, silu=True)
+                                rows_per_group=1, silu=True, rows_per_sample=1)
         else:
-            silu_emb = b.linear(e1, T["time_embedding.linear_2.w"], bias=T["time_embedding.linear_2.b"], silu=True)
-        self.temb_all = b.linear(silu_emb, T["temb_all.w"], bias=T["temb_all.b"], out_f32=True)
+            silu_emb = b.linear(e1, T["time_embedding.linear_2.w"], bias=T["time_embedding.linear_2.b"], silu=True, rows_per_sample=1)
+        self.temb_all = b.linear(silu_emb, T["temb_all.w"], bias=T["temb_all.b"], out_f32=True, rows_per_sample=1)
         # --- every cross-attention K/V projection of the network in one GEMM --------------------------
         D = ctx.shape[-1]
-        self.ctx_kv = b.linear(ctx.view(NB * self.ctx_len, D), T["ctx_kv.w"])
+        self.ctx_kv = b.linear(ctx.view(NB * self.ctx_len, D), T["ctx_kv.w"], rows_per_sample=self.ctx_len)
         # --- down path --------------------------------------------------------------------------------
         x = b.conv(unet_in.view(NB, h, w, self.pk.cin_pad), T["conv_in.w"], bias=T["conv_in.b"])
         skips = [x]
@@ -404,6 +405,7 @@ class B200UNet:
         self._adapters: "OrderedDict[str, dict]" = OrderedDict()
         self._adapter_weights: Dict[str, float] = {}
         self.packed: Optional[PackedUNet] = None
+        self.pack_version = 0  # bumped by every re-pack (LoRA load / set / delete): cache key of everything built on `packed`
         self._programs: Dict[tuple, dict] = {}
         if cfg_is_sdxl(self.config):
             self.add_embedding = _AddEmbeddingShim(self.config["projection_class_embeddings_input_dim"])
@@ -416,6 +418,7 @@ class B200UNet:
 
         sd = merged_state_dict(self._master, self._adapters, self._adapter_weights, prefix="unet")
         self.packed = PackedUNet(self.config, sd, self.device)
+        self.pack_version += 1
         self._programs.clear()
 
     def to(self, device=None, dtype=None):

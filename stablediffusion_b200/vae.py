@@ -210,7 +210,7 @@ class VAELowering:
         NB, H, W, C = x.shape
         HW = H * W
         hn = b.groupnorm(x.view(NB, HW, C), T[f"{a}.norm.g"], T[f"{a}.norm.b"], 1e-6, False)
-        qk = b.linear(hn.view(NB * HW, C), T[f"{a}.qk.w"], bias=T[f"{a}.qk.b"]).view(NB, HW, 2 * C)
+        qk = b.linear(hn.view(NB * HW, C), T[f"{a}.qk.w"], bias=T[f"{a}.qk.b"], rows_per_sample=HW).view(NB, HW, 2 * C)
         o = b.empty([NB, HW, C])
         S = b.empty([HW, HW])
         vT = b.empty([C, HW])
@@ -220,7 +220,7 @@ class VAELowering:
             b.linear(qk[n, :, :C], qk[n, :, C:], out=S)
             b.softmax_rows(S, C ** -0.5, out=S)
             b.linear(S, vT, out=o[n])
-        out = b.linear(o.view(NB * HW, C), T[f"{a}.out.w"], bias=T[f"{a}.out.b"], residual=x.view(NB * HW, C))
+        out = b.linear(o.view(NB * HW, C), T[f"{a}.out.w"], bias=T[f"{a}.out.b"], residual=x.view(NB * HW, C), rows_per_sample=HW)
         return out.view(NB, H, W, C)
 
     def mid(self, p, x):
@@ -232,7 +232,7 @@ class VAELowering:
     def decode(self, z_in, NB, h, w):
         """z_in: bf16 [NB, h*w, 8] latents (already divided by scaling_factor).  Returns bf16 [NB, 8h*8w, C_out]."""
         b, T, s = self.b, self.T, self.pk.s
-        z = b.linear(z_in.view(NB * h * w, z_in.shape[-1]), T["post_quant_conv.w"], bias=T["post_quant_conv.b"])
+        z = b.linear(z_in.view(NB * h * w, z_in.shape[-1]), T["post_quant_conv.w"], bias=T["post_quant_conv.b"], rows_per_sample=h * w)
         x = b.conv(z.view(NB, h, w, z.shape[-1]), T["decoder.conv_in.w"], bias=T["decoder.conv_in.b"])
         x = self.mid("decoder.mid_block", x)
         for blk in s["dec"]:
@@ -260,21 +260,46 @@ class VAELowering:
         NB, h, w, C = x.shape
         hn = b.groupnorm(x.view(NB, h * w, C), T["encoder.conv_norm_out.g"], T["encoder.conv_norm_out.b"], 1e-6, True)
         m = b.conv(hn.view(NB, h, w, C), T["encoder.conv_out.w"], bias=T["encoder.conv_out.b"])
-        q = b.linear(m.view(NB * h * w, m.shape[-1]), T["quant_conv.w"], bias=T["quant_conv.b"])
+        q = b.linear(m.view(NB * h * w, m.shape[-1]), T["quant_conv.w"], bias=T["quant_conv.b"], rows_per_sample=h * w)
         return q.view(NB, h * w, q.shape[-1])
 
 
 class _LatentDist:
-    """`vae.encode(x).latent_dist` (diffusers DiagonalGaussianDistribution) — sample = mean + std * randn(generator)."""
+    """`vae.encode(x).latent_dist` (diffusers DiagonalGaussianDistribution).  `sample(generator)` — the call the pipeline
+    makes (:98-106, :1027) — is ONE library kernel (OP_GAUSS_SAMPLE: mean + exp(0.5*clamp(logvar,-30,20)) * noise in fp32
+    from the encoder's fp32 moments); torch only draws the standard-normal noise from the caller's generator, in the
+    order the reference draws it (App. D7).  `mean` / `logvar` / `std` are inspection accessors, not on the path."""
 
-    def __init__(self, moments_nchw: torch.Tensor):
-        self.mean, logvar = moments_nchw.chunk(2, dim=1)
-        self.logvar = logvar.clamp(-30.0, 20.0)
-        self.std = torch.exp(0.5 * self.logvar)
+    def __init__(self, moments_nchw: torch.Tensor, dtype: torch.dtype):
+        self._moments = moments_nchw  # fp32 [B, 2C, h, w]
+        self._dtype = dtype
+        self._prog = None
+
+    @property
+    def mean(self):
+        return self._moments.chunk(2, dim=1)[0].to(self._dtype)
+
+    @property
+    def logvar(self):
+        return self._moments.chunk(2, dim=1)[1].clamp(-30.0, 20.0).to(self._dtype)
+
+    @property
+    def std(self):
+        return torch.exp(0.5 * self._moments.chunk(2, dim=1)[1].clamp(-30.0, 20.0)).to(self._dtype)
 
     def sample(self, generator=None):
-        noise = torch.randn(self.mean.shape, generator=generator, device=self.mean.device, dtype=self.mean.dtype)
-        return self.mean + self.std * noise
+        m = self._moments
+        B, C2, h, w = m.shape
+        noise = torch.randn((B, C2 // 2, h, w), generator=generator, device=m.device, dtype=self._dtype)
+        if self._prog is None:
+            b = L.Builder(m.device, workspace_bytes=16)
+            self._noise = b.empty(noise.shape, self._dtype)
+            self._out = b.empty(noise.shape, self._dtype)
+            b.gauss_sample(m, self._noise, self._out)
+            self._prog = b
+        self._noise.copy_(noise)
+        self._prog.prog.run(torch.cuda.current_stream(m.device).cuda_stream)
+        return self._out.clone()
 
     def mode(self):
         return self.mean
@@ -363,4 +388,4 @@ class B200VAE:
         st = self._encode_program(NB, H, W, x.dtype)
         st["x"].copy_(x)
         st["b"].prog.run(torch.cuda.current_stream(self.device).cuda_stream)
-        return _EncodeOut(_LatentDist(st["out"].clone().to(x.dtype)))
+        return _EncodeOut(_LatentDist(st["out"].clone(), x.dtype))

@@ -12,12 +12,8 @@ def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a B200 (sm_100a) GPU; run with -m gpu")
 
 
-def pytest_collection_modifyitems(config, items):
-    # GPU tests never run silently on a machine without a GPU: they are deselected by `-m "not gpu"`,
-    # and if selected without a device they fail loudly (no CPU fallback exists).
-    pass
-
-
+# GPU tests never run silently on a machine without a GPU: they are deselected by `-m "not gpu"`, and if selected without
+# a device the fixture below fails them loudly (no CPU fallback exists).
 @pytest.fixture(scope="session")
 def cuda_device():
     import torch

@@ -38,7 +38,7 @@ def test_library_has_no_libcuda_link_dependency():
 
 def test_struct_layouts_match_header():
     lib = N.lib()
-    assert lib.b200sd_abi_version() == N.ABI_VERSION == 2
+    assert lib.b200sd_abi_version() == N.ABI_VERSION == 3
     assert lib.b200sd_sizeof_op() == C.sizeof(N.Op)
     for kind, st in N.STRUCT_OF_KIND.items():
         assert lib.b200sd_sizeof_struct(kind) == C.sizeof(st), st.__name__
@@ -77,6 +77,42 @@ def test_planning_helpers_run_without_gpu():
     assert lib.b200sd_gemm_workspace_bytes(C.byref(g)) == N.ERR_INVALID
     assert "multiple of 8" in N.last_error()
     assert 1 <= lib.b200sd_groupnorm_chunks(2, 4096, 320) <= 4096 // 16
+
+
+def test_batch_invariant_mode_pins_reduction_order_choices():
+    """In the batch-invariant mode the split-K factor and the GroupNorm chunking follow the per-image shape only."""
+    lib = N.lib()
+
+    def splits(M, rps, K=11520, Nn=1280):
+        g = N.Gemm()
+        g.nseg, g.M, g.N, g.rows_per_sample = 1, M, Nn, rps
+        g.seg[0].channels, g.seg[0].taps = K, 1
+        ws = lib.b200sd_gemm_workspace_bytes(C.byref(g))
+        assert ws >= 0
+        return ws
+
+    def conv_ws(NB, H=8, W=8, Cin=1280, Nn=1280):
+        g = N.Gemm()
+        g.spatial, g.nseg, g.N, g.NB, g.H, g.W, g.M = 1, 1, Nn, NB, H, W, NB * H * W
+        g.seg[0].channels, g.seg[0].taps = Cin, 9
+        ws = lib.b200sd_gemm_workspace_bytes(C.byref(g))
+        assert ws >= 0
+        return ws
+
+    prev = N.set_batch_invariant(False)
+    try:
+        assert splits(128, 64) > 0 and splits(16384, 64) == 0            # default: the factor follows M
+        N.set_batch_invariant(True)
+        assert N.batch_invariant()
+        per_row = {splits(M, 64) // ((M + 127) // 128) for M in (128, 256, 1024, 4096)}
+        assert len(per_row) == 1, per_row                                 # same split factor at every batch (workspace ~ M tiles)
+        per_img = {conv_ws(NB) // ((NB * 64 + 127) // 128) for NB in (2, 4, 16, 32)}
+        assert len(per_img) == 1, per_img
+        ch = {lib.b200sd_groupnorm_chunks(NB, 4096, 320) for NB in (1, 2, 8, 16, 64)}
+        assert len(ch) == 1, ch
+    finally:
+        N.set_batch_invariant(prev)
+    assert len({lib.b200sd_groupnorm_chunks(NB, 4096, 320) for NB in (1, 64)}) == 2
 
 
 def test_compute_fails_loudly_without_gpu():

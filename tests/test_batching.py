@@ -48,6 +48,30 @@ def test_compatible_jobs_share_calls_and_keep_their_noise():
     assert futs[6].result().shape[0] == 1 and "latents" not in pipe.calls[2]      # ran alone, untouched config
 
 
+def test_second_encoder_prompts_are_forwarded_per_request():
+    """SDXL jobs carry prompt_2 / negative_prompt_2 (the reference worker sets both, handler_logic.py:315-327): a merged call
+    hands every request its own, with the pipeline's defaults (prompt_2 = prompt, negative_prompt_2 = negative_prompt)."""
+    pipe = _FakePipe()
+    rb = RequestBatcher(pipe, _model(), max_batch=8)
+    rb.submit(prompt="a", prompt_2="a2", negative_prompt="na", seed=1)
+    rb.submit(prompt=["b", "c"], negative_prompt_2=["nb2", "nc2"], seed=2)
+    assert rb.run_pending() == 1
+    kw = pipe.calls[0]
+    assert kw["prompt"] == ["a", "b", "c"] and kw["prompt_2"] == ["a2", "b", "c"]
+    assert kw["negative_prompt"] == ["na", "", ""] and kw["negative_prompt_2"] == ["na", "nb2", "nc2"]
+    pipe.calls.clear()
+    rb.submit(prompt="a", seed=1)
+    rb.submit(prompt="b", seed=2)
+    rb.run_pending()
+    assert "prompt_2" not in pipe.calls[0]          # SD1.5-style jobs: nothing extra is passed
+    # pre-encoded jobs with and without negative embeddings never share a call
+    pipe.calls.clear()
+    e = torch.zeros(1, 77, 8)
+    rb.submit(prompt_embeds=e, negative_prompt_embeds=e, seed=1)
+    rb.submit(prompt_embeds=e, seed=2)
+    assert rb.run_pending() == 2
+
+
 def test_incompatible_jobs_run_alone():
     pipe, model = _FakePipe(), _model()
     b = RequestBatcher(pipe, model, max_batch=8)

@@ -250,3 +250,115 @@ def test_param_shapes_match_oracle_strictly():
         with torch.device("meta"):
             osd = {k: tuple(v.shape) for k, v in UNet2DConditionOracle(**oc).state_dict().items()}
         assert osd == {k: tuple(v) for k, v in unet_param_shapes(unet_config(mt)).items()}
+
+
+# ---------------------------------------------------------------------------------------------------
+# round-2 advisor findings
+# ---------------------------------------------------------------------------------------------------
+ALL_NAMES = ("euler", "euler_a", "DDIM", "DPM++ 2M", "DPM++ 2M Karras", "DPM++ 2M SDE Karras", "PNDM", "uni_pc")
+
+
+@pytest.mark.parametrize("model_type", ["sd15", "sdxl"])
+@pytest.mark.parametrize("name", ALL_NAMES)
+def test_every_scheduler_name_builds_from_both_model_configs(name, model_type):
+    """The reference's set_scheduler (models/stable_diffusion.py:199-227) accepts every name on SD1.5 AND SDXL; the SDXL
+    scheduler config carries timestep_spacing="leading" / steps_offset=1 into every class through from_config."""
+    base = B200EulerDiscreteScheduler(**scheduler_config(model_type))
+    s = make_scheduler(name, base.config)
+    s.set_timesteps(30)
+    o = OS.make_scheduler(name, dict(OS.SDXL_SCHEDULER_CONFIG if model_type == "sdxl" else OS.SD15_SCHEDULER_CONFIG))
+    o.set_timesteps(30)
+    assert s.timesteps.dtype == o.timesteps.dtype and torch.equal(s.timesteps.cpu(), o.timesteps)
+    if model_type == "sdxl" and name in ("DPM++ 2M", "uni_pc", "DPM++ 2M SDE Karras"):
+        # leading spacing of the multistep solvers: arange(0, n+1) * (1000 // (n+1)), reversed, last dropped, + steps_offset
+        assert s.timesteps.tolist()[:3] == [961, 929, 897] and s.timesteps.tolist()[-1] == 33
+
+
+@pytest.mark.parametrize("name", ["DPM++ 2M", "uni_pc", "DPM++ 2M SDE Karras", "DPM++ 2M Karras"])
+def test_multistep_solvers_on_the_sdxl_config_follow_the_oracle(name):
+    s = make_scheduler(name, B200EulerDiscreteScheduler(**scheduler_config("sdxl")).config)
+    s.set_timesteps(12)
+    o = OS.make_scheduler(name, dict(OS.SDXL_SCHEDULER_CONFIG))
+    o.set_timesteps(12)
+    g = torch.Generator().manual_seed(3)
+    x = torch.randn(1, 4, 8, 8, generator=g)
+    xo, ks = x.clone(), _KernelState(x)
+    for i, t in enumerate(o.timesteps):
+        eps, noise = torch.randn(1, 4, 8, 8, generator=g), torch.randn(1, 4, 8, 8, generator=g)
+        xo = o.step(eps, t, xo, noise) if name in OS.STOCHASTIC else o.step(eps, t, xo)
+        x = ks.step(s._table[i], x, eps, noise, s)
+        torch.testing.assert_close(x, xo, rtol=5e-5, atol=5e-5)
+
+
+def test_unfused_multistep_first_call_is_first_order_wherever_it_starts():
+    """img2img hands scheduler.step a timestep from the middle of the schedule: diffusers runs that first call
+    first-order (no history yet), so the un-fused table must carry C1 = 0 on ITS first row, not on row 0 only."""
+    s = make_scheduler("DPM++ 2M", B200EulerDiscreteScheduler(**CFG).config)
+    s.set_timesteps(20)
+    assert s._table[8, N.ST_C1] != 0
+    s._init_step_index(s.timesteps[8])
+    tab = s._unfused_table("cpu")
+    assert tab[8, N.ST_C1] == 0 and tab[9, N.ST_C1] == s._table[9, N.ST_C1] != 0
+    o = OS.make_scheduler("DPM++ 2M", CFG)
+    o.set_timesteps(20)
+    g = torch.Generator().manual_seed(5)
+    x = torch.randn(1, 4, 8, 8, generator=g)
+    xo, ks = x.clone(), _KernelState(x)
+    for i in range(8, 20):
+        eps = torch.randn(1, 4, 8, 8, generator=g)
+        xo = o.step(eps, o.timesteps[i], xo)
+        x = ks.step(tab[i], x, eps, None, s)
+        torch.testing.assert_close(x, xo, rtol=5e-5, atol=5e-5)
+
+
+def test_lora_with_unresolvable_modules_raises_instead_of_loading_as_a_noop():
+    from stablediffusion_b200.lora import parse_lora_state_dict
+
+    mods = ["down_blocks.0.attentions.0.transformer_blocks.0.attn1.to_q"]
+    good = {"lora_unet_down_blocks_0_attentions_0_transformer_blocks_0_attn1_to_q.lora_down.weight": torch.zeros(4, 8),
+            "lora_unet_down_blocks_0_attentions_0_transformer_blocks_0_attn1_to_q.lora_up.weight": torch.zeros(8, 4)}
+    assert list(parse_lora_state_dict(good, unet_modules=mods)["unet"]) == mods
+    sgm = {"lora_unet_input_blocks_1_1_transformer_blocks_0_attn1_to_q.lora_down.weight": torch.zeros(4, 8),
+           "lora_unet_input_blocks_1_1_transformer_blocks_0_attn1_to_q.lora_up.weight": torch.zeros(8, 4)}
+    with pytest.raises(ValueError, match="does not have"):
+        parse_lora_state_dict(sgm, unet_modules=mods)
+
+
+def test_text_encoder_lora_kohya_names_and_exact_restore():
+    """kohya text-encoder keys resolve through the flattened module names; load / set / delete cycles re-merge from an fp32
+    pristine copy, so the encoder's weights come back bit for bit."""
+    from stablediffusion_b200.models.stable_diffusion import SDModelWrapper
+
+    class Enc(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.text_model = torch.nn.Module()
+            self.text_model.q_proj = torch.nn.Linear(8, 8, bias=False).to(torch.bfloat16)
+
+    enc = Enc()
+    w0 = enc.text_model.q_proj.weight.data.clone()
+    w = SDModelWrapper.__new__(SDModelWrapper)
+    layers = {"lora_te_text_model_q_proj": dict(down=torch.randn(2, 8), up=torch.randn(8, 2), alpha=2.0)}
+    w._merge_text_encoder_lora(enc, layers, "a")
+    for wt in (0.7, 0.3, 1.0, 0.0):
+        w._apply_text_encoder_weights(enc, ["a"], [wt])
+    assert torch.equal(enc.text_model.q_proj.weight.data, w0)
+    w._apply_text_encoder_weights(enc, ["a"], [1.0])
+    assert not torch.equal(enc.text_model.q_proj.weight.data, w0)
+    with pytest.raises(ValueError, match="do not exist"):
+        w._merge_text_encoder_lora(enc, {"lora_te_text_model_nope": layers["lora_te_text_model_q_proj"]}, "b")
+
+
+def test_cross_attention_scale_is_not_silently_ignored():
+    from stablediffusion_b200.pipelines.sd_unified_pipeline import StableDiffusionUnifiedPipeline
+
+    pipe = StableDiffusionUnifiedPipeline(do_cfg=True, device="cuda")
+    with pytest.raises(ValueError, match="set_adapters"):
+        pipe(object(), prompt="x", cross_attention_kwargs={"scale": 0.5})
+
+
+def test_unet_pack_version_is_monotonic():
+    from stablediffusion_b200.unet import B200UNet
+
+    u = B200UNet(unet_config(), None, device="cpu")
+    assert u.pack_version == 0
