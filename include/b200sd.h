@@ -67,7 +67,8 @@ typedef enum b200sd_op_kind {
   B200SD_OP_STEP_ADVANCE = 13, /* ++(*step_counter)                                                       */
   B200SD_OP_IMAGE_U8 = 14,     /* NCHW image in [-1,1] -> uint8 HWC (runpod-worker/handler_logic.py:21-29) */
   B200SD_OP_EMBED = 15,        /* token + position embedding lookup of the CLIP text encoders             */
-  B200SD_OP_GAUSS_SAMPLE = 16  /* VAE posterior sample: mean + exp(0.5*clamp(logvar)) * noise (pipeline :1027)  */
+  B200SD_OP_GAUSS_SAMPLE = 16, /* VAE posterior sample: mean + exp(0.5*clamp(logvar)) * noise (pipeline :1027)  */
+  B200SD_OP_PAIR_EXCHANGE = 17 /* cond/uncond GPU-pair split: this rank's eps half -> the peer's window, in-graph    */
 } b200sd_op_kind;
 
 /* element types of host-visible tensors (latents, images) */
@@ -319,8 +320,27 @@ typedef struct b200sd_gauss_sample {
   int32_t B, C, hw, pad_;
 } b200sd_gauss_sample;
 
+/* The per-step exchange of the cond/uncond GPU-pair split (BASELINE config 5), inside the captured step graph: copy this
+ * rank's eps half into the same slot of the PEER's window (peer-mapped memory, b200sd_peer_open), release the peer's
+ * flag, then wait for the peer's half to land in the local window.  `sync_*` are int32[2] {flag, ack} inside the
+ * windows, `state` is a LOCAL int32[4] {seq, err, arrival counter, -} (zero-initialised; err != 0 after a spin timed out). */
+typedef struct b200sd_pair_exchange {
+  const void* src;      /* local window: this rank's eps half (16-byte aligned)                                  */
+  void* dst_remote;     /* the same slot of the peer's window                                                    */
+  int64_t bytes;        /* multiple of 16                                                                        */
+  const int32_t* sync_local;
+  int32_t* sync_remote;
+  int32_t* state;
+  int32_t timeout_ms;   /* 0 = 5000                                                                              */
+  int32_t pad_;
+} b200sd_pair_exchange;
+
 typedef struct b200sd_step_advance {
   int32_t* step_counter;
+  /* pair split only (else NULL): after the step, acknowledge to the peer that its eps half has been consumed
+   * (sync_remote[1] = seq) and advance the local sequence number (state[0] = seq) */
+  int32_t* ack_remote;  /* &sync_remote[1] of the peer's window */
+  int32_t* state;
 } b200sd_step_advance;
 
 typedef struct b200sd_op {
@@ -343,6 +363,7 @@ typedef struct b200sd_op {
     b200sd_image_u8 image_u8;
     b200sd_embed embed;
     b200sd_gauss_sample gauss_sample;
+    b200sd_pair_exchange pair_exchange;
   } u;
 } b200sd_op;
 
@@ -362,6 +383,15 @@ B200SD_API int b200sd_device_check(int device);          /* 0 iff `device` exist
  * data-parallel shard == full-batch guarantee of SURVEY section 4).  Ops planned before a change keep their plan. */
 B200SD_API int b200sd_set_batch_invariant(int on);       /* returns the previous setting                              */
 B200SD_API int b200sd_get_batch_invariant(void);
+
+/* Peer windows: device buffers another PROCESS on the same node can map and store into over NVLink (cudaIpc* under the
+ * hood; one process per GPU).  `peer_alloc` returns a zero-filled buffer and its 64-byte handle; the handle travels to the
+ * peer by any host channel (torch.distributed here), which maps it with `peer_open`. */
+#define B200SD_IPC_HANDLE_BYTES 64
+B200SD_API int b200sd_peer_alloc(int device, size_t bytes, void** ptr, unsigned char* handle);
+B200SD_API int b200sd_peer_open(int device, const unsigned char* handle, void** remote_ptr);
+B200SD_API int b200sd_peer_close(void* remote_ptr);
+B200SD_API int b200sd_peer_free(void* ptr);
 
 /* workspace sizing helpers (pure host arithmetic; callable without a GPU) */
 B200SD_API int b200sd_groupnorm_chunks(int32_t NB, int32_t HW, int32_t C);

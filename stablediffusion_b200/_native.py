@@ -18,16 +18,17 @@ BUILD_SCRIPT = os.path.join(_HERE, "csrc", "build.sh")
 MAX_SEG = 3
 MAX_TAPS = 9
 STEP_ROW = 16
+IPC_HANDLE_BYTES = 64
 
 # enum b200sd_op_kind
 OP_GEMM, OP_GROUPNORM, OP_LAYERNORM, OP_ATTENTION, OP_TIMESTEP_EMBED, OP_PREP_LATENTS = 1, 2, 3, 4, 5, 6
 OP_UPSAMPLE2X, OP_PHASE_SPLIT, OP_SOFTMAX_ROWS, OP_CFG_STEP, OP_AXPBY, OP_IMAGE_OUT, OP_STEP_ADVANCE = 7, 8, 9, 10, 11, 12, 13
-OP_IMAGE_U8, OP_EMBED, OP_GAUSS_SAMPLE = 14, 15, 16
+OP_IMAGE_U8, OP_EMBED, OP_GAUSS_SAMPLE, OP_PAIR_EXCHANGE = 14, 15, 16, 17
 ABI_VERSION = 3  # include/b200sd.h B200SD_ABI_VERSION
 OP_NAMES = {
     1: "gemm", 2: "groupnorm", 3: "layernorm", 4: "attention", 5: "timestep_embed", 6: "prep_latents",
     7: "upsample2x", 8: "phase_split", 9: "softmax_rows", 10: "cfg_step", 11: "axpby", 12: "image_out",
-    13: "step_advance", 14: "image_u8", 15: "embed", 16: "gauss_sample",
+    13: "step_advance", 14: "image_u8", 15: "embed", 16: "gauss_sample", 17: "pair_exchange",
 }
 # enum b200sd_dtype
 BF16, F32, F16 = 0, 1, 2
@@ -148,7 +149,12 @@ class ImageOut(C.Structure):
 
 
 class StepAdvance(C.Structure):
-    _fields_ = [("step_counter", C.c_void_p)]
+    _fields_ = [("step_counter", C.c_void_p), ("ack_remote", C.c_void_p), ("state", C.c_void_p)]
+
+
+class PairExchange(C.Structure):
+    _fields_ = [("src", C.c_void_p), ("dst_remote", C.c_void_p), ("bytes", C.c_int64), ("sync_local", C.c_void_p),
+                ("sync_remote", C.c_void_p), ("state", C.c_void_p), ("timeout_ms", C.c_int32), ("pad_", C.c_int32)]
 
 
 class ImageU8(C.Structure):
@@ -172,7 +178,7 @@ class _OpUnion(C.Union):
         ("timestep_embed", TimestepEmbed), ("prep_latents", PrepLatents), ("upsample2x", Upsample2x),
         ("phase_split", PhaseSplit), ("softmax_rows", SoftmaxRows), ("cfg_step", CfgStep), ("axpby", Axpby),
         ("image_out", ImageOut), ("step_advance", StepAdvance), ("image_u8", ImageU8), ("embed", Embed),
-        ("gauss_sample", GaussSample),
+        ("gauss_sample", GaussSample), ("pair_exchange", PairExchange),
     ]
 
 
@@ -184,13 +190,13 @@ STRUCT_OF_KIND = {
     OP_GEMM: Gemm, OP_GROUPNORM: GroupNorm, OP_LAYERNORM: LayerNorm, OP_ATTENTION: Attention,
     OP_TIMESTEP_EMBED: TimestepEmbed, OP_PREP_LATENTS: PrepLatents, OP_UPSAMPLE2X: Upsample2x,
     OP_PHASE_SPLIT: PhaseSplit, OP_SOFTMAX_ROWS: SoftmaxRows, OP_CFG_STEP: CfgStep, OP_AXPBY: Axpby,
-    OP_IMAGE_OUT: ImageOut, OP_STEP_ADVANCE: StepAdvance, OP_IMAGE_U8: ImageU8, OP_EMBED: Embed, OP_GAUSS_SAMPLE: GaussSample, 100: GemmSeg,
+    OP_IMAGE_OUT: ImageOut, OP_STEP_ADVANCE: StepAdvance, OP_IMAGE_U8: ImageU8, OP_EMBED: Embed, OP_GAUSS_SAMPLE: GaussSample, OP_PAIR_EXCHANGE: PairExchange, 100: GemmSeg,
 }
 FIELD_OF_KIND = {
     OP_GEMM: "gemm", OP_GROUPNORM: "groupnorm", OP_LAYERNORM: "layernorm", OP_ATTENTION: "attention",
     OP_TIMESTEP_EMBED: "timestep_embed", OP_PREP_LATENTS: "prep_latents", OP_UPSAMPLE2X: "upsample2x",
     OP_PHASE_SPLIT: "phase_split", OP_SOFTMAX_ROWS: "softmax_rows", OP_CFG_STEP: "cfg_step", OP_AXPBY: "axpby",
-    OP_IMAGE_OUT: "image_out", OP_STEP_ADVANCE: "step_advance", OP_IMAGE_U8: "image_u8", OP_EMBED: "embed", OP_GAUSS_SAMPLE: "gauss_sample",
+    OP_IMAGE_OUT: "image_out", OP_STEP_ADVANCE: "step_advance", OP_IMAGE_U8: "image_u8", OP_EMBED: "embed", OP_GAUSS_SAMPLE: "gauss_sample", OP_PAIR_EXCHANGE: "pair_exchange",
 }
 
 ENTRY_POINTS = {
@@ -201,6 +207,10 @@ ENTRY_POINTS = {
     "b200sd_device_check": (C.c_int, [C.c_int]),
     "b200sd_set_batch_invariant": (C.c_int, [C.c_int]),
     "b200sd_get_batch_invariant": (C.c_int, []),
+    "b200sd_peer_alloc": (C.c_int, [C.c_int, C.c_size_t, C.POINTER(C.c_void_p), C.c_char_p]),
+    "b200sd_peer_open": (C.c_int, [C.c_int, C.c_char_p, C.POINTER(C.c_void_p)]),
+    "b200sd_peer_close": (C.c_int, [C.c_void_p]),
+    "b200sd_peer_free": (C.c_int, [C.c_void_p]),
     "b200sd_groupnorm_chunks": (C.c_int, [C.c_int32, C.c_int32, C.c_int32]),
     "b200sd_gemm_workspace_bytes": (C.c_int64, [C.POINTER(Gemm)]),
     "b200sd_program_create": (C.c_int, [C.POINTER(C.c_void_p), C.c_int]),

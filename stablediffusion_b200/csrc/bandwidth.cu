@@ -887,14 +887,19 @@ int launch_embed(const void* plan, cudaStream_t s) {
   return 0;
 }
 
-__global__ void step_advance_kernel(int* counter) {
+struct SAParams { int* counter; int* ack_remote; int* state; };
+__global__ void step_advance_kernel(const SAParams p) {
   pdl_launch_dependents();
   pdl_wait();
-  *counter += 1;
+  *p.counter += 1;
+  if (p.ack_remote) {  // pair split: the peer's eps half of this step has been consumed by CFG_STEP (it ran before us)
+    const int seq = p.state[0] + 1;
+    asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(p.ack_remote), "r"(seq) : "memory");
+    p.state[0] = seq;
+  }
 }
-struct SAParams { int* counter; };
 int launch_step_advance(const void* plan, cudaStream_t s) {
-  B200SD_CUDA(launch_kernel(step_advance_kernel, dim3(1), dim3(1), 0, s, 1, static_cast<const SAParams*>(plan)->counter));
+  B200SD_CUDA(launch_kernel(step_advance_kernel, dim3(1), dim3(1), 0, s, 1, *static_cast<const SAParams*>(plan)));
   B200SD_CUDA(cudaGetLastError());
   return 0;
 }
@@ -1087,7 +1092,8 @@ int plan_gauss_sample(const b200sd_gauss_sample& g, PlannedOp* out) {
 
 int plan_step_advance(const b200sd_step_advance& g, PlannedOp* out) {
   B200SD_CHECK_ARG(g.step_counter, "step_advance: NULL counter");
-  SAParams p{g.step_counter};
+  B200SD_CHECK_ARG((g.ack_remote == nullptr) == (g.state == nullptr), "step_advance: ack_remote and state go together");
+  SAParams p{g.step_counter, g.ack_remote, g.state};
   return finish_plan(out, B200SD_OP_STEP_ADVANCE, p, launch_step_advance);
 }
 

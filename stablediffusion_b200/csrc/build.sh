@@ -10,7 +10,7 @@ FLAGS=(${B200SD_EXTRA_NVCC_FLAGS:-} -gencode arch=compute_100a,code=sm_100a -O3 
        -Xcompiler -fPIC -Xcompiler -fvisibility=hidden -Xptxas -v --expt-relaxed-constexpr)
 OBJS=()
 pids=()
-for f in gemm attention bandwidth program; do
+for f in gemm attention bandwidth peer program; do
   ( "$NVCC" "${FLAGS[@]}" -c "$HERE/$f.cu" -o "$OUT/$f.o" > "$OUT/$f.ptxas.log" 2>&1 || { cat "$OUT/$f.ptxas.log"; exit 1; } ) &
   pids+=($!)
   OBJS+=("$OUT/$f.o")

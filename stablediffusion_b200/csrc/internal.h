@@ -63,6 +63,7 @@ int plan_step_advance(const b200sd_step_advance& g, PlannedOp* out);
 int plan_image_u8(const b200sd_image_u8& g, PlannedOp* out);
 int plan_embed(const b200sd_embed& g, PlannedOp* out);
 int plan_gauss_sample(const b200sd_gauss_sample& g, PlannedOp* out);
+int plan_pair_exchange(const b200sd_pair_exchange& g, PlannedOp* out);
 
 // host-only helpers used by sizing entry points
 struct GemmTiling {

@@ -156,6 +156,7 @@ size_t b200sd_sizeof_struct(int32_t kind) {
     case B200SD_OP_IMAGE_U8: return sizeof(b200sd_image_u8);
     case B200SD_OP_EMBED: return sizeof(b200sd_embed);
     case B200SD_OP_GAUSS_SAMPLE: return sizeof(b200sd_gauss_sample);
+    case B200SD_OP_PAIR_EXCHANGE: return sizeof(b200sd_pair_exchange);
     case 100: return sizeof(b200sd_gemm_seg);
   }
   return 0;
@@ -224,6 +225,7 @@ int b200sd_program_add(b200sd_program* p, const b200sd_op* op) {
     case B200SD_OP_IMAGE_U8: rc = plan_image_u8(op->u.image_u8, &po); break;
     case B200SD_OP_EMBED: rc = plan_embed(op->u.embed, &po); break;
     case B200SD_OP_GAUSS_SAMPLE: rc = plan_gauss_sample(op->u.gauss_sample, &po); break;
+    case B200SD_OP_PAIR_EXCHANGE: rc = plan_pair_exchange(op->u.pair_exchange, &po); break;
     default: return fail(B200SD_ERR_INVALID, "unknown op kind %d", op->kind);
   }
   if (rc) return rc;

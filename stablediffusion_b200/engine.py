@@ -12,13 +12,19 @@ scheduler.step) is here ONE captured op program:
 Latents stay on the device in fp32 for the whole trajectory (the reference rounds them to fp16 every step —
 SURVEY App. B.1; keeping an fp32 master is strictly more accurate and is the documented deviation).
 
-Optional cond/uncond GPU-pair split: each rank of a pair runs the UNet on ONE half of the CFG
-batch, the eps halves are exchanged with one NCCL all-gather per step, and both ranks then run the same
-CFG_STEP so latents stay replicated.
+Optional cond/uncond GPU-pair split (BASELINE config 5): each rank of a pair runs the UNet on ONE half
+of the CFG batch, the eps halves are exchanged once per step, and both ranks then run the same CFG_STEP so latents
+stay replicated.  Two exchanges:
+  * "peer" (default when the two GPUs can map each other's memory): the exchange is INSIDE the step graph — conv_out
+    stores this rank's half into its slot of a peer window, OP_PAIR_EXCHANGE copies the slot into the peer's window over
+    NVLink and waits for the peer's half (csrc/peer.cu); still one graph launch per step, no NCCL kernel, no host step
+  * "nccl": UNet graph | one all_gather_into_tensor | CFG_STEP graph — the tested fallback
 """
 from __future__ import annotations
 
 from typing import Dict, Optional
+
+import ctypes as C
 
 import torch
 
@@ -29,10 +35,71 @@ from .unet import B200UNet, UNetLowering, cfg_is_sdxl
 MAX_STEPS = 1000
 
 
+class _RawCuda:
+    """Device memory owned by the library (a peer window) seen as a torch tensor (__cuda_array_interface__)."""
+
+    def __init__(self, ptr: int, nbytes: int):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 3, "strides": None}
+
+
+class PeerWindow:
+    """A zero-filled device buffer the pair's other process maps and stores into (include/b200sd.h peer windows).
+    Layout: [payload ... | 256 B: int32 sync words {flag, ack} written by the peer]."""
+    SYNC_BYTES = 256
+
+    def __init__(self, device: torch.device, payload_bytes: int, group):
+        import torch.distributed as dist
+
+        self.device, self.group = device, group
+        self.payload_bytes = (payload_bytes + 255) // 256 * 256
+        nbytes = self.payload_bytes + self.SYNC_BYTES
+        ptr, handle = C.c_void_p(), C.create_string_buffer(N.IPC_HANDLE_BYTES)
+        N.check(N.lib().b200sd_peer_alloc(device.index, nbytes, C.byref(ptr), handle))
+        self.ptr = ptr.value
+        self.remote = None
+        mine = torch.frombuffer(bytearray(handle.raw), dtype=torch.uint8).to(device)
+        both = [torch.empty_like(mine) for _ in range(2)]
+        dist.all_gather(both, mine, group=group)       # (also a barrier: both windows are zeroed before anyone maps them)
+        peer = both[1 - dist.get_rank(group)].cpu().numpy().tobytes()
+        rptr = C.c_void_p()
+        rc = N.lib().b200sd_peer_open(device.index, peer, C.byref(rptr))
+        ok = torch.tensor([1 if rc == 0 else 0], device=device)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)   # both ranks take the same path
+        if rc == 0:
+            self.remote = rptr.value
+        if int(ok.item()) == 0:
+            err = N.last_error() if rc != 0 else "the peer could not map this rank's window"
+            self.close()
+            raise RuntimeError(f"peer window unavailable: {err}")
+        self.bytes = torch.as_tensor(_RawCuda(self.ptr, nbytes), device=device)
+
+    @property
+    def sync_local(self) -> int:
+        return self.ptr + self.payload_bytes
+
+    @property
+    def sync_remote(self) -> int:
+        return self.remote + self.payload_bytes
+
+    def close(self):
+        if getattr(self, "remote", None):
+            N.lib().b200sd_peer_close(C.c_void_p(self.remote))
+            self.remote = None
+        if getattr(self, "ptr", None):
+            N.lib().b200sd_peer_free(C.c_void_p(self.ptr))
+            self.ptr = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
 class DenoiseEngine:
     def __init__(self, unet: B200UNet, B: int, h: int, w: int, do_cfg: bool, ctx_dim: int, uses_history: bool,
                  pair_group=None, pair_rank: int = 0, use_graph: bool = True, eps_history: bool = False,
-                 noise_steps: int = 0, blend: bool = False):
+                 noise_steps: int = 0, blend: bool = False, pair_exchange: str = "auto"):
         if unet.packed is None:
             raise RuntimeError("UNet has no weights on a CUDA device")
         self.unet, self.B, self.h, self.w, self.do_cfg = unet, B, h, w, do_cfg
@@ -79,13 +146,41 @@ class DenoiseEngine:
             self.time_ids = b.empty([NB, 6], torch.float32)
             kw = dict(text_embeds=self.text_embeds, time_ids=self.time_ids)
         low = UNetLowering(b, pk, NB, h, w, unet.ctx_len)
-        self.eps_full = b.empty([rep_total * B, h * w, cfg["out_channels"]])
-        eps_local = low.emit(unet_in, self.ctx, step_table=self.table, step_counter=self.counter, **kw)
+        self.window = None
+        self.exchange_kind = None
+        eps_shape = [rep_total * B, h * w, cfg["out_channels"]]
+        if self.split:
+            if pair_exchange not in ("auto", "peer", "nccl"):
+                raise ValueError("pair_exchange must be 'auto', 'peer' or 'nccl'")
+            self.exchange_kind = "nccl"
+            if pair_exchange != "nccl":
+                try:
+                    self.window = PeerWindow(self.device, 2 * B * h * w * cfg["out_channels"] * 2, pair_group)
+                    self.exchange_kind = "peer"
+                except RuntimeError:
+                    if pair_exchange == "peer":
+                        raise
+        if self.window is not None:
+            n_el = eps_shape[0] * eps_shape[1] * eps_shape[2]
+            self.eps_full = self.window.bytes[:2 * n_el].view(torch.bfloat16).view(eps_shape)
+            b.prog.keep(self.window)
+            self.xstate = b.zeros([4], torch.int32)      # {seq, err, arrival counter, -}
+            mine = self.eps_full[pair_rank * B:(pair_rank + 1) * B]
+            eps_local = low.emit(unet_in, self.ctx, step_table=self.table, step_counter=self.counter, eps_out=mine, **kw)
+            off = mine.data_ptr() - self.window.ptr
+            b.pair_exchange(mine, self.window.remote + off, self.window.sync_local, self.window.sync_remote, self.xstate)
+        else:
+            self.eps_full = b.empty(eps_shape)
+            eps_local = low.emit(unet_in, self.ctx, step_table=self.table, step_counter=self.counter, **kw)
         self.eps_local = eps_local
         self.unet_ops = b.prog.num_ops
         if not self.split:
             self.eps_for_step = eps_local
             self._emit_tail(b, eps_local)
+            self.tail = None
+        elif self.window is not None:
+            # ONE graph per step: UNet -> PAIR_EXCHANGE (peer stores + flag) -> CFG_STEP -> STEP_ADVANCE (+ ack)
+            self._emit_tail(b, self.eps_full, ack_remote=self.window.sync_remote + 4, state=self.xstate)
             self.tail = None
         else:
             # UNet graph | NCCL all-gather of eps halves | CFG_STEP graph
@@ -96,11 +191,11 @@ class DenoiseEngine:
         self._captured = False
         self._stream = torch.cuda.Stream(self.device)
 
-    def _emit_tail(self, b: L.Builder, eps):
+    def _emit_tail(self, b: L.Builder, eps, ack_remote: int = 0, state=None):
         b.cfg_step(eps, self.latents, self.latents, self.table, self.counter, 1.0, self.do_cfg, MAX_STEPS,
                    x0_prev=self.hist, next_in=self.unet_in_full, rep=2 if self.do_cfg else 1, gs_from_table=True,
                    noise=self.noise, eps_hist=self.eps_hist, x_saved=self.x_saved, blend=self.blend)
-        b.step_advance(self.counter)
+        b.step_advance(self.counter, ack_remote=ack_remote, state=state)
 
     @property
     def launches_per_step(self) -> int:
@@ -164,6 +259,10 @@ class DenoiseEngine:
             for _ in range(n):
                 self.step_once(s)
         torch.cuda.current_stream(self.device).wait_stream(s)
+        if self.window is not None:  # a spin in the exchange kernel timed out (peer gone / fell out of step): fail loudly
+            err = int(self.xstate[1].item())
+            if err:
+                raise RuntimeError(f"cond/uncond pair exchange timed out (code {err}: 1 = ack, 2 = peer's eps half never arrived)")
         return self.latents
 
     def step_once(self, s):

@@ -406,7 +406,20 @@ class Builder:
         self.prog.add(N.OP_GAUSS_SAMPLE, p, self.tag, (moments, noise, out))
         return out
 
-    def step_advance(self, step_counter):
+    def step_advance(self, step_counter, ack_remote: int = 0, state=None):
+        """++step counter; with the pair split also the acknowledgement to the peer (`ack_remote`: raw peer address)."""
         p = N.StepAdvance()
         p.step_counter = step_counter.data_ptr()
-        self.prog.add(N.OP_STEP_ADVANCE, p, self.tag, (step_counter,))
+        if ack_remote:
+            p.ack_remote, p.state = int(ack_remote), state.data_ptr()
+        self.prog.add(N.OP_STEP_ADVANCE, p, self.tag, (step_counter, state))
+
+    def pair_exchange(self, src, dst_remote: int, sync_local: int, sync_remote: int, state, timeout_ms: int = 5000):
+        """This rank's eps half (`src`, a tensor inside the local window) -> the same slot of the peer's window
+        (`dst_remote`, raw peer address), flag / ack handshake through the windows' sync words (csrc/peer.cu)."""
+        if not src.is_contiguous():
+            raise ValueError("pair_exchange: src must be contiguous")
+        p = N.PairExchange()
+        p.src, p.dst_remote, p.bytes = src.data_ptr(), int(dst_remote), src.numel() * src.element_size()
+        p.sync_local, p.sync_remote, p.state, p.timeout_ms = int(sync_local), int(sync_remote), state.data_ptr(), int(timeout_ms)
+        self.prog.add(N.OP_PAIR_EXCHANGE, p, self.tag, (src, state))

@@ -42,12 +42,14 @@ def denoising_value_valid(dnv):
 
 class StableDiffusionUnifiedPipeline:
     def __init__(self, do_cfg: bool = True, device: Optional[str] = None, output_type: Optional[str] = None,
-                 pair_group=None, pair_rank: int = 0, use_graph: bool = True, verbose: bool = False):
+                 pair_group=None, pair_rank: int = 0, use_graph: bool = True, verbose: bool = False,
+                 pair_exchange: str = "auto"):
         self.do_classifier_free_guidance = bool(do_cfg)
         self.device = torch.device(device) if device is not None else torch.device("cpu")
         self.output_type = output_type if output_type is not None else "pt"
         self.model = None
         self.pair_group, self.pair_rank = pair_group, pair_rank   # optional cond/uncond GPU-pair split
+        self.pair_exchange = pair_exchange                        # "auto" | "peer" (in-graph NVLink stores) | "nccl"
         self.use_graph = use_graph
         self.verbose = verbose
         self._engines: Dict[tuple, DenoiseEngine] = {}
@@ -71,7 +73,8 @@ class StableDiffusionUnifiedPipeline:
         if eng is None:
             eng = DenoiseEngine(m.base, B, h, w, self.do_classifier_free_guidance, ctx_dim, sch._uses_history,
                                 pair_group=self.pair_group, pair_rank=self.pair_rank, use_graph=self.use_graph,
-                                eps_history=sch._uses_eps_history, noise_steps=noise_steps, blend=blend)
+                                eps_history=sch._uses_eps_history, noise_steps=noise_steps, blend=blend,
+                                pair_exchange=self.pair_exchange)
             self._engines = {k: v for k, v in self._engines.items() if k[:2] == key[:2]}  # drop engines of stale weights
             self._engines[key] = eng
         return eng

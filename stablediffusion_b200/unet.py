@@ -20,6 +20,7 @@ from typing import Dict, List, Optional, Tuple
 
 import torch
 
+from . import _native as N
 from . import lowering as L
 from .config import Config, unet_config
 from .packing import conv_weight_to_gemm, geglu_block_n, geglu_interleave
@@ -316,8 +317,10 @@ class UNetLowering:
         out = b.linear(t, T[f"{p}.proj_out.w"], bias=T[f"{p}.proj_out.b"], residual=x.view(tok, C), rows_per_sample=rps)
         return out.view(NB, H, W, C)
 
-    def emit(self, unet_in, ctx, t_explicit=None, step_table=None, step_counter=None, text_embeds=None, time_ids=None):
-        """unet_in: bf16 [NB, h*w, cin_pad] (already scaled); ctx: bf16 [NB, ctx_len, D].  Returns eps bf16 [NB, h*w, C_out]."""
+    def emit(self, unet_in, ctx, t_explicit=None, step_table=None, step_counter=None, text_embeds=None, time_ids=None,
+             eps_out=None):
+        """unet_in: bf16 [NB, h*w, cin_pad] (already scaled); ctx: bf16 [NB, ctx_len, D].  Returns eps bf16 [NB, h*w, C_out]
+        (written into `eps_out` when given: the pair split lets conv_out store straight into its window slot)."""
         b, T, cfg, s = self.b, self.T, self.cfg, self.s
         NB, h, w = self.NB, self.h, self.w
         eps_r = cfg["norm_eps"]
@@ -374,7 +377,8 @@ class UNetLowering:
                 x = b.conv(b.upsample2x(x), T[f"{p}.w"], bias=T[f"{p}.b"])
         NBx, H, W, C = x.shape
         hn = b.groupnorm(x.view(NB, H * W, C), T["conv_norm_out.g"], T["conv_norm_out.b"], eps_r, True)
-        eps = b.conv(hn.view(NB, H, W, C), T["conv_out.w"], bias=T["conv_out.b"])
+        eps = b.conv(hn.view(NB, H, W, C), T["conv_out.w"], bias=T["conv_out.b"],
+                     out=None if eps_out is None else eps_out.view(NB, H, W, eps_out.shape[-1]))
         return eps.view(NB, H * W, eps.shape[-1])
 
 
@@ -464,7 +468,7 @@ class B200UNet:
 
     # ---- standalone forward (the reference's un-fused call) ------------------------------------------
     def _program(self, NB, h, w, in_dtype, D):
-        key = (NB, h, w, in_dtype, D)
+        key = (NB, h, w, in_dtype, D, N.batch_invariant())  # (plans made in the batch-invariant mode differ)
         if key in self._programs:
             return self._programs[key]
         b = L.Builder(self.device)

@@ -13,6 +13,7 @@ from typing import Dict, Optional, Tuple
 
 import torch
 
+from . import _native as N
 from . import lowering as L
 from .config import Config, vae_config
 from .packing import conv_weight_to_gemm
@@ -337,7 +338,7 @@ class B200VAE:
         return self
 
     def _decode_program(self, NB, h, w, in_dtype, scale=1.0):
-        key = ("dec", NB, h, w, in_dtype, float(scale))
+        key = ("dec", NB, h, w, in_dtype, float(scale), N.batch_invariant())
         if key in self._programs:
             return self._programs[key]
         b = L.Builder(self.device)
@@ -365,7 +366,7 @@ class B200VAE:
         return (st["out"].clone(),)
 
     def _encode_program(self, NB, H, W, in_dtype):
-        key = ("enc", NB, H, W, in_dtype)
+        key = ("enc", NB, H, W, in_dtype, N.batch_invariant())
         if key in self._programs:
             return self._programs[key]
         if not self.packed.has_encoder:

@@ -43,7 +43,7 @@ def _make_unet(dev, model_type="sd15", seed=0, **over):
     return cfg, ours, oracle.eval()
 
 
-def _unet_case(dev, cfg, ours, oracle, B, h, w, t, oracle_on_gpu):
+def _unet_case(dev, cfg, ours, oracle, B, h, w, t, oracle_on_gpu, max_ratio_vs_eager=None):
     g = torch.Generator().manual_seed(11)
     x = torch.randn(B, 4, h, w, generator=g)
     ctx = torch.randn(B, 77, cfg["cross_attention_dim"], generator=g).to(torch.bfloat16).float()
@@ -78,6 +78,8 @@ def _unet_case(dev, cfg, ours, oracle, B, h, w, t, oracle_on_gpu):
     print("UNET PARITY", tuple(x.shape), "t=", t, msg)
     assert rl2 <= 2e-2, msg
     assert mabs <= 0.1, msg
+    if max_ratio_vs_eager is not None:  # no worse than 1.5x the error of torch-eager bf16 on the same GPU
+        assert eager is not None and rl2 <= max_ratio_vs_eager * _rel_l2(eager, ref), msg
     return rl2
 
 
@@ -190,7 +192,7 @@ def test_fused_loop_vs_oracle(cuda_device, sched_name, steps):
     ref = OP.denoise(oracle.cpu(), osched, x0, torch.cat([ne, pe]).float(), osched.timesteps, 7.5, step_noise=step_noise)
     rl2 = _rel_l2(out, ref)
     print(f"LOOP PARITY {sched_name} x{steps}: rel-L2 {rl2:.4g}")
-    assert torch.isfinite(out).all() and rl2 <= 5e-2
+    assert torch.isfinite(out).all() and rl2 <= 3.3e-2   # measured 1.8-2.2e-2 (round 1): 1.5x head-room
 
 
 @pytest.mark.parametrize("sched_name", ["euler", "PNDM", "euler_a", "DPM++ 2M SDE Karras", "uni_pc"])
@@ -332,7 +334,7 @@ def test_inpaint_loop_vs_oracle(cuda_device, sched_name, strength):
                      inpaint=(m, image_latents, noise))
     rl2 = _rel_l2(out, ref)
     print(f"INPAINT PARITY {sched_name} strength {strength}: rel-L2 {rl2:.4g}")
-    assert torch.isfinite(out).all() and rl2 <= 5e-2
+    assert torch.isfinite(out).all() and rl2 <= 3.3e-2   # measured <= 2.2e-2 (round 1): 1.5x head-room
     # outside the mask the result IS the original image latents (last step: no re-noising)
     keep = (m == 0).expand_as(out)
     torch.testing.assert_close(out[keep], image_latents[keep], rtol=1e-6, atol=1e-6)
