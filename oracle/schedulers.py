@@ -185,7 +185,13 @@ class DPMSolverMultistepOracle(_Base):
             ts = np.array([self._sigma_to_t(s, log_sig) for s in sig]).round()
         else:
             sig = np.interp(ts, np.arange(0, len(sig)), sig)
-        sig = np.concatenate([sig, [0.0]]).astype(np.float32)
+        # final_sigmas_type: "zero" (class default, what every SD config gets) or "sigma_min" (only used to check this
+        # restatement against diffusers' own scheduler unit tests, which pin the older behaviour)
+        if self.config.get("final_sigmas_type", "zero") == "sigma_min":
+            sigma_last = float(((1 - self.alphas_cumprod[0]) / self.alphas_cumprod[0]) ** 0.5)
+        else:
+            sigma_last = 0.0
+        sig = np.concatenate([sig, [sigma_last]]).astype(np.float32)
         self.sigmas = torch.from_numpy(sig)
         self.timesteps = torch.from_numpy(ts).to(torch.int64)
         self.m = [None, None]
@@ -211,11 +217,18 @@ class DPMSolverMultistepOracle(_Base):
     def scale_model_input(self, x, t):
         return x
 
+    def _lower_final(self, i, n):
+        """diffusers: (step_index == len(timesteps) - 1) and (euler_at_final or (lower_order_final and len < 15) or
+        final_sigmas_type == "zero") — with the class defaults the last step is always first-order."""
+        c = self.config
+        return i == n - 1 and (c.get("euler_at_final", False) or (c.get("lower_order_final", True) and n < 15)
+                               or c.get("final_sigmas_type", "zero") == "zero")
+
     def step(self, eps, t, x):
         self._init_step_index(t)
         i = self.step_index
         n = len(self.timesteps)
-        lower_final = i == n - 1  # final_sigmas_type == "zero" (default) always forces first order on the last step
+        lower_final = self._lower_final(i, n)
         a_s, s_s = self._alpha_sigma(self.sigmas[i])
         x0 = (x - s_s * eps) / a_s
         self.m = [self.m[1], x0]
@@ -274,7 +287,7 @@ class DPMSolverSDEOracle(DPMSolverMultistepOracle):
         self._init_step_index(t)
         i = self.step_index
         n = len(self.timesteps)
-        lower_final = i == n - 1
+        lower_final = self._lower_final(i, n)
         a_s, s_s = self._alpha_sigma(self.sigmas[i])
         x0 = (x - s_s * eps) / a_s
         self.m = [self.m[1], x0]
@@ -454,7 +467,7 @@ class UniPCOracle(DPMSolverMultistepOracle):
         if use_corrector:
             x = self._uni_c(x0, self.last_sample, self.this_order)
         self.model_outputs = [self.model_outputs[1], x0]
-        this_order = min(2, len(self.timesteps) - i)                 # lower_order_final
+        this_order = min(2, len(self.timesteps) - i) if self.config.get("lower_order_final", True) else 2
         self.this_order = min(this_order, self.lower_order_nums + 1)  # warm-up
         self.last_sample = x
         out = self._uni_p(x, self.this_order)

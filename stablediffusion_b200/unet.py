@@ -317,10 +317,16 @@ class UNetLowering:
         out = b.linear(t, T[f"{p}.proj_out.w"], bias=T[f"{p}.proj_out.b"], residual=x.view(tok, C), rows_per_sample=rps)
         return out.view(NB, H, W, C)
 
+    def project_context(self, b, ctx):
+        """Every cross-attention K/V projection of the network as ONE GEMM over the prompt: [NB*ctx_len, sum 2C]."""
+        return b.linear(ctx.view(self.NB * self.ctx_len, ctx.shape[-1]), self.T["ctx_kv.w"], rows_per_sample=self.ctx_len)
+
     def emit(self, unet_in, ctx, t_explicit=None, step_table=None, step_counter=None, text_embeds=None, time_ids=None,
-             eps_out=None):
+             eps_out=None, ctx_kv=None):
         """unet_in: bf16 [NB, h*w, cin_pad] (already scaled); ctx: bf16 [NB, ctx_len, D].  Returns eps bf16 [NB, h*w, C_out]
-        (written into `eps_out` when given: the pair split lets conv_out store straight into its window slot)."""
+        (written into `eps_out` when given: the pair split lets conv_out store straight into its window slot).
+        `ctx_kv`: the cross-attention K/V projections of the prompt when the caller computed them already (they do not
+        depend on the timestep: the fused loop projects the prompt once per trajectory, not once per step)."""
         b, T, cfg, s = self.b, self.T, self.cfg, self.s
         NB, h, w = self.NB, self.h, self.w
         eps_r = cfg["norm_eps"]
@@ -345,8 +351,7 @@ class UNetLowering:
             silu_emb = b.linear(e1, T["time_embedding.linear_2.w"], bias=T["time_embedding.linear_2.b"], silu=True, rows_per_sample=1)
         self.temb_all = b.linear(silu_emb, T["temb_all.w"], bias=T["temb_all.b"], out_f32=True, rows_per_sample=1)
         # --- every cross-attention K/V projection of the network in one GEMM --------------------------
-        D = ctx.shape[-1]
-        self.ctx_kv = b.linear(ctx.view(NB * self.ctx_len, D), T["ctx_kv.w"], rows_per_sample=self.ctx_len)
+        self.ctx_kv = ctx_kv if ctx_kv is not None else self.project_context(b, ctx)
         # --- down path --------------------------------------------------------------------------------
         x = b.conv(unet_in.view(NB, h, w, self.pk.cin_pad), T["conv_in.w"], bias=T["conv_in.b"])
         skips = [x]

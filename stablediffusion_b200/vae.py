@@ -354,16 +354,32 @@ class B200VAE:
         self._programs[key] = st
         return st
 
+    # Decoder activations grow to 128 channels at full resolution (64 MiB per image at 512^2, 256 MiB at 1024^2, times the
+    # ~60 intermediates of the program): a batch is decoded in chunks of at most this many output pixels per program run
+    # (16 images at 512^2, 4 at 1024^2: ~60 GB of intermediates), so any batch size fits the 180 GB of a B200 and reuses ONE planned program.
+    MAX_PIXELS_PER_RUN = 4 * 1024 * 1024
+
     @torch.no_grad()
     def decode(self, z, return_dict=False, scale: float = 1.0, **unused):
         """`scale` multiplies z first (the pipeline passes 1/scaling_factor so the un-scale of reference :521 is fused)."""
         if self.packed is None:
             raise RuntimeError("B200VAE has no weights on a CUDA device")
         NB, _, h, w = z.shape
-        st = self._decode_program(NB, h, w, z.dtype, scale)
-        st["z"].copy_(z)
-        st["b"].prog.run(torch.cuda.current_stream(self.device).cuda_stream)
-        return (st["out"].clone(),)
+        chunk = max(1, min(NB, self.MAX_PIXELS_PER_RUN // (64 * h * w)))
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        if chunk >= NB:
+            st = self._decode_program(NB, h, w, z.dtype, scale)
+            st["z"].copy_(z)
+            st["b"].prog.run(stream)
+            return (st["out"].clone(),)
+        outs = []
+        for lo in range(0, NB, chunk):
+            n = min(chunk, NB - lo)
+            st = self._decode_program(n, h, w, z.dtype, scale)
+            st["z"].copy_(z[lo:lo + n])
+            st["b"].prog.run(stream)
+            outs.append(st["out"].clone())
+        return (torch.cat(outs, dim=0),)
 
     def _encode_program(self, NB, H, W, in_dtype):
         key = ("enc", NB, H, W, in_dtype, N.batch_invariant())
