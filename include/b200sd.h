@@ -331,7 +331,7 @@ typedef struct b200sd_pair_exchange {
   const int32_t* sync_local;
   int32_t* sync_remote;
   int32_t* state;
-  int32_t timeout_ms;   /* 0 = 5000                                                                              */
+  int32_t timeout_ms;   /* 0 = 20000                                                                             */
   int32_t pad_;
 } b200sd_pair_exchange;
 

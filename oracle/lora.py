@@ -18,7 +18,8 @@ def attach_unmerged(model: nn.Module, adapters: dict, weights: dict):
             scale = (ent["alpha"] / A.shape[0]) if ent.get("alpha") is not None else 1.0
 
             def hook(mod, inp, out, A=A, B=B, s=w * scale):
-                return out + s * (inp[0] @ A.t() @ B.t())
+                x = inp[0]
+                return out + s * (x @ A.to(x.device, x.dtype).t() @ B.to(x.device, x.dtype).t())
 
             handles.append(m.register_forward_hook(hook))
     return handles

@@ -92,7 +92,7 @@ int plan_pair_exchange(const b200sd_pair_exchange& g, PlannedOp* out) {
   PXPlan* pl = new (std::nothrow) PXPlan();
   if (!pl) return fail(B200SD_ERR_CUDA, "out of host memory");
   pl->p = PXParams{static_cast<const uint4*>(g.src), static_cast<uint4*>(g.dst_remote), g.bytes / 16, g.sync_local, g.sync_remote,
-                   g.state, static_cast<long long>(g.timeout_ms > 0 ? g.timeout_ms : 5000) * 1000000LL};
+                   g.state, static_cast<long long>(g.timeout_ms > 0 ? g.timeout_ms : 20000) * 1000000LL};
   // 32 KiB (B = 1, 512^2) .. 8 MiB (B = 64, 1024^2): a CTA moves 16 KiB per pass; a few CTAs saturate one NVLink direction
   pl->grid = static_cast<int>(std::max<long long>(1, std::min<long long>((g.bytes + 16383) / 16384, 32)));
   out->kind = B200SD_OP_PAIR_EXCHANGE;

@@ -414,7 +414,7 @@ class Builder:
             p.ack_remote, p.state = int(ack_remote), state.data_ptr()
         self.prog.add(N.OP_STEP_ADVANCE, p, self.tag, (step_counter, state))
 
-    def pair_exchange(self, src, dst_remote: int, sync_local: int, sync_remote: int, state, timeout_ms: int = 5000):
+    def pair_exchange(self, src, dst_remote: int, sync_local: int, sync_remote: int, state, timeout_ms: int = 20000):
         """This rank's eps half (`src`, a tensor inside the local window) -> the same slot of the peer's window
         (`dst_remote`, raw peer address), flag / ack handshake through the windows' sync words (csrc/peer.cu)."""
         if not src.is_contiguous():
