@@ -393,6 +393,18 @@ B200SD_API int b200sd_peer_open(int device, const unsigned char* handle, void** 
 B200SD_API int b200sd_peer_close(void* remote_ptr);
 B200SD_API int b200sd_peer_free(void* ptr);
 
+/* GroupNorm (+SiLU) without any allocation, for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  NO COUNTERPART IN THE REFERENCE.
+ * Same arithmetic and kernels as B200SD_OP_GROUPNORM (two-kernel form), launched directly on `cuda_stream`; the partial
+ * sums live in a file-scope `static __device__` array of B200SD_GN_STATIC_SCRATCH_BYTES inside the library (held by every
+ * GPU that loads it until the process exits), so `g->partials` must be NULL and `partials_bytes` is ignored.  The caller
+ * still passes inputs and outputs.  Shapes that need more scratch (NB * chunks * groups * 8 bytes, chunks =
+ * b200sd_groupnorm_chunks()) are rejected with B200SD_ERR_INVALID.  Calls no cudaMalloc / cudaFree / allocating routine.
+ * The array is shared by all calls and keeps the last call's contents (nothing needs to start at zero: every slot read is
+ * written first); calls that OVERLAP on the GPU race on it — keep them on one stream or order them with events. */
+#define B200SD_GN_STATIC_SCRATCH_BYTES (1 << 20)
+B200SD_API int b200sd_groupnorm_static_scratch(int device, const b200sd_groupnorm* g, void* cuda_stream);
+
 /* workspace sizing helpers (pure host arithmetic; callable without a GPU) */
 B200SD_API int b200sd_groupnorm_chunks(int32_t NB, int32_t HW, int32_t C);
 B200SD_API int64_t b200sd_gemm_workspace_bytes(const b200sd_gemm* g); /* bytes needed for the split-K it would choose */

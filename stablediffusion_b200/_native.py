@@ -19,6 +19,7 @@ MAX_SEG = 3
 MAX_TAPS = 9
 STEP_ROW = 16
 IPC_HANDLE_BYTES = 64
+GN_STATIC_SCRATCH_BYTES = 1 << 20  # include/b200sd.h B200SD_GN_STATIC_SCRATCH_BYTES
 
 # enum b200sd_op_kind
 OP_GEMM, OP_GROUPNORM, OP_LAYERNORM, OP_ATTENTION, OP_TIMESTEP_EMBED, OP_PREP_LATENTS = 1, 2, 3, 4, 5, 6
@@ -211,6 +212,7 @@ ENTRY_POINTS = {
     "b200sd_peer_open": (C.c_int, [C.c_int, C.c_char_p, C.POINTER(C.c_void_p)]),
     "b200sd_peer_close": (C.c_int, [C.c_void_p]),
     "b200sd_peer_free": (C.c_int, [C.c_void_p]),
+    "b200sd_groupnorm_static_scratch": (C.c_int, [C.c_int, C.POINTER(GroupNorm), C.c_void_p]),
     "b200sd_groupnorm_chunks": (C.c_int, [C.c_int32, C.c_int32, C.c_int32]),
     "b200sd_gemm_workspace_bytes": (C.c_int64, [C.POINTER(Gemm)]),
     "b200sd_program_create": (C.c_int, [C.POINTER(C.c_void_p), C.c_int]),

@@ -1098,3 +1098,94 @@ int plan_step_advance(const b200sd_step_advance& g, PlannedOp* out) {
 }
 
 }  // namespace b200sd
+
+// ======================================================================================================
+// b200sd_groupnorm_static_scratch — GroupNorm (+SiLU) for callers that cannot allocate device memory (code under CUDA
+// graph capture, tight serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// Same two kernels as the program op (gn_stats_kernel -> gn_apply_kernel), but the
+// per-(image, chunk, group) partial sums live in the file-scope device array below instead of a caller workspace, and the
+// call plans on the stack: no cudaMalloc / cudaFree / allocating library routine, no host heap either.
+//   * every GPU that loads the library holds B200SD_GN_STATIC_SCRATCH_BYTES (1 MiB) until the process exits;
+//   * shapes whose partials exceed that are rejected with B200SD_ERR_INVALID (the largest UNet / VAE shape of the path,
+//     64 images x 37 chunks x 32 groups, needs 0.6 MiB);
+//   * the array is shared by every call and keeps the last call's contents.  Nothing has to start at zero: the stats kernel
+//     overwrites every slot the apply kernel reads.  Calls that OVERLAP on the GPU (two streams, two threads) race on it —
+//     issue them on one stream, or order them with events.
+// In host code `g_gn_static_scratch` is only a stand-in for the symbol, not a device address: the address is fetched once
+// per device, with that device current, through cudaGetSymbolAddress and handed to the kernels.
+// ======================================================================================================
+static __device__ __align__(256) float g_gn_static_scratch[B200SD_GN_STATIC_SCRATCH_BYTES / sizeof(float)];
+
+namespace b200sd {
+namespace {
+constexpr int kMaxDevices = 64;
+float* g_gn_scratch_ptr[kMaxDevices];  // device address of g_gn_static_scratch, per device (nullptr = not set up yet)
+
+// once per device (the caller holds the device current): the symbol's address and the >48 KB shared-memory opt-in
+int gn_static_setup(int device, float** ptr) {
+  if (g_gn_scratch_ptr[device] == nullptr) {
+    void* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&p, g_gn_static_scratch);
+    if (e != cudaSuccess || p == nullptr) {
+      (void)cudaGetLastError();
+      return fail(B200SD_ERR_CUDA, "groupnorm_static_scratch: cudaGetSymbolAddress failed on device %d: %s", device,
+                  cudaGetErrorString(e));
+    }
+    B200SD_CUDA(cudaFuncSetAttribute(gn_stats_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 1024 * GN_FOLD_FLOATS * 4));
+    g_gn_scratch_ptr[device] = static_cast<float*>(p);
+  }
+  *ptr = g_gn_scratch_ptr[device];
+  return 0;
+}
+}  // namespace
+}  // namespace b200sd
+
+extern "C" int b200sd_groupnorm_static_scratch(int device, const b200sd_groupnorm* gp, void* cuda_stream) {
+  using namespace b200sd;
+  if (!gp) return fail(B200SD_ERR_INVALID, "groupnorm_static_scratch: NULL op");
+  const b200sd_groupnorm& g = *gp;
+  // ---- validation (host arithmetic only; the same rules as the program op) ----
+  B200SD_CHECK_ARG(g.x1 && g.out && g.gamma && g.beta, "groupnorm_static_scratch: NULL pointer");
+  B200SD_CHECK_ARG(g.partials == nullptr, "groupnorm_static_scratch: `partials` must be NULL (the scratch is the library's static array)");
+  B200SD_CHECK_ARG(g.C1 > 0 && g.C1 % 8 == 0 && g.C2 >= 0 && g.C2 % 8 == 0, "groupnorm: C1=%d C2=%d must be multiples of 8", g.C1, g.C2);
+  B200SD_CHECK_ARG(g.C2 == 0 || g.x2, "groupnorm: C2>0 needs x2");
+  const int C = g.C1 + g.C2;
+  B200SD_CHECK_ARG(g.groups >= 1 && g.groups <= 64 && C % g.groups == 0, "groupnorm: groups=%d does not divide C=%d", g.groups, C);
+  B200SD_CHECK_ARG(g.NB >= 1 && g.HW >= 1, "groupnorm: NB=%d HW=%d", g.NB, g.HW);
+  B200SD_CHECK_ARG(g.ld1 % 8 == 0 && g.ld1 >= g.C1 && (g.C2 == 0 || (g.ld2 % 8 == 0 && g.ld2 >= g.C2)), "groupnorm: bad pitches");
+  B200SD_CHECK_ARG(aligned16(g.x1) && aligned16(g.out) && (g.C2 == 0 || aligned16(g.x2)), "groupnorm: pointers must be 16-byte aligned");
+  B200SD_CHECK_ARG(C / 8 <= 1024, "groupnorm: C=%d too large", C);
+  B200SD_CHECK_ARG(device >= 0 && device < kMaxDevices, "groupnorm_static_scratch: device %d out of range", device);
+  GNPlan pl;
+  GNParams& p = pl.p;
+  p.x1 = static_cast<const bf16*>(g.x1); p.x2 = static_cast<const bf16*>(g.x2);
+  p.ld1 = g.ld1; p.ld2 = g.ld2; p.C1 = g.C1; p.C2 = g.C2; p.C = C;
+  p.NB = g.NB; p.HW = g.HW; p.groups = g.groups; p.cpg = C / g.groups; p.silu = g.silu; p.eps = g.eps;
+  p.gamma = g.gamma; p.beta = g.beta; p.out = static_cast<bf16*>(g.out);
+  p.chunks = groupnorm_chunks(g.NB, g.HW, C);
+  p.ppc = (g.HW + p.chunks - 1) / p.chunks;
+  p.chunks = (g.HW + p.ppc - 1) / p.ppc;
+  p.cols = C / 8;
+  p.R = std::max(1, 256 / p.cols);
+  pl.threads = p.cols * p.R;
+  if (pl.threads < g.groups) { p.R = (g.groups + p.cols - 1) / p.cols; pl.threads = p.cols * p.R; }
+  pl.smem = (2 * static_cast<size_t>(C) + 2 * g.groups) * sizeof(float) + 8 +
+            static_cast<size_t>(pl.threads / g.groups + 1) * g.groups * 2 * sizeof(double);
+  pl.smem_stats = static_cast<size_t>(pl.threads) * GN_FOLD_FLOATS * 4;
+  pl.fused = 0;  // always the two-kernel form: it is the one that needs scratch
+  const long long need = static_cast<long long>(g.NB) * p.chunks * g.groups * 2 * 4;
+  if (need > static_cast<long long>(B200SD_GN_STATIC_SCRATCH_BYTES))
+    return fail(B200SD_ERR_INVALID,
+                "groupnorm_static_scratch: NB=%d HW=%d C=%d needs %lld bytes of partial sums, the static scratch holds %d "
+                "(B200SD_GN_STATIC_SCRATCH_BYTES): use the program op with a caller workspace for this shape",
+                g.NB, g.HW, C, need, (int)B200SD_GN_STATIC_SCRATCH_BYTES);
+  // ---- device: current device, symbol address (once per device), two launches ----
+  int rc = b200sd_device_check(device);
+  if (rc) return rc;
+  B200SD_CUDA(cudaSetDevice(device));
+  float* scratch = nullptr;
+  rc = gn_static_setup(device, &scratch);
+  if (rc) return rc;
+  p.partials = scratch;
+  return launch_groupnorm(&pl, static_cast<cudaStream_t>(cuda_stream));
+}
