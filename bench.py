@@ -415,7 +415,7 @@ def run_workload(wl, dev, rank, world, local_rank, steps, warmup, B=None, pair=N
                h2d=sum(v.numel() * v.element_size() for v in host.values()), d2h=himg.numel() * himg.element_size(),
                clocks=clk.summary() if clock else None, eng=eng, model=model, pipe=pipe,
                exchange=getattr(eng, "exchange_kind", None))
-    if detail and rank == 0:
+    if detail and (rank == 0 or pair is not None):   # (the ranks of a cond/uncond pair step together: the exchange needs both)
         share, med_ms, sum_ms = step_breakdown(eng, N)
         kinds = eng.b.prog.kinds
         n_gemm = sum(1 for k in kinds if k == N.OP_GEMM)

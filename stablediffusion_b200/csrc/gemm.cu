@@ -1133,19 +1133,25 @@ int plan_gemm(const b200sd_gemm& g, PlannedOp* out) {
     const bool geglu = (g.flags & B200SD_GEMM_GEGLU) != 0;
     const int n_out = geglu ? g.N / 2 : g.N;
     const int bn_out = geglu ? bn / 2 : bn;
-    const bool identity = !g.spatial || (kp.OH == g.H && kp.OW == g.W && kp.sy == 1 && kp.sx == 1 && kp.oy == 0 && kp.ox == 0);
+    // A strided output lattice (out_scatter: the phase convs of a folded nearest-2x upsample write every second pixel of
+    // every second row) is still a plain tile grid for TMA: the tensor map carries the pixel / row strides and the base
+    // pointer carries the phase offset, coordinates stay those of the H x W grid this GEMM computes.
     const bool res = (g.flags & B200SD_GEMM_RESIDUAL) != 0;
     bool ok = t.splits == 1 && !(g.flags & B200SD_GEMM_OUT_F32) && bn >= 64 && bn_out % 32 == 0 && g.ldc % 8 == 0 &&
-              (reinterpret_cast<uintptr_t>(g.out) & 15) == 0 && identity && n_out >= 32;
+              (reinterpret_cast<uintptr_t>(g.out) & 15) == 0 && n_out >= 32;
+    if (g.spatial)
+      ok = ok && kp.oy >= 0 && kp.ox >= 0 && kp.oy < kp.sy && kp.ox < kp.sx && (g.H - 1) * kp.sy + kp.oy < kp.OH &&
+           (g.W - 1) * kp.sx + kp.ox < kp.OW;
     if (res) ok = ok && g.ldr % 8 == 0 && (reinterpret_cast<uintptr_t>(g.residual) & 15) == 0;
     kp.staged = 0;
     if (ok) {
       auto make = [&](CUtensorMap* m, const void* base, long long ld) {
         if (g.spatial) {
+          const char* b0 = static_cast<const char*>(base) + (static_cast<long long>(kp.oy) * kp.OW + kp.ox) * ld * 2;
           uint64_t dims[4] = {(uint64_t)n_out, (uint64_t)g.W, (uint64_t)g.H, (uint64_t)g.NB};
-          uint64_t st[3] = {(uint64_t)ld * 2, (uint64_t)g.W * ld * 2, (uint64_t)g.H * g.W * ld * 2};
+          uint64_t st[3] = {(uint64_t)kp.sx * ld * 2, (uint64_t)kp.sy * kp.OW * ld * 2, (uint64_t)kp.OH * kp.OW * ld * 2};
           uint32_t box[4] = {32, 1u << t.bw_log2, 1u << t.bh_log2, 1u << t.bn_log2};
-          return encode_tensor_map_bf16(m, base, 4, dims, st, box, 64);
+          return encode_tensor_map_bf16(m, b0, 4, dims, st, box, 64);
         }
         uint64_t dims[2] = {(uint64_t)n_out, (uint64_t)g.M};
         uint64_t st[1] = {(uint64_t)ld * 2};

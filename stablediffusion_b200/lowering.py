@@ -164,13 +164,14 @@ class Builder:
         return out
 
     def conv(self, x, w, out=None, taps=TAPS_3X3_S1, phases=1, out_hw=None, bias=None, rowvec=None, residual=None,
-             silu=False, extra=None, out_scatter=None, splits=0, block_n=0, cta_pair=0):
+             silu=False, extra=None, out_scatter=None, splits=0, block_n=0, cta_pair=0, algo_flops=None):
         """Implicit-GEMM convolution on NHWC bf16.
 
         x: [NB,H,W,C] (phases == 1) or [4,NB,H/2,W/2,C] (after phase_split); w: [Cout, len(taps)*C (+ extra K)].
         extra: optional list of (x_i [NB,H,W,C_i], 1x1) segments appended along K (their weights follow in w).
         rowvec: fp32 [NB, Cout] added per image (time embedding); residual: [NB,H,W,Cout].
         out_scatter: (OH, OW, sy, sx, oy, ox) to write a strided sub-lattice of a larger output.
+        algo_flops: algorithmic 2*MAC this op stands for when that differs from what it executes (folded upsample).
         """
         if x.dtype != torch.bfloat16 or not x.is_contiguous():
             raise ValueError("conv: x must be contiguous bf16")
@@ -191,6 +192,8 @@ class Builder:
         if ktot != Kw:
             raise ValueError(f"conv: weight K {Kw} != sum of segments {ktot}")
         if out is None:
+            if out_scatter is not None:
+                raise ValueError("conv: out_scatter needs the (larger) output tensor")
             out = self.empty([NB, H, W, Cout])
         g = N.Gemm()
         g.spatial = 1
@@ -216,9 +219,33 @@ class Builder:
         g.splits, g.block_n, g.cta_pair = splits, block_n, cta_pair
         ldr = residual.shape[-1] if residual is not None else 0
         self._epilogue(g, bias, rowvec, residual, ldr, silu, False, False, False, 1.0, 0)
-        self._pending_meta = dict(op=f'conv{len(taps)}', M=NB * H * W, N=Cout, K=ktot, flops=2 * NB * H * W * Cout * ktot, hw=(H, W))
+        flops = 2 * NB * H * W * Cout * ktot if algo_flops is None else int(algo_flops)
+        self._pending_meta = dict(op=f'conv{len(taps)}', M=NB * H * W, N=Cout, K=ktot, flops=flops, hw=(H, W))
         self._finish_gemm(g, (x, w, out, bias, residual, rowvec) + tuple(extra or ()))
-        self.gemm_flops += 2 * NB * H * W * Cout * ktot
+        self.gemm_flops += flops
+        return out
+
+    def upsample2x_conv(self, x, w, w_phase, bias=None, fold=None):
+        """conv3x3(nearest_upsample_2x(x)) (+bias): x [NB,H,W,C] -> [NB,2H,2W,Cout].
+        w: [Cout, 9C] plain packing; w_phase: [4, Cout, 4C] (packing.upsample_conv_phase_weights).
+        Folded form (four 2x2-tap phase convs over x, each writing its lattice of the output: 2.25x fewer MACs, no upsampled
+        tensor) where the phase GEMMs are large enough to fill the GPU, else upsample2x + one 3x3 conv (fewer launches).
+        `fold`: None = decide here; the decision reads the batch only outside the batch-invariant mode (the two forms round
+        differently: phase weights are pre-summed)."""
+        from .packing import upsample_conv_phase_taps
+
+        NB, H, W, Cin = x.shape
+        Cout = w.shape[0]
+        if fold is None:
+            rows = (8 if N.batch_invariant() else NB) * H * W      # kCanonBatch images in the batch-invariant mode
+            fold = rows >= 4096
+        if not fold:
+            return self.conv(self.upsample2x(x), w, bias=bias)
+        out = self.empty([NB, 2 * H, 2 * W, Cout])
+        for py in (0, 1):
+            for px in (0, 1):
+                self.conv(x, w_phase[py * 2 + px], out=out, taps=upsample_conv_phase_taps(py, px), bias=bias,
+                          out_scatter=(2 * H, 2 * W, 2, 2, py, px), algo_flops=2 * NB * H * W * Cout * 9 * Cin)
         return out
 
     # ---- normalisation ------------------------------------------------------------------------------

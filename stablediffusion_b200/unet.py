@@ -23,7 +23,7 @@ import torch
 from . import _native as N
 from . import lowering as L
 from .config import Config, unet_config
-from .packing import conv_weight_to_gemm, geglu_block_n, geglu_interleave
+from .packing import conv_weight_to_gemm, geglu_block_n, geglu_interleave, upsample_conv_phase_weights
 
 TEMB_MULT = 4
 
@@ -256,6 +256,7 @@ class PackedUNet:
             if blk["up"]:
                 p = f"{blk['name']}.upsamplers.0.conv"
                 T[f"{p}.w"], T[f"{p}.b"] = self._bf(conv_weight_to_gemm(self._w(f"{p}.weight"))), self._f32(self._w(f"{p}.bias"))
+                T[f"{p}.wph"] = self._bf(upsample_conv_phase_weights(self._w(f"{p}.weight")))
         T["conv_norm_out.g"], T["conv_norm_out.b"] = self._f32(self._w("conv_norm_out.weight")), self._f32(self._w("conv_norm_out.bias"))
         T["conv_out.w"] = self._bf(conv_weight_to_gemm(self._w("conv_out.weight")))
         T["conv_out.b"] = self._f32(self._w("conv_out.bias"))
@@ -379,7 +380,7 @@ class UNetLowering:
                     x = self.transformer(f"{blk['name']}.attentions.{j}", x, blk["attn"]["heads"], blk["attn"]["layers"])
             if blk["up"]:
                 p = f"{blk['name']}.upsamplers.0.conv"
-                x = b.conv(b.upsample2x(x), T[f"{p}.w"], bias=T[f"{p}.b"])
+                x = b.upsample2x_conv(x, T[f"{p}.w"], T[f"{p}.wph"], bias=T[f"{p}.b"])
         NBx, H, W, C = x.shape
         hn = b.groupnorm(x.view(NB, H * W, C), T["conv_norm_out.g"], T["conv_norm_out.b"], eps_r, True)
         eps = b.conv(hn.view(NB, H, W, C), T["conv_out.w"], bias=T["conv_out.b"],

@@ -16,7 +16,7 @@ import torch
 from . import _native as N
 from . import lowering as L
 from .config import Config, vae_config
-from .packing import conv_weight_to_gemm
+from .packing import conv_weight_to_gemm, upsample_conv_phase_weights
 
 
 def _resnet_shapes(p, cin, cout, sh):
@@ -174,6 +174,8 @@ class PackedVAE:
                     self._resnet(f"{blk['name']}.resnets.{j}", cin != cout)
                 if blk["up"]:
                     self._conv(f"{blk['name']}.upsamplers.0.conv")
+                    self.t[f"{blk['name']}.upsamplers.0.conv.wph"] = self._bf(
+                        upsample_conv_phase_weights(self._w(f"{blk['name']}.upsamplers.0.conv.weight")))
             self.t["decoder.conv_norm_out.g"] = self._f32(self._w("decoder.conv_norm_out.weight"))
             self.t["decoder.conv_norm_out.b"] = self._f32(self._w("decoder.conv_norm_out.bias"))
             self._conv("decoder.conv_out")
@@ -241,7 +243,7 @@ class VAELowering:
                 x = self.resnet(f"{blk['name']}.resnets.{j}", x, cout)
             if blk["up"]:
                 p = f"{blk['name']}.upsamplers.0.conv"
-                x = b.conv(b.upsample2x(x), T[f"{p}.w"], bias=T[f"{p}.b"])
+                x = b.upsample2x_conv(x, T[f"{p}.w"], T[f"{p}.wph"], bias=T[f"{p}.b"])
         NB, H, W, C = x.shape
         hn = b.groupnorm(x.view(NB, H * W, C), T["decoder.conv_norm_out.g"], T["decoder.conv_norm_out.b"], 1e-6, True)
         img = b.conv(hn.view(NB, H, W, C), T["decoder.conv_out.w"], bias=T["decoder.conv_out.b"])

@@ -362,3 +362,29 @@ def test_unet_pack_version_is_monotonic():
 
     u = B200UNet(unet_config(), None, device="cpu")
     assert u.pack_version == 0
+
+
+def test_upsample_conv_phase_weights_reproduce_conv_of_upsampled_input():
+    """Upsample2D folded into its conv (packing.upsample_conv_phase_weights): four 2x2-tap phase convs over the low-resolution
+    input, each filling one lattice of the output, equal conv3x3(nearest_upsample_2x(x)) exactly (fp64), border included."""
+    import torch.nn.functional as F
+
+    from stablediffusion_b200.packing import upsample_conv_phase_taps, upsample_conv_phase_weights
+
+    g = torch.Generator().manual_seed(0)
+    NB, H, W, Ci, Co = 2, 5, 7, 8, 6
+    x = torch.randn(NB, Ci, H, W, generator=g, dtype=torch.float64)
+    w = torch.randn(Co, Ci, 3, 3, generator=g, dtype=torch.float64)
+    ref = F.conv2d(F.interpolate(x, scale_factor=2.0, mode="nearest"), w, padding=1)
+    wp = upsample_conv_phase_weights(w)
+    assert wp.shape == (4, Co, 4 * Ci)
+    out = torch.zeros_like(ref)
+    xp = F.pad(x, (1, 1, 1, 1))
+    for py in (0, 1):
+        for px in (0, 1):
+            acc = torch.zeros(NB, Co, H, W, dtype=torch.float64)
+            for t, (ph, dh, dw) in enumerate(upsample_conv_phase_taps(py, px)):
+                assert ph == 0 and dh in (-1, 0, 1) and dw in (-1, 0, 1)
+                acc += torch.einsum("oc,nchw->nohw", wp[py * 2 + px][:, t * Ci:(t + 1) * Ci], xp[:, :, 1 + dh:1 + dh + H, 1 + dw:1 + dw + W])
+            out[:, :, py::2, px::2] = acc
+    assert (out - ref).abs().max().item() < 1e-12

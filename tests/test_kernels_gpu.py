@@ -276,6 +276,31 @@ def test_upsample_then_conv(cuda_device):
     _check(out, F.conv2d(upr, w.float(), padding=1).permute(0, 2, 3, 1), name="upsample+conv")
 
 
+@pytest.mark.parametrize("NB,H,W,C,Co", [(2, 16, 16, 320, 320), (1, 24, 40, 128, 64), (3, 8, 8, 64, 32), (16, 16, 16, 640, 640)])
+def test_upsample_folded_into_conv(cuda_device, NB, H, W, C, Co):
+    """Upsample2D as four 2x2-tap phase convs over the low-resolution input (lowering.upsample2x_conv, fold=True): strided
+    TMA-store epilogue (Co >= 64) and the direct strided epilogue (Co = 32), vs conv3x3(nearest 2x) in fp32 and vs the
+    unfolded path of the same builder."""
+    from stablediffusion_b200.packing import upsample_conv_phase_weights
+
+    dev = cuda_device
+    x = _bf(_randn((NB, H, W, C), dev, 1))
+    w = _bf(_randn((Co, C, 3, 3), dev, 2, 1.0 / math.sqrt(9 * C)))
+    bias = _randn((Co,), dev, 3) * 0.1
+    wph = _bf(upsample_conv_phase_weights(w.float()))
+    b = _builder(dev)
+    folded = b.upsample2x_conv(x, _pack_conv(w), wph, bias=bias, fold=True)
+    plain = b.upsample2x_conv(x, _pack_conv(w), wph, bias=bias, fold=False)
+    folded.fill_(float("nan"))          # every output pixel must be written by exactly one phase
+    _run(b)
+    assert folded.shape == (NB, 2 * H, 2 * W, Co) and b.prog.num_launches >= 6
+    upr = F.interpolate(x.float().permute(0, 3, 1, 2), scale_factor=2.0, mode="nearest")
+    ref = F.conv2d(upr, w.float(), bias, padding=1).permute(0, 2, 3, 1)
+    _check(folded, ref, name="folded upsample conv")
+    _check(plain, ref, name="upsample + conv")
+    _check(folded, plain.float(), name="folded vs unfolded")
+
+
 # ---------------------------------------------------------------------------------------------------
 # attention
 # ---------------------------------------------------------------------------------------------------
@@ -365,7 +390,8 @@ def test_attention_fused_qkv_views(cuda_device):
      (3, 100, 64, 32, True, 1e-5),
      # images that fit one cluster's shared memory take the single-launch kernel (gn_fused_kernel)
      (16, 1024, 640, 0, True, 1e-5), (2, 1024, 320, 320, True, 1e-5), (1, 7, 32, 0, True, 1e-5),
-     (2, 256, 1280, 1280, True, 1e-5), (5, 64, 1280, 0, False, 1e-5), (2, 1000, 640, 0, True, 1e-5)],
+     (2, 256, 1280, 1280, True, 1e-5), (5, 64, 1280, 0, False, 1e-5), (2, 1000, 640, 0, True, 1e-5),
+     (2, 1024, 640, 0, True, 1e-5), (2, 256, 1280, 640, True, 1e-5), (1, 2304, 320, 320, True, 1e-5), (2, 576, 1280, 0, True, 1e-5)],
 )
 def test_groupnorm(cuda_device, NB, HW, C1, C2, silu, eps):
     dev = cuda_device

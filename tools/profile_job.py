@@ -9,7 +9,7 @@ from stablediffusion_b200.models.stable_diffusion import SDModelWrapper
 from stablediffusion_b200.pipelines.sd_unified_pipeline import StableDiffusionUnifiedPipeline
 
 dev = torch.device("cuda:0")
-model_type, H, W, B, sampler, steps, guidance = bench.WORKLOADS["sd15_512_b8_ddim50_cfg"]
+model_type, H, W, B, sampler, steps, guidance, _ = bench.WORKLOADS["sd15_512_b8_ddim50_cfg"]
 model = SDModelWrapper.from_random(model_type, seed=0, device=str(dev))
 with contextlib.redirect_stdout(sys.stderr):
     model.set_scheduler(sampler)
