@@ -51,28 +51,115 @@ class _ImageProcessor:
         self.f = vae_scale_factor
         self.do_normalize = do_normalize
 
-    def preprocess(self, image, height=None, width=None, **unused):
+    @staticmethod
+    def get_crop_region(mask_image, width: int, height: int, pad: int = 0):
+        """`mask_processor.get_crop_region` (pipeline :271; diffusers VaeImageProcessor): the rectangle (x1, y1, x2, y2) that
+        holds every non-zero mask pixel, grown by `pad`, then expanded to the aspect ratio of the (width, height) the pipeline
+        processes at, and shifted back inside the image."""
+        import numpy as np
+
+        if isinstance(mask_image, (list, tuple)):
+            mask_image = mask_image[0]
+        if not hasattr(mask_image, "convert"):
+            raise ValueError("padding_mask_crop needs PIL images (the reference's get_crop_region works on a PIL mask)")
+        mask = np.array(mask_image.convert("L"))
+        h, w = mask.shape
+        cols = np.nonzero(mask.any(axis=0))[0]
+        rows = np.nonzero(mask.any(axis=1))[0]
+        crop_left, crop_right = (int(cols[0]), int(w - 1 - cols[-1])) if len(cols) else (w, w)
+        crop_top, crop_bottom = (int(rows[0]), int(h - 1 - rows[-1])) if len(rows) else (h, h)
+        x1, y1 = int(max(crop_left - pad, 0)), int(max(crop_top - pad, 0))
+        x2, y2 = int(min(w - crop_right + pad, w)), int(min(h - crop_bottom + pad, h))
+        ratio_crop_region = (x2 - x1) / (y2 - y1)
+        ratio_processing = width / height
+        if ratio_crop_region > ratio_processing:
+            desired_height = (x2 - x1) / ratio_processing
+            diff = int(desired_height - (y2 - y1))
+            y1 -= diff // 2
+            y2 += diff - diff // 2
+            if y2 >= h:
+                d = y2 - h
+                y2 -= d
+                y1 -= d
+            if y1 < 0:
+                y2 -= y1
+                y1 -= y1
+            if y2 >= h:
+                y2 = h
+        else:
+            desired_width = (y2 - y1) * ratio_processing
+            diff = int(desired_width - (x2 - x1))
+            x1 -= diff // 2
+            x2 += diff - diff // 2
+            if x2 >= w:
+                d = x2 - w
+                x2 -= d
+                x1 -= d
+            if x1 < 0:
+                x2 -= x1
+                x1 -= x1
+            if x2 >= w:
+                x2 = w
+        return x1, y1, x2, y2
+
+    @staticmethod
+    def _resize_and_fill(im, width: int, height: int):
+        """resize_mode="fill" (pipeline :272): keep the aspect ratio, centre, fill what is left with the stretched border."""
+        from PIL import Image
+
+        ratio, src_ratio = width / height, im.width / im.height
+        src_w = width if ratio < src_ratio else im.width * height // im.height
+        src_h = height if ratio >= src_ratio else im.height * width // im.width
+        resized = im.resize((src_w, src_h), resample=Image.LANCZOS)
+        res = Image.new(im.mode, (width, height))
+        res.paste(resized, box=(width // 2 - src_w // 2, height // 2 - src_h // 2))
+        if ratio < src_ratio:
+            fill = height // 2 - src_h // 2
+            if fill > 0:
+                res.paste(resized.resize((width, fill), box=(0, 0, width, 0)), box=(0, 0))
+                res.paste(resized.resize((width, fill), box=(0, resized.height, width, resized.height)), box=(0, fill + src_h))
+        elif ratio > src_ratio:
+            fill = width // 2 - src_w // 2
+            if fill > 0:
+                res.paste(resized.resize((fill, height), box=(0, 0, 0, height)), box=(0, 0))
+                res.paste(resized.resize((fill, height), box=(resized.width, 0, resized.width, height)), box=(fill + src_w, 0))
+        return res
+
+    def _pil_resize(self, im, width, height, crops_coords, resize_mode):
+        w, h = im.size
+        w, h = (width or w) // self.f * self.f, (height or h) // self.f * self.f
+        if crops_coords is not None:
+            im = im.crop(crops_coords)
+        if resize_mode == "fill":
+            return self._resize_and_fill(im, w, h)
+        if resize_mode != "default":
+            raise ValueError(f"resize_mode {resize_mode} is not supported")
+        return im.resize((w, h))
+
+    def preprocess(self, image, height=None, width=None, crops_coords=None, resize_mode="default", **unused):
         import numpy as np
 
         if isinstance(image, torch.Tensor):
+            if crops_coords is not None:
+                raise ValueError("padding_mask_crop needs PIL images")
             x = image if image.dim() == 4 else image[None]
             return x  # tensors are taken as already in [-1, 1] (diffusers does the same for tensor input in [-1,1])
         imgs = image if isinstance(image, list) else [image]
         arrs = []
         for im in imgs:
-            w, h = im.size
-            w, h = (width or w) // self.f * self.f, (height or h) // self.f * self.f
-            im = im.convert("RGB").resize((w, h))
+            im = self._pil_resize(im.convert("RGB"), width, height, crops_coords, resize_mode)
             arrs.append(np.asarray(im, dtype=np.float32) / 255.0)
         x = torch.from_numpy(np.stack(arrs)).permute(0, 3, 1, 2)
         return 2.0 * x - 1.0 if self.do_normalize else x
 
-    def preprocess_mask(self, mask, height=None, width=None):
+    def preprocess_mask(self, mask, height=None, width=None, crops_coords=None, resize_mode="default"):
         """`mask_processor.preprocess` (pipeline :283-285; VaeImageProcessor(do_normalize=False, do_binarize=True,
-        do_convert_grayscale=True)): one channel in {0, 1}, 1 = repaint, resized (nearest) to (height, width)."""
+        do_convert_grayscale=True)): one channel in {0, 1}, 1 = repaint, resized to (height, width)."""
         import numpy as np
 
         if isinstance(mask, torch.Tensor):
+            if crops_coords is not None:
+                raise ValueError("padding_mask_crop needs PIL images")
             x = mask.float()
             while x.dim() < 4:
                 x = x[None]
@@ -80,6 +167,8 @@ class _ImageProcessor:
                 x = x.mean(dim=1, keepdim=True)
         else:
             masks = mask if isinstance(mask, list) else [mask]
+            if crops_coords is not None or resize_mode != "default":
+                masks = [self._pil_resize(mm.convert("L"), width, height, crops_coords, resize_mode) for mm in masks]
             x = torch.from_numpy(np.stack([np.asarray(mm.convert("L"), dtype=np.float32) / 255.0 for mm in masks]))[:, None]
         if height is not None and width is not None and tuple(x.shape[-2:]) != (height, width):
             x = torch.nn.functional.interpolate(x, size=(height, width))

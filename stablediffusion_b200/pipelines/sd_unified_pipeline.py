@@ -170,13 +170,17 @@ class StableDiffusionUnifiedPipeline:
         """reference :266-380 for a 4-channel UNet (the only inpainting mode the reference's loop implements: it never
         concatenates mask / masked-image latents to the UNet input, :465-482).  Returns the blend inputs of :492-506."""
         m = self.model
-        if padding_mask_crop is not None:
-            raise ValueError("padding_mask_crop is not supported on the B200 path")
+        crops_coords, resize_mode = None, "default"
+        if padding_mask_crop is not None:  # reference :270-275 (the crop happens before the loop; no overlay: a tensor is returned)
+            crops_coords = m.mask_processor.get_crop_region(mask_image, width, height, pad=padding_mask_crop)
+            resize_mode = "fill"
         if m.base.config.in_channels != 4:
             raise ValueError(f"The unet {m.base.__class__} should have 4 input channels for inpainting on this path, "
                              f"not {m.base.config.in_channels}.")
-        init_image = m.image_processor.preprocess(image, height=height, width=width).to(dtype=torch.float32)
-        mask = m.mask_processor.preprocess_mask(mask_image, height=height, width=width)
+        init_image = m.image_processor.preprocess(image, height=height, width=width, crops_coords=crops_coords,
+                                                  resize_mode=resize_mode).to(dtype=torch.float32)
+        mask = m.mask_processor.preprocess_mask(mask_image, height=height, width=width, crops_coords=crops_coords,
+                                                resize_mode=resize_mode)
         timesteps, num_inference_steps = self.get_timesteps(
             num_inference_steps, strength, denoising_start if denoising_value_valid(denoising_start) else None)
         if num_inference_steps < 1:

@@ -388,3 +388,34 @@ def test_upsample_conv_phase_weights_reproduce_conv_of_upsampled_input():
                 acc += torch.einsum("oc,nchw->nohw", wp[py * 2 + px][:, t * Ci:(t + 1) * Ci], xp[:, :, 1 + dh:1 + dh + H, 1 + dw:1 + dw + W])
             out[:, :, py::2, px::2] = acc
     assert (out - ref).abs().max().item() < 1e-12
+
+
+def test_padding_mask_crop_region_and_fill_resize():
+    """`padding_mask_crop` (reference :270-285): the crop region holds the padded mask box, has the processing aspect ratio,
+    stays inside the image; image and mask are cropped to it and brought to (width, height)."""
+    import numpy as np
+    from PIL import Image
+
+    from stablediffusion_b200.models.stable_diffusion import _ImageProcessor
+
+    proc = _ImageProcessor(8)
+    m = np.zeros((300, 400), dtype=np.uint8)
+    m[100:160, 250:330] = 255
+    mask = Image.fromarray(m)
+    x1, y1, x2, y2 = proc.get_crop_region(mask, 512, 512, pad=16)
+    assert x1 <= 250 - 16 and x2 >= 330 + 16 and y1 <= 100 - 16 and y2 >= 160 + 16
+    assert 0 <= x1 < x2 <= 400 and 0 <= y1 < y2 <= 300
+    assert abs((x2 - x1) / (y2 - y1) - 1.0) < 0.05
+    # a box at the border is shifted back inside, not clipped out of ratio
+    m2 = np.zeros((300, 400), dtype=np.uint8)
+    m2[0:40, 380:400] = 255
+    bx = proc.get_crop_region(Image.fromarray(m2), 512, 256, pad=8)
+    assert bx[0] >= 0 and bx[2] <= 400 and bx[1] >= 0 and bx[3] <= 300 and abs((bx[2] - bx[0]) / (bx[3] - bx[1]) - 2.0) < 0.1
+    img = Image.fromarray((np.random.default_rng(0).random((300, 400, 3)) * 255).astype(np.uint8))
+    t = proc.preprocess(img, height=512, width=512, crops_coords=(x1, y1, x2, y2), resize_mode="fill")
+    assert t.shape == (1, 3, 512, 512) and -1.0 <= float(t.min()) and float(t.max()) <= 1.0
+    mk = _ImageProcessor(8, do_normalize=False).preprocess_mask(mask, height=512, width=512, crops_coords=(x1, y1, x2, y2), resize_mode="fill")
+    assert mk.shape == (1, 1, 512, 512) and set(mk.unique().tolist()) <= {0.0, 1.0}
+    assert 0.05 < mk.mean().item() < 0.6        # the masked box now fills a good part of the frame
+    with pytest.raises(ValueError, match="PIL"):
+        proc.preprocess(torch.zeros(1, 3, 64, 64), crops_coords=(0, 0, 8, 8))
