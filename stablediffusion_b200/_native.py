@@ -12,7 +12,8 @@ import subprocess
 import threading
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "_lib", "libb200sd.so")
+# B200SD_LIB_DIR: tuning aid — load a variant build (csrc/build.sh with B200SD_LIB_OUT / B200SD_EXTRA_NVCC_FLAGS) for same-box A/Bs
+LIB_PATH = os.path.join(os.environ.get("B200SD_LIB_DIR") or os.path.join(_HERE, "_lib"), "libb200sd.so")
 BUILD_SCRIPT = os.path.join(_HERE, "csrc", "build.sh")
 
 MAX_SEG = 3

@@ -3,7 +3,7 @@
 # fast-math stays off: GroupNorm / timestep-embedding parity needs IEEE sinf/cosf/expf/division.
 set -euo pipefail
 HERE="$(cd "$(dirname "${BASH_SOURCE[0]}")" && pwd)"
-OUT="$HERE/../_lib"
+OUT="${B200SD_LIB_OUT:-$HERE/../_lib}"
 mkdir -p "$OUT"
 NVCC="${NVCC:-/usr/local/cuda/bin/nvcc}"
 FLAGS=(${B200SD_EXTRA_NVCC_FLAGS:-} -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17

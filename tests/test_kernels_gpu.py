@@ -352,6 +352,7 @@ def test_attention_growing_scores(cuda_device, Nkv, d):
     k = _randn((B, Nkv, C), dev, 2) * 0.25 + ramp
     k[:, Nkv - 37] += 3.0
     k[:, Nkv // 2 + 5] += 2.0
+    k[:, 3 * 64 + 45] += 4.0  # an outlier in the SECOND 32-key chunk of its block (the first chunk's P is already stored)
     k = _bf(k)
     v = _bf(_randn((B, Nkv, C), dev, 3))
     scale = d ** -0.5
