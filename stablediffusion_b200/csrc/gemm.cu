@@ -338,8 +338,13 @@ __device__ __forceinline__ void epilogue_geglu16(const GemmKParams& p, const Row
   reinterpret_cast<uint4*>(op)[1] = o1;
 }
 
-template <int BN, int NCTA>
+// GEGLU: compile-time epilogue family.  The epilogue is the critical path of the short-K GEMMs and is bound by its register
+// allocation and dependent chains, not by its instruction count: code of the family NOT taken costs every launch (measured:
+// profiles/r02_ln_fold_experiment.txt), so the h * gelu(g) epilogue and the bias / residual / activation one are separate kernels.
+// EPI: 0 = any flag combination but GEGLU (runtime branches), 1 = GEGLU, 2 = bias only (or nothing), 3 = bias + residual.
+template <int BN, int NCTA, int EPI>
 __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_constant__ GemmKParams p) {
+  constexpr bool GEGLU = EPI == 1;
   constexpr int B_ROWS = BN / NCTA;                   // weight rows this CTA stages (a CTA pair splits the N tile)
   constexpr int B_STAGE_BYTES = B_ROWS * 128;
   constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
@@ -516,13 +521,13 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
     // Issuing a 128-row TMA box costs the issuing thread several hundred cycles, so it is kept off the epilogue warps:
     // this lane prefetches the residual sub-tiles of its group RES_AHEAD ahead into the ring slots and stores every
     // sub-tile its 128 epilogue threads have marked ready.
-    if (p.staged && n_items > 0 && elect_one()) {
+    if ((EPI >= 2 || p.staged) && n_items > 0 && elect_one()) {
       const int g = warp - 10;
-      const bool geglu = (p.flags & B200SD_GEMM_GEGLU) != 0;
+      constexpr bool geglu = GEGLU;
 #ifdef B200SD_GEMM_NORES  // diagnostic build only: residual sub-tiles are not loaded (nor added)
       const bool has_res = false;
 #else
-      const bool has_res = (p.flags & B200SD_GEMM_RESIDUAL) != 0;
+      const bool has_res = EPI == 3 || (EPI == 0 && (p.flags & B200SD_GEMM_RESIDUAL) != 0);
 #endif
       const int bn_out = geglu ? BN / 2 : BN;
       const int nsub = bn_out / 32;
@@ -584,17 +589,17 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
         else mbar_arrive(&tempty_bar[a]);
       }
     };
-    if (p.staged) {
+    if (EPI >= 2 || p.staged) {  // (families 2 and 3 are only planned for staged outputs)
       // ---- staged epilogue: sub-tiles go through an 8-slot swizzled smem ring; the residual sub-tile is prefetched by
       // TMA RES_AHEAD sub-tiles ahead into the slot it is added in, results leave by TMA store (coalesced, OOB clipped).
-      const bool geglu = (p.flags & B200SD_GEMM_GEGLU) != 0;
+      constexpr bool geglu = GEGLU;
 #ifdef B200SD_GEMM_NORES
       const bool has_res = false;
 #else
-      const bool has_res = (p.flags & B200SD_GEMM_RESIDUAL) != 0;
+      const bool has_res = EPI == 3 || (EPI == 0 && (p.flags & B200SD_GEMM_RESIDUAL) != 0);
 #endif
       const bool has_bias = (p.flags & B200SD_GEMM_BIAS) != 0;
-      const bool extra = (p.flags & (B200SD_GEMM_BIAS_ROW | B200SD_GEMM_ROWVEC | B200SD_GEMM_SILU | B200SD_GEMM_QUICK_GELU | B200SD_GEMM_GELU)) != 0;
+      const bool extra = EPI == 0 && (p.flags & (B200SD_GEMM_BIAS_ROW | B200SD_GEMM_ROWVEC | B200SD_GEMM_SILU | B200SD_GEMM_QUICK_GELU | B200SD_GEMM_GELU)) != 0;
       const int bn_out = geglu ? BN / 2 : BN;
       const int nsub = bn_out / 32;
       const int sw = (r >> 1) & 3;  // SWIZZLE_64B: 16-byte chunk index ^= (row / 2) % 4
@@ -628,7 +633,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
           for (int j = 0; j < 32; ++j) v[j] = 0.f;
           if (false) {
 #else
-          if (geglu) {
+          if constexpr (geglu) {
 #endif
             uint32_t uh[32], ug[32];
             tmem_ld32(taddr + sub * 32, uh);
@@ -734,8 +739,8 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
             for (int j = 0; j < 4; ++j)
               reinterpret_cast<uint4*>(dst + c * 16)[j] = make_uint4(u[4 * j], u[4 * j + 1], u[4 * j + 2], u[4 * j + 3]);
           }
-        } else if (p.flags & B200SD_GEMM_GEGLU) {
-          if constexpr (BN % 32 == 0) {
+        } else if (GEGLU) {
+          if constexpr (GEGLU && BN % 32 == 0) {
 #pragma unroll 1
             for (int c = g; c < BN / 32; c += 2) {
               uint32_t uh[16], ug[16];
@@ -826,53 +831,63 @@ struct GemmPlan {
   int ncta;
   int grid;
   int reduce_grid_x, reduce_grid_y;
+  int epi;  // epilogue family the kernel is instantiated for (epilogue_family)
 };
 
-template <int BN, int NCTA>
+template <int BN, int NCTA, int EPI>
 int prepare_gemm_bn() {  // called at plan time (outside any stream capture)
   static bool attr_set = false;
   if (!attr_set) {
-    B200SD_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<BN, NCTA>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    B200SD_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<BN, NCTA, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      gemm_smem_bytes(BN, NCTA)));
     attr_set = true;
   }
   return 0;
 }
-template <int NCTA>
-int prepare_gemm_n(int bn) {
-  switch (bn) {
-    case 32: return prepare_gemm_bn<32, NCTA>();
-    case 64: return prepare_gemm_bn<64, NCTA>();
-    case 128: return prepare_gemm_bn<128, NCTA>();
-    case 160: return prepare_gemm_bn<160, NCTA>();
-    case 256: return prepare_gemm_bn<256, NCTA>();
-  }
-  return fail(B200SD_ERR_INVALID, "gemm: unsupported block_n %d", bn);
+// Epilogue family of a plan (the specialised families exist for the tile widths the UNet / VAE layers use).
+int epilogue_family(int bn, int flags, int staged) {
+  if (flags & B200SD_GEMM_GEGLU) return 1;
+  if (!staged || bn < 128) return 0;
+  const int other = flags & ~(B200SD_GEMM_BIAS | B200SD_GEMM_RESIDUAL);
+  if (other) return 0;
+  return (flags & B200SD_GEMM_RESIDUAL) ? 3 : 2;
 }
-int prepare_gemm(int bn, int ncta) { return ncta == 2 ? prepare_gemm_n<2>(bn) : prepare_gemm_n<1>(bn); }
-
-template <int BN, int NCTA>
-int launch_gemm_bn(const GemmPlan& pl, cudaStream_t s) {
-  B200SD_CUDA(launch_kernel(gemm_tc_kernel<BN, NCTA>, dim3(pl.grid), dim3(GEMM_THREADS), gemm_smem_bytes(BN, NCTA), s, NCTA, pl.kp));
+template <int BN, int NCTA, int EPI>
+int launch_gemm_epi(const GemmPlan& pl, cudaStream_t s) {
+  B200SD_CUDA(launch_kernel(gemm_tc_kernel<BN, NCTA, EPI>, dim3(pl.grid), dim3(GEMM_THREADS), gemm_smem_bytes(BN, NCTA), s, NCTA, pl.kp));
   if (pl.kp.splits > 1) {
     B200SD_CUDA(launch_kernel(gemm_splitk_reduce_kernel<BN>, dim3(pl.reduce_grid_x, pl.reduce_grid_y), dim3(128), 0, s, 1, pl.kp));
   }
   return 0;
 }
-template <int NCTA>
-int launch_gemm_n(const GemmPlan& pl, cudaStream_t s) {
-  switch (pl.block_n) {
-    case 32: return launch_gemm_bn<32, NCTA>(pl, s);
-    case 64: return launch_gemm_bn<64, NCTA>(pl, s);
-    case 128: return launch_gemm_bn<128, NCTA>(pl, s);
-    case 160: return launch_gemm_bn<160, NCTA>(pl, s);
-    case 256: return launch_gemm_bn<256, NCTA>(pl, s);
+// One switch for both uses: LAUNCH = false sets the kernel attribute, true launches.
+template <bool LAUNCH, int BN, int NCTA>
+int dispatch_gemm_epi(int epi, const GemmPlan* pl, cudaStream_t s) {
+#define B200SD_GEMM_EPI(E) \
+  if (epi == E) { if constexpr (LAUNCH) return launch_gemm_epi<BN, NCTA, E>(*pl, s); else return prepare_gemm_bn<BN, NCTA, E>(); }
+  B200SD_GEMM_EPI(0)
+  if constexpr (BN % 64 == 0) { B200SD_GEMM_EPI(1) }   // (a GEGLU tile holds whole 32-column h | g halves)
+  if constexpr (BN >= 128) { B200SD_GEMM_EPI(2) B200SD_GEMM_EPI(3) }
+#undef B200SD_GEMM_EPI
+  return fail(B200SD_ERR_INVALID, "gemm: epilogue family %d not built for block_n %d", epi, BN);
+}
+template <bool LAUNCH, int NCTA>
+int dispatch_gemm_n(int bn, int epi, const GemmPlan* pl, cudaStream_t s) {
+  switch (bn) {
+    case 32: return dispatch_gemm_epi<LAUNCH, 32, NCTA>(epi, pl, s);
+    case 64: return dispatch_gemm_epi<LAUNCH, 64, NCTA>(epi, pl, s);
+    case 128: return dispatch_gemm_epi<LAUNCH, 128, NCTA>(epi, pl, s);
+    case 160: return dispatch_gemm_epi<LAUNCH, 160, NCTA>(epi, pl, s);
+    case 256: return dispatch_gemm_epi<LAUNCH, 256, NCTA>(epi, pl, s);
   }
-  return fail(B200SD_ERR_INVALID, "gemm: unsupported block_n %d", pl.block_n);
+  return fail(B200SD_ERR_INVALID, "gemm: unsupported block_n %d", bn);
+}
+int prepare_gemm(int bn, int ncta, int epi) {
+  return ncta == 2 ? dispatch_gemm_n<false, 2>(bn, epi, nullptr, nullptr) : dispatch_gemm_n<false, 1>(bn, epi, nullptr, nullptr);
 }
 int launch_gemm(const void* plan, cudaStream_t s) {
   const GemmPlan& pl = *static_cast<const GemmPlan*>(plan);
-  return pl.ncta == 2 ? launch_gemm_n<2>(pl, s) : launch_gemm_n<1>(pl, s);
+  return pl.ncta == 2 ? dispatch_gemm_n<true, 2>(pl.block_n, pl.epi, &pl, s) : dispatch_gemm_n<true, 1>(pl.block_n, pl.epi, &pl, s);
 }
 
 int ilog2(int v) {
@@ -1166,7 +1181,8 @@ int plan_gemm(const b200sd_gemm& g, PlannedOp* out) {
   }
   pl->block_n = bn;
   pl->ncta = t.ncta;
-  rc = prepare_gemm(bn, t.ncta);
+  pl->epi = epilogue_family(bn, kp.flags, kp.staged);
+  rc = prepare_gemm(bn, t.ncta, pl->epi);
   if (rc) { delete pl; return rc; }
   long long total_work = static_cast<long long>(t.num_pm) * t.num_n_tiles * t.splits;
   pl->grid = static_cast<int>(std::min<long long>(total_work, std::max(1, sm_count() / t.ncta))) * t.ncta;
