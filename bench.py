@@ -423,11 +423,11 @@ def run_workload(wl, dev, rank, world, local_rank, steps, warmup, B=None, pair=N
         att_ms = step_ms * share.get(N.OP_ATTENTION, 0.0)
         achieved = eng.gemm_flops / (gemm_ms * 1e-3) / 1e12
         traffic, traffic_src = None, None   # DRAM bytes per launch of the same kernel from the committed ncu capture
-        tp = os.path.join(ROOT, "profiles", "r01_gemm_traffic.json")
-        if wl == "sd15_512_b8_ddim50_cfg" and os.path.exists(tp):
-            with open(tp) as f:
+        tps = sorted(f for f in os.listdir(os.path.join(ROOT, "profiles")) if f.endswith("_gemm_traffic.json"))
+        if wl == "sd15_512_b8_ddim50_cfg" and tps:   # the latest committed capture of the same command
+            with open(os.path.join(ROOT, "profiles", tps[-1])) as f:
                 td = json.load(f)
-            traffic, traffic_src = td["dram_bytes_per_launch"], "profiles/r01_gemm_traffic.json (ncu --set full, cold cache per launch)"
+            traffic, traffic_src = td["dram_bytes_per_launch"], f"profiles/{tps[-1]} (ncu launch list of this workload, cold cache per launch)"
         res["roofline"] = {
             "bound": "tensor", "kernel": "gemm_tc_kernel (tcgen05 implicit GEMM, all conv/linear launches of one sampler step)",
             "achieved": achieved, "peak": pk["tf"], "unit": "TFLOP/s", "frac": achieved / pk["tf"], "traffic": traffic,

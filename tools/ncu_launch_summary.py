@@ -3,7 +3,10 @@
 runs torch `at::` kernels outside the timed region)."""
 import csv, sys, collections, re
 ours = "--ours" in sys.argv
-rows = list(csv.reader(l for l in open([x for x in sys.argv[1:] if not x.startswith("--")][0]) if l.startswith('"')))
+# --traffic-json=OUT: also write the per-launch DRAM traffic of the GEMM kernel family (bench.py's roofline.traffic reads it)
+traffic_out = next((x.split("=", 1)[1] for x in sys.argv[1:] if x.startswith("--traffic-json=")), None)
+src_csv = [x for x in sys.argv[1:] if not x.startswith("--")][0]
+rows = list(csv.reader(l for l in open(src_csv) if l.startswith('"')))
 hdr = rows[0]; H = {h: i for i, h in enumerate(hdr)}
 agg = collections.defaultdict(lambda: dict(ids=set(), ns=0.0, rd=0.0, wr=0.0))
 def val(r):
@@ -26,3 +29,12 @@ print(f"{'kernel':48s} {'launches':>8s} {'total ms':>9s} {'share':>6s} {'avg us'
 for name, a in sorted(agg.items(), key=lambda x: -x[1]["ns"]):
     n = len(a["ids"])
     print(f"{name[:48]:48s} {n:8d} {a['ns']/1e6:9.3f} {100*a['ns']/tot:5.1f}% {a['ns']/n/1e3:8.1f} {a['rd']/n/1e6:17.2f} {a['wr']/n/1e6:17.2f}")
+
+if traffic_out:
+    import json
+    g = [a for n, a in agg.items() if n.startswith("gemm_tc_kernel")]
+    n = sum(len(a["ids"]) for a in g)
+    json.dump({"kernel": "gemm_tc_kernel", "launches_profiled": n, "dram_bytes_per_launch": sum(a["rd"] + a["wr"] for a in g) / max(n, 1),
+               "source": "ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none over "
+                         "bench.py --steps 1 --warmup 3 (sd15_512_b8_ddim50_cfg); ncu flushes caches before every kernel, so this is a cold-cache figure",
+               "csv": src_csv}, open(traffic_out, "w"), indent=1)

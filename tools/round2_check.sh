@@ -5,7 +5,13 @@ set -u
 T=${1:-r02}
 OUT=gpurun_out
 mkdir -p $OUT
-python -m pytest tests/test_kernels_gpu.py tests/test_configs_gpu.py tests/test_zz_no_alloc.py -m gpu -x -q -p no:cacheprovider > $OUT/${T}_pytest_kernels.log 2>&1; echo "pytest rc=$?"; tail -3 $OUT/${T}_pytest_kernels.log
+if [ "${FULL:-0}" = "1" ]; then   # what the driver runs at round end: the whole GPU suite, then smoke()
+  python -m pytest tests -m gpu -x -q -p no:cacheprovider > $OUT/${T}_pytest_gpu.log 2>&1; echo "pytest -m gpu rc=$?"; tail -3 $OUT/${T}_pytest_gpu.log
+  grep -E "PARITY|PSNR|rel-L2" $OUT/${T}_pytest_gpu.log | head -40
+  python -c "import __graft_entry__ as g; g.smoke()" > $OUT/${T}_smoke.log 2>&1; echo "smoke rc=$?"; tail -2 $OUT/${T}_smoke.log
+else
+  python -m pytest tests/test_kernels_gpu.py tests/test_configs_gpu.py tests/test_zz_no_alloc.py -m gpu -x -q -p no:cacheprovider > $OUT/${T}_pytest_kernels.log 2>&1; echo "pytest rc=$?"; tail -3 $OUT/${T}_pytest_kernels.log
+fi
 python tools/profile_step.py --batch 8 --out $OUT/${T}_profile_step_b8.txt > /dev/null 2>&1; head -1 $OUT/${T}_profile_step_b8.txt
 python tools/profile_step.py --batch 1 --out $OUT/${T}_profile_step_b1.txt > /dev/null 2>&1; head -1 $OUT/${T}_profile_step_b1.txt
 python tools/profile_vae.py --out $OUT/${T}_profile_vae_b8.txt > /dev/null 2>&1; head -3 $OUT/${T}_profile_vae_b8.txt
@@ -18,8 +24,8 @@ python -c "import json; a=json.load(open('$OUT/${T}_bench.json')); b=json.load(o
 if [ "${NCU:-1}" = "1" ]; then
   SHORT="python bench.py --steps 1 --warmup 3 --no-cpu-baseline --no-extras --no-yardstick"
   timeout 900 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none -s 61500 -c 1000 --csv --log-file $OUT/${T}_launches.csv $SHORT > $OUT/${T}_ncu_launch.log 2>&1; echo "ncu launch list rc=$?"; tail -2 $OUT/${T}_ncu_launch.log | cut -c1-300
-  python tools/ncu_launch_summary.py $OUT/${T}_launches.csv --ours > $OUT/${T}_ncu_launch_list.txt 2>&1; head -14 $OUT/${T}_ncu_launch_list.txt
+  python tools/ncu_launch_summary.py $OUT/${T}_launches.csv --ours --traffic-json=$OUT/${T}_gemm_traffic.json > $OUT/${T}_ncu_launch_list.txt 2>&1; head -14 $OUT/${T}_ncu_launch_list.txt
   timeout 600 ncu --set full --clock-control none --import-source on -k regex:gemm_tc_kernel -s 20000 -c 3 -o $OUT/${T}_prof_gemm $SHORT > $OUT/${T}_ncu_gemm.log 2>&1; echo "ncu gemm rc=$?"
   timeout 600 ncu --set full --clock-control none --import-source on -k regex:attention_kernel -s 600 -c 2 -o $OUT/${T}_prof_attn $SHORT > $OUT/${T}_ncu_attn.log 2>&1; echo "ncu attention rc=$?"
-  timeout 600 ncu --set full --clock-control none -k regex:gn_ -s 4000 -c 4 -o $OUT/${T}_prof_gn $SHORT > $OUT/${T}_ncu_gn.log 2>&1; echo "ncu groupnorm rc=$?"
+  timeout 600 ncu --set full --clock-control none -k regex:gn_apply -s 2000 -c 3 -o $OUT/${T}_prof_gn $SHORT > $OUT/${T}_ncu_gn.log 2>&1; echo "ncu groupnorm rc=$?"
 fi
