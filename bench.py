@@ -438,6 +438,22 @@ def run_workload(wl, dev, rank, world, local_rank, steps, warmup, B=None, pair=N
             "step_share_by_kind": {N.OP_NAMES[k]: round(v, 4) for k, v in sorted(share.items())},
             "step_ms_by_kind": {N.OP_NAMES[k]: round(step_ms * v, 4) for k, v in sorted(share.items())},
             "attention_tflops": (eng.attn_flops / (att_ms * 1e-3) / 1e12) if att_ms > 0 else None}
+        # The attention kernels of this model are bound by the MUFU ex2 rate, not by the tensor pipe (head dim 40..160: one
+        # exponential per score against 4*d tensor flops): 16 ex2 per clock and SM (measured, tools/micro/mufu.cu) at the SM clock
+        # sampled during the timed region.  Reported for the self-attention launches of the largest sequence (the dominant kernel).
+        att_idx = [i for i, k in enumerate(kinds) if k == N.OP_ATTENTION and i in eng.b.meta]
+        if att_idx and res["clocks"] and res["clocks"].get("sm_mhz"):
+            big = max(att_idx, key=lambda i: eng.b.meta[i]["Nq"] * eng.b.meta[i]["Nkv"])
+            m = eng.b.meta[big]
+            same = [i for i in att_idx if all(eng.b.meta[i][k] == m[k] for k in ("B", "heads", "Nq", "Nkv", "d"))]
+            us = sum(med_ms[i] for i in same) / len(same) * 1e3 * (step_ms / sum_ms)
+            exps = float(m["B"]) * m["heads"] * m["Nq"] * m["Nkv"]
+            xu_peak = 16.0 * torch.cuda.get_device_properties(dev).multi_processor_count * res["clocks"]["sm_mhz"] * 1e6
+            res["roofline"]["attention_xu"] = {
+                "bound": "xu (MUFU ex2)", "kernel": f"attention_kernel, {m['B']}x{m['heads']} heads, {m['Nq']}x{m['Nkv']}, d={m['d']}",
+                "launches_per_step": len(same), "us_per_launch_in_step": us, "exp_per_launch": exps, "achieved_gexp_s": exps / (us * 1e-6) / 1e9,
+                "peak_gexp_s": xu_peak / 1e9, "frac": exps / (us * 1e-6) / xu_peak, "tflops": m["flops"] / (us * 1e-6) / 1e12,
+                "peak_source": "16 ex2/clk/SM x SMs x median SM clock under load (clocks.sm_mhz)"}
         # HBM-bound kernels: algorithmic bytes = one read + one write of the tensor in bf16
         scale = step_ms / sum_ms
         hb = {}
