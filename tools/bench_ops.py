@@ -66,6 +66,12 @@ gn("gn_16x1024x640", 16, 1024, 640)
 gn("gn_16x256x1280", 16, 256, 1280)
 gn("gn_16x64x1280", 16, 64, 1280)
 gn("gn_16x64x2560", 16, 64, 2560)
+gn("gn_16x256x2560", 16, 256, 2560)
+gn("gn_16x1024x1280", 16, 1024, 1280)
+gn("gn_2x4096x320", 2, 4096, 320)
+gn("gn_2x1024x640", 2, 1024, 640)
+gn("gn_2x256x1280", 2, 256, 1280)
+gn("gn_2x64x1280", 2, 64, 1280)
 ln("ln_65536x320", 65536, 320)
 
 flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
