@@ -341,7 +341,8 @@ __device__ __forceinline__ void epilogue_geglu16(const GemmKParams& p, const Row
 // GEGLU: compile-time epilogue family.  The epilogue is the critical path of the short-K GEMMs and is bound by its register
 // allocation and dependent chains, not by its instruction count: code of the family NOT taken costs every launch (measured:
 // profiles/r02_ln_fold_experiment.txt), so the h * gelu(g) epilogue and the bias / residual / activation one are separate kernels.
-// EPI: 0 = any flag combination but GEGLU (runtime branches), 1 = GEGLU, 2 = bias only (or nothing), 3 = bias + residual.
+// EPI: 0 = any flag combination but GEGLU (runtime branches), 1 = GEGLU, 2 = bias only (or nothing), 3 = bias + residual,
+// 4 = split-K main kernel (fp32 partial tiles only; the reduce kernel owns the epilogue).
 template <int BN, int NCTA, int EPI>
 __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_constant__ GemmKParams p) {
   constexpr bool GEGLU = EPI == 1;
@@ -521,7 +522,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
     // Issuing a 128-row TMA box costs the issuing thread several hundred cycles, so it is kept off the epilogue warps:
     // this lane prefetches the residual sub-tiles of its group RES_AHEAD ahead into the ring slots and stores every
     // sub-tile its 128 epilogue threads have marked ready.
-    if ((EPI >= 2 || p.staged) && n_items > 0 && elect_one()) {
+    if (EPI != 4 && (EPI >= 2 || p.staged) && n_items > 0 && elect_one()) {
       const int g = warp - 10;
       constexpr bool geglu = GEGLU;
 #ifdef B200SD_GEMM_NORES  // diagnostic build only: residual sub-tiles are not loaded (nor added)
@@ -589,7 +590,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
         else mbar_arrive(&tempty_bar[a]);
       }
     };
-    if (EPI >= 2 || p.staged) {  // (families 2 and 3 are only planned for staged outputs)
+    if (EPI != 4 && (EPI >= 2 || p.staged)) {  // (families 2 and 3 are only planned for staged outputs)
       // ---- staged epilogue: sub-tiles go through an 8-slot swizzled smem ring; the residual sub-tile is prefetched by
       // TMA RES_AHEAD sub-tiles ahead into the slot it is added in, results leave by TMA store (coalesced, OOB clipped).
       constexpr bool geglu = GEGLU;
@@ -726,7 +727,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
         const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN;
         if (!tile_exists) {
           // phantom tile of an odd pair: nothing to write
-        } else if (p.splits > 1) {
+        } else if (EPI == 4 || (EPI == 0 && p.splits > 1)) {
           float* dst = p.partial +
                        (static_cast<long long>((t.ks * p.num_n_tiles + t.nt)) * p.num_m_tiles + t.mt) * (BM * BN) +
                        static_cast<long long>(r) * BN;
@@ -739,6 +740,8 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
             for (int j = 0; j < 4; ++j)
               reinterpret_cast<uint4*>(dst + c * 16)[j] = make_uint4(u[4 * j], u[4 * j + 1], u[4 * j + 2], u[4 * j + 3]);
           }
+        } else if (EPI == 4) {
+          // (unreachable: family 4 only writes partial tiles)
         } else if (GEGLU) {
           if constexpr (GEGLU && BN % 32 == 0) {
 #pragma unroll 1
@@ -845,7 +848,8 @@ int prepare_gemm_bn() {  // called at plan time (outside any stream capture)
   return 0;
 }
 // Epilogue family of a plan (the specialised families exist for the tile widths the UNet / VAE layers use).
-int epilogue_family(int bn, int flags, int staged) {
+int epilogue_family(int bn, int flags, int staged, int splits) {
+  if (splits > 1) return 4;
   if (flags & B200SD_GEMM_GEGLU) return 1;
   if (!staged || bn < 128) return 0;
   const int other = flags & ~(B200SD_GEMM_BIAS | B200SD_GEMM_RESIDUAL);
@@ -868,6 +872,7 @@ int dispatch_gemm_epi(int epi, const GemmPlan* pl, cudaStream_t s) {
   B200SD_GEMM_EPI(0)
   if constexpr (BN % 64 == 0) { B200SD_GEMM_EPI(1) }   // (a GEGLU tile holds whole 32-column h | g halves)
   if constexpr (BN >= 128) { B200SD_GEMM_EPI(2) B200SD_GEMM_EPI(3) }
+  B200SD_GEMM_EPI(4)
 #undef B200SD_GEMM_EPI
   return fail(B200SD_ERR_INVALID, "gemm: epilogue family %d not built for block_n %d", epi, BN);
 }
@@ -1181,7 +1186,7 @@ int plan_gemm(const b200sd_gemm& g, PlannedOp* out) {
   }
   pl->block_n = bn;
   pl->ncta = t.ncta;
-  pl->epi = epilogue_family(bn, kp.flags, kp.staged);
+  pl->epi = epilogue_family(bn, kp.flags, kp.staged, kp.splits);
   rc = prepare_gemm(bn, t.ncta, pl->epi);
   if (rc) { delete pl; return rc; }
   long long total_work = static_cast<long long>(t.num_pm) * t.num_n_tiles * t.splits;
