@@ -342,7 +342,8 @@ __device__ __forceinline__ void epilogue_geglu16(const GemmKParams& p, const Row
 // allocation and dependent chains, not by its instruction count: code of the family NOT taken costs every launch (measured:
 // profiles/r02_ln_fold_experiment.txt), so the h * gelu(g) epilogue and the bias / residual / activation one are separate kernels.
 // EPI: 0 = any flag combination but GEGLU (runtime branches), 1 = GEGLU, 2 = bias only (or nothing), 3 = bias + residual,
-// 4 = split-K main kernel (fp32 partial tiles only; the reduce kernel owns the epilogue).
+// 4 = split-K main kernel (fp32 partial tiles only; the reduce kernel owns the epilogue), 5 = bias + per-image row vector (the
+// time-embedding add of every resnet's conv1).
 template <int BN, int NCTA, int EPI>
 __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_constant__ GemmKParams p) {
   constexpr bool GEGLU = EPI == 1;
@@ -601,6 +602,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
 #endif
       const bool has_bias = (p.flags & B200SD_GEMM_BIAS) != 0;
       const bool extra = EPI == 0 && (p.flags & (B200SD_GEMM_BIAS_ROW | B200SD_GEMM_ROWVEC | B200SD_GEMM_SILU | B200SD_GEMM_QUICK_GELU | B200SD_GEMM_GELU)) != 0;
+      constexpr bool rowvec_only = EPI == 5;
       const int bn_out = geglu ? BN / 2 : BN;
       const int nsub = bn_out / 32;
       const int sw = (r >> 1) & 3;  // SWIZZLE_64B: 16-byte chunk index ^= (row / 2) % 4
@@ -688,6 +690,22 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
               }
             }
             if (extra) epilogue_extra32(p, ri, t.nt * BN + sub * 32, v);
+            if constexpr (rowvec_only) {
+              const int n = t.nt * BN + sub * 32;
+              if (ri.valid && n < p.N) {
+                const float* rv = p.rowvec + static_cast<long long>(ri.group) * p.ld_rowvec + n;
+                if (n + 32 <= p.N) {
+#pragma unroll
+                  for (int j = 0; j < 8; ++j) {
+                    const float4 b = __ldg(reinterpret_cast<const float4*>(rv) + j);
+                    v[4 * j + 0] += b.x; v[4 * j + 1] += b.y; v[4 * j + 2] += b.z; v[4 * j + 3] += b.w;
+                  }
+                } else {
+#pragma unroll
+                  for (int j = 0; j < 32; ++j) if (n + j < p.N) v[j] += __ldg(rv + j);
+                }
+              }
+            }
           }
           if (sub == my_last) release_acc(acc);  // accumulator fully read by this warp: hand it back to the MMA warp
           if (has_res) {
@@ -853,6 +871,7 @@ int epilogue_family(int bn, int flags, int staged, int splits) {
   if (flags & B200SD_GEMM_GEGLU) return 1;
   if (!staged || bn < 128) return 0;
   const int other = flags & ~(B200SD_GEMM_BIAS | B200SD_GEMM_RESIDUAL);
+  if (other == B200SD_GEMM_ROWVEC && !(flags & B200SD_GEMM_RESIDUAL)) return 5;
   if (other) return 0;
   return (flags & B200SD_GEMM_RESIDUAL) ? 3 : 2;
 }
@@ -871,7 +890,7 @@ int dispatch_gemm_epi(int epi, const GemmPlan* pl, cudaStream_t s) {
   if (epi == E) { if constexpr (LAUNCH) return launch_gemm_epi<BN, NCTA, E>(*pl, s); else return prepare_gemm_bn<BN, NCTA, E>(); }
   B200SD_GEMM_EPI(0)
   if constexpr (BN % 64 == 0) { B200SD_GEMM_EPI(1) }   // (a GEGLU tile holds whole 32-column h | g halves)
-  if constexpr (BN >= 128) { B200SD_GEMM_EPI(2) B200SD_GEMM_EPI(3) }
+  if constexpr (BN >= 128) { B200SD_GEMM_EPI(2) B200SD_GEMM_EPI(3) B200SD_GEMM_EPI(5) }
   B200SD_GEMM_EPI(4)
 #undef B200SD_GEMM_EPI
   return fail(B200SD_ERR_INVALID, "gemm: epilogue family %d not built for block_n %d", epi, BN);
