@@ -58,11 +58,45 @@ struct GNParams {
   bf16* out;
   float* partials;
   int chunks, ppc, cols, R;
+  double inv_cnt;  // 1 / (HW * channels per group)
 };
 
 __device__ __forceinline__ const bf16* gn_src(const GNParams& p, int n, int pix, int c0) {
   long long row = static_cast<long long>(n) * p.HW + pix;
   return (c0 < p.C1) ? p.x1 + row * p.ld1 + c0 : p.x2 + row * p.ld2 + (c0 - p.C1);
+}
+
+
+// Affine (+SiLU) on two values at once: packed FFMA2 / FMUL2 / FADD2 (two results per issue slot) around the four MUFU operations;
+// the same operation sequence as fmaf + silu_f (x * rcp(1 + ex2(-x * log2 e))), so the results are bit-identical to the scalar form.
+__device__ __forceinline__ uint32_t gn_affine_pack(float x0, float x1, float a0, float a1, float b0, float b1, bool silu) {
+  uint64_t Y = f32x2_fma(f32x2_pack(x0, x1), f32x2_pack(a0, a1), f32x2_pack(b0, b1));
+  if (silu) {
+    float e0, e1;
+    f32x2_unpack(f32x2_mul(Y, f32x2_pack(-1.4426950408889634f, -1.4426950408889634f)), e0, e1);
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e0) : "f"(e0));
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e1) : "f"(e1));
+    float d0, d1;
+    f32x2_unpack(f32x2_add(f32x2_pack(e0, e1), f32x2_pack(1.0f, 1.0f)), d0, d1);
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(d0) : "f"(d0));
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(d1) : "f"(d1));
+    Y = f32x2_mul(Y, f32x2_pack(d0, d1));
+  }
+  float y0, y1;
+  f32x2_unpack(Y, y0, y1);
+  return pack_bf16x2(y0, y1);
+}
+// mean and 1/sqrt(var + eps) of one group from its fp32 totals: the cancellation-prone step (E[x^2] - mean^2) in fp64 (three
+// operations), the reciprocal square root as MUFU.RSQ + one Newton step in fp32 (relative error ~1e-7) instead of an fp64
+// divide + square root (~150 instructions on a 1/64-rate pipe, once per CTA of every launch).
+__device__ __forceinline__ void gn_finalize(float S, float SS, double inv_cnt, float eps, float& mean, float& rstd) {
+  const double m = static_cast<double>(S) * inv_cnt;
+  const double var = static_cast<double>(SS) * inv_cnt - m * m;
+  const float v = fmaxf(static_cast<float>(var), 0.f) + eps;
+  float r = rsqrtf(v);
+  r = r * fmaf(-0.5f * v * r, r, 1.5f);
+  mean = static_cast<float>(m);
+  rstd = r;
 }
 
 // Deterministic fold of the per-thread channel sums (s, ss: 8 channels of pixel-row slot r) into per-group sums.
@@ -118,10 +152,12 @@ __global__ void gn_stats_kernel(const GNParams p) {
   for (int j = 0; j < 8; ++j) { s[j] = 0.f; ss[j] = 0.f; }
   const int pix_end = min((chunk + 1) * p.ppc, p.HW);
   int pix = chunk * p.ppc + r;
-  for (; pix + 3 * p.R < pix_end; pix += 4 * p.R) {  // 4 independent 16-byte loads in flight per thread
+  const bf16* src = gn_src(p, n, pix, c0);                               // pointer walk: no 64-bit multiplies in the loop
+  const long long step = static_cast<long long>(p.R) * (c0 < p.C1 ? p.ld1 : p.ld2);
+  for (; pix + 3 * p.R < pix_end; pix += 4 * p.R, src += 4 * step) {  // 4 independent 16-byte loads in flight per thread
     uint4 v4[4];
 #pragma unroll
-    for (int u = 0; u < 4; ++u) v4[u] = ldg_stream(gn_src(p, n, pix + u * p.R, c0));
+    for (int u = 0; u < 4; ++u) v4[u] = ldg_stream(src + u * step);
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
       uint32_t w[4] = {v4[u].x, v4[u].y, v4[u].z, v4[u].w};
@@ -133,8 +169,8 @@ __global__ void gn_stats_kernel(const GNParams p) {
       }
     }
   }
-  for (; pix < pix_end; pix += p.R) {
-    uint4 v = ldg_stream(gn_src(p, n, pix, c0));
+  for (; pix < pix_end; pix += p.R, src += step) {
+    uint4 v = ldg_stream(src);
     uint32_t w[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
@@ -153,21 +189,26 @@ __global__ void gn_stats_kernel(const GNParams p) {
 
 __global__ void gn_apply_kernel(const GNParams p) {
   pdl_launch_dependents();
-  pdl_wait();
-  extern __shared__ float sm[];  // a[C], b[C], mean[groups], rstd[groups]
-  float* sa = sm;
-  float* sb = sm + p.C;
-  float* smean = sb + p.C;
+  extern __shared__ float sm[];  // mean[groups], rstd[groups], red[parts][groups][2]
+  float* smean = sm;
   float* srstd = smean + p.groups;
   const int chunk = blockIdx.x, n = blockIdx.y;
   const int tid = threadIdx.x;
+  const int vcol = tid % p.cols, r = tid / p.cols;
+  const int c0 = vcol * 8;
+  // this thread's affine parameters: weights, not produced by the previous kernel -> fetched before the dependency wait
+  float a[8], b[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) { a[j] = __ldg(p.gamma + c0 + j); b[j] = __ldg(p.beta + c0 + j); }
+  pdl_wait();
   {
-    // all threads cooperate: thread -> (group, part); parts stride over the chunk partials, then a shared-memory fold
-    double* red = reinterpret_cast<double*>(srstd + p.groups);  // [parts][groups][2]
+    // all threads cooperate: thread -> (group, part); parts stride over the chunk partials (fp32 sums of fp32 partials, fixed
+    // order), then a shared-memory fold and the finalize of gn_finalize
+    float* red = srstd + p.groups;  // [parts][groups][2]
     const int parts = blockDim.x / p.groups;
     const int g = tid % p.groups, part = tid / p.groups;
     if (part < parts) {
-      double S = 0.0, SS = 0.0;
+      float S = 0.f, SS = 0.f;
       const float* src = p.partials + (static_cast<long long>(n) * p.chunks * p.groups + g) * 2;
       for (int c = part; c < p.chunks; c += parts) {
         const float2 v = *reinterpret_cast<const float2*>(src + static_cast<long long>(c) * p.groups * 2);
@@ -178,53 +219,43 @@ __global__ void gn_apply_kernel(const GNParams p) {
     }
     __syncthreads();
     if (tid < p.groups) {
-      double S = 0.0, SS = 0.0;
+      float S = 0.f, SS = 0.f;
       for (int q = 0; q < parts; ++q) { S += red[(q * p.groups + tid) * 2]; SS += red[(q * p.groups + tid) * 2 + 1]; }
-      const double cnt = static_cast<double>(p.HW) * p.cpg;
-      const double mean = S / cnt;
-      double var = SS / cnt - mean * mean;
-      if (var < 0.0) var = 0.0;
-      smean[tid] = static_cast<float>(mean);
-      srstd[tid] = static_cast<float>(1.0 / sqrt(var + static_cast<double>(p.eps)));
+      gn_finalize(S, SS, p.inv_cnt, p.eps, smean[tid], srstd[tid]);
     }
   }
   __syncthreads();
-  for (int c = tid; c < p.C; c += blockDim.x) {
-    const int g = c / p.cpg;
-    const float a = srstd[g] * __ldg(p.gamma + c);
-    sa[c] = a;
-    sb[c] = __ldg(p.beta + c) - smean[g] * a;
-  }
-  __syncthreads();
-  const int vcol = tid % p.cols, r = tid / p.cols;
-  const int c0 = vcol * 8;
-  float a[8], b[8];
 #pragma unroll
-  for (int j = 0; j < 8; ++j) { a[j] = sa[c0 + j]; b[j] = sb[c0 + j]; }
+  for (int j = 0; j < 8; ++j) {
+    const int g = (c0 + j) / p.cpg;
+    a[j] *= srstd[g];
+    b[j] -= smean[g] * a[j];
+  }
   const int pix_end = min((chunk + 1) * p.ppc, p.HW);
-  auto apply_store = [&](const uint4& v, int pix) {
-    uint32_t w[4] = {v.x, v.y, v.z, v.w};
+  const bool silu = p.silu != 0;
+  auto apply_store = [&](const uint4& v, bf16* dst) {
+    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
     uint32_t o[4];
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
-      float2 f = unpack_bf16x2(w[j]);
-      float y0 = fmaf(f.x, a[2 * j], b[2 * j]);
-      float y1 = fmaf(f.y, a[2 * j + 1], b[2 * j + 1]);
-      if (p.silu) { y0 = silu_f(y0); y1 = silu_f(y1); }
-      o[j] = pack_bf16x2(y0, y1);
+      const float2 f = unpack_bf16x2(w[j]);
+      o[j] = gn_affine_pack(f.x, f.y, a[2 * j], a[2 * j + 1], b[2 * j], b[2 * j + 1], silu);
     }
-    bf16* dst = p.out + (static_cast<long long>(n) * p.HW + pix) * p.C + c0;
     *reinterpret_cast<uint4*>(dst) = make_uint4(o[0], o[1], o[2], o[3]);
   };
   int pix = chunk * p.ppc + r;
-  for (; pix + 3 * p.R < pix_end; pix += 4 * p.R) {
+  const bf16* src = gn_src(p, n, pix, c0);  // pointer walk: no 64-bit multiplies in the loop
+  const long long sstep = static_cast<long long>(p.R) * (c0 < p.C1 ? p.ld1 : p.ld2);
+  bf16* dst = p.out + (static_cast<long long>(n) * p.HW + pix) * p.C + c0;
+  const long long dstep = static_cast<long long>(p.R) * p.C;
+  for (; pix + 3 * p.R < pix_end; pix += 4 * p.R, src += 4 * sstep, dst += 4 * dstep) {
     uint4 v4[4];
 #pragma unroll
-    for (int u = 0; u < 4; ++u) v4[u] = ldg_stream(gn_src(p, n, pix + u * p.R, c0));
+    for (int u = 0; u < 4; ++u) v4[u] = ldg_stream(src + u * sstep);
 #pragma unroll
-    for (int u = 0; u < 4; ++u) apply_store(v4[u], pix + u * p.R);
+    for (int u = 0; u < 4; ++u) apply_store(v4[u], dst + u * dstep);
   }
-  for (; pix < pix_end; pix += p.R) apply_store(ldg_stream(gn_src(p, n, pix, c0)), pix);
+  for (; pix < pix_end; pix += p.R, src += sstep, dst += dstep) apply_store(ldg_stream(src), dst);
 }
 
 // Single-launch GroupNorm for small images (the 8x8 level of the UNet, where the two-kernel form is bound by its
@@ -291,19 +322,14 @@ __global__ void __launch_bounds__(512) gn_fused_kernel(const GNParams p) {
   gn_fold_groups(p, reinterpret_cast<float*>(gnf_smem + GNF_HEADER_BYTES + GNF_MAX_DATA_BYTES), s, ss, r, c0, tid, nthreads, gsum);
   cluster_sync_all();  // every CTA's group sums are complete and visible cluster-wide
   if (tid < p.groups) {
-    double S = 0.0, SS = 0.0;
+    float S = 0.f, SS = 0.f;
     const uint32_t local = smem_u32(gsum + 2 * tid);
     for (int q = 0; q < p.chunks; ++q) {  // same order in every CTA: identical statistics across the cluster
       const uint32_t remote = mapa_u32(local, static_cast<uint32_t>(q));
       S += ld_shared_cluster_f32(remote);
       SS += ld_shared_cluster_f32(remote + 4);
     }
-    const double cnt = static_cast<double>(p.HW) * p.cpg;
-    const double mean = S / cnt;
-    double var = SS / cnt - mean * mean;
-    if (var < 0.0) var = 0.0;
-    smean[tid] = static_cast<float>(mean);
-    srstd[tid] = static_cast<float>(1.0 / sqrt(var + static_cast<double>(p.eps)));
+    gn_finalize(S, SS, p.inv_cnt, p.eps, smean[tid], srstd[tid]);
   }
   cluster_sync_all();  // peers have finished reading this CTA's sums (it may exit); mean / rstd visible to the CTA
   float a[8], b[8];
@@ -321,11 +347,8 @@ __global__ void __launch_bounds__(512) gn_fused_kernel(const GNParams p) {
     uint32_t o[4];
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
-      float2 f = unpack_bf16x2(w[j]);
-      float y0 = fmaf(f.x, a[2 * j], b[2 * j]);
-      float y1 = fmaf(f.y, a[2 * j + 1], b[2 * j + 1]);
-      if (p.silu) { y0 = silu_f(y0); y1 = silu_f(y1); }
-      o[j] = pack_bf16x2(y0, y1);
+      const float2 f = unpack_bf16x2(w[j]);
+      o[j] = gn_affine_pack(f.x, f.y, a[2 * j], a[2 * j + 1], b[2 * j], b[2 * j + 1], p.silu != 0);
     }
     bf16* dst = p.out + (static_cast<long long>(n) * p.HW + pix) * p.C + c0;
     *reinterpret_cast<uint4*>(dst) = make_uint4(o[0], o[1], o[2], o[3]);
@@ -947,6 +970,7 @@ int plan_groupnorm(const b200sd_groupnorm& g, PlannedOp* out) {
   p.x1 = static_cast<const bf16*>(g.x1); p.x2 = static_cast<const bf16*>(g.x2);
   p.ld1 = g.ld1; p.ld2 = g.ld2; p.C1 = g.C1; p.C2 = g.C2; p.C = C;
   p.NB = g.NB; p.HW = g.HW; p.groups = g.groups; p.cpg = C / g.groups; p.silu = g.silu; p.eps = g.eps;
+  p.inv_cnt = 1.0 / (static_cast<double>(g.HW) * (C / g.groups));
   p.gamma = g.gamma; p.beta = g.beta; p.out = static_cast<bf16*>(g.out); p.partials = g.partials;
   p.cols = C / 8;
   pl.fused = 0;
@@ -1161,6 +1185,7 @@ extern "C" int b200sd_groupnorm_static_scratch(int device, const b200sd_groupnor
   p.x1 = static_cast<const bf16*>(g.x1); p.x2 = static_cast<const bf16*>(g.x2);
   p.ld1 = g.ld1; p.ld2 = g.ld2; p.C1 = g.C1; p.C2 = g.C2; p.C = C;
   p.NB = g.NB; p.HW = g.HW; p.groups = g.groups; p.cpg = C / g.groups; p.silu = g.silu; p.eps = g.eps;
+  p.inv_cnt = 1.0 / (static_cast<double>(g.HW) * (C / g.groups));
   p.gamma = g.gamma; p.beta = g.beta; p.out = static_cast<bf16*>(g.out);
   p.chunks = groupnorm_chunks(g.NB, g.HW, C);
   p.ppc = (g.HW + p.chunks - 1) / p.chunks;
