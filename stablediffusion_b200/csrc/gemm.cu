@@ -16,6 +16,9 @@
 // bf16 -> swizzled smem ring -> TMA store), warps 10-11 issue the epilogue's TMA loads / stores.
 // Split-K (for the M=128..512 low-resolution levels) writes fp32 partial tiles that a second small kernel
 // reduces with the same epilogue; a weight-resident mode serves the short-K linears (see choose_gemm_tiling).
+// The kernel is instantiated once per tile shape AND epilogue family (generic / GEGLU / bias / bias + residual / split-K partials /
+// bias + row vector: epilogue_family): the epilogue is the critical path of the short-K GEMMs and is bound by its register allocation
+// and dependent chains, so code of a family not taken costs every launch (profiles/r02_gemm_epilogue_families_ab.txt).
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
