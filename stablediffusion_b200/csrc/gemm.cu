@@ -805,14 +805,21 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
   }
 }
 
-// Split-K reduction + epilogue.  grid = (tiles, BN/16 or BN/32 for GEGLU), block = 128 (thread = tile row).
+// Split-K reduction + epilogue.  grid = (tiles, row groups), block = 128.  Consecutive threads take consecutive 16-column chunks of
+// a tile row (a warp reads 1-2 whole rows of every partial tile: 64-byte pieces back to back, and writes its outputs the same way);
+// round 1 mapped a thread to a row, which made every warp access 32 pieces a kilobyte apart.
+__host__ __device__ constexpr int splitk_rows_per_block(int bn, bool geglu) { return 128 / (geglu ? bn / 32 : bn / 16); }
 template <int BN>
 __global__ void __launch_bounds__(128) gemm_splitk_reduce_kernel(const __grid_constant__ GemmKParams p) {
   pdl_launch_dependents();
   pdl_wait();
   const int tile = blockIdx.x;  // nt * num_m_tiles + mt
-  const int c = blockIdx.y;
-  const int r = threadIdx.x;
+  const bool is_geglu = (p.flags & B200SD_GEMM_GEGLU) != 0;
+  const int nchunks = is_geglu ? BN / 32 : BN / 16;
+  const int rpb = 128 / nchunks;
+  const int c = threadIdx.x % nchunks;
+  const int r = blockIdx.y * rpb + threadIdx.x / nchunks;
+  if (static_cast<int>(threadIdx.x) >= rpb * nchunks || r >= BM) return;
   const TileCoord t = decode_tile(p, tile % p.num_m_tiles, tile / p.num_m_tiles, 0);
   const RowInfo ri = row_info(p, t, r);
   const long long tile_elems = static_cast<long long>(BM) * BN;
@@ -1215,7 +1222,10 @@ int plan_gemm(const b200sd_gemm& g, PlannedOp* out) {
   pl->grid = static_cast<int>(std::min<long long>(total_work, std::max(1, sm_count() / t.ncta))) * t.ncta;
   if (t.wres) pl->grid = t.units_per_nt * t.num_n_tiles * t.ncta;  // unit u: N tile u % num_n_tiles, M slots u / num_n_tiles + k * units_per_nt
   pl->reduce_grid_x = t.num_m_tiles * t.num_n_tiles;
-  pl->reduce_grid_y = (g.flags & B200SD_GEMM_GEGLU) ? bn / 32 : bn / 16;
+  {
+    const int rpb = splitk_rows_per_block(bn, (g.flags & B200SD_GEMM_GEGLU) != 0);
+    pl->reduce_grid_y = (BM + rpb - 1) / rpb;
+  }
   out->kind = B200SD_OP_GEMM;
   out->plan = pl;
   out->launch = launch_gemm;
